@@ -1,0 +1,519 @@
+/*
+ * geom_oracle.c -- CPU restatement of the reference's point-cloud geometry kernels.
+ *
+ * TEST INFRASTRUCTURE ONLY.  This file is the parity oracle for tests/, for
+ * __graft_entry__.smoke() and for bench.py's cpu_baseline / --impl reference
+ * legs.  Nothing under graspnet-baseline_b200/ may import, link or call it.
+ *
+ * Every function restates the loop semantics of one legacy CUDA kernel of the
+ * reference (paths relative to /root/reference); the reference has NO CPU
+ * implementation of the pointnet2 ops (every wrapper ends in
+ * TORCH_CHECK(false,"CPU not supported"), e.g. pointnet2/_ext_src/src/sampling.cpp:39),
+ * so the rounding recipe follows what nvcc 12.9 -O2 (default --fmad=true)
+ * emits for those kernels on sm_100 -- checked with `cuobjdump -sass` on
+ * oracle/_ref (see DESIGN.md "Rounding recipes") and, on the GPU box, against
+ * the legacy extension itself (tests/test_gpu_vs_legacy.py).
+ *
+ * Parity status: pinned on the GPU box against oracle/_ref (the reference's own
+ * kernels, bit-exact indices) and, for knn, here against the reference's
+ * knn/src/cpu/knn_cpu.cpp (tests/golden/knn_*.npz).
+ *
+ * All fp32 arithmetic that feeds a comparison is written with explicit fmaf()
+ * / single operations and the file must be compiled with -ffp-contract=off so
+ * the compiler adds no contraction of its own.
+ */
+#define _GNU_SOURCE
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#if defined(__GNUC__) && defined(__x86_64__)
+#define HOT __attribute__((target_clones("fma", "default")))
+#else
+#define HOT
+#endif
+
+/* ------------------------------------------------------------------ helpers */
+
+/* squared norm / distance as the legacy pointnet2 kernels compute it:
+ * source  a*a + b*b + c*c  is contracted to  fma(c,c, fma(a,a, b*b))
+ * (sampling_gpu.cu:105,108-109; ball_query_gpu.cu:36-37; interpolate_gpu.cu:38) */
+static inline float sq3_p2(float a, float b, float c) {
+  float t = b * b;
+  t = fmaf(a, a, t);
+  return fmaf(c, c, t);
+}
+
+static inline unsigned bitrev(unsigned v, int bits) {
+  unsigned r = 0;
+  for (int i = 0; i < bits; ++i) r |= ((v >> i) & 1u) << (bits - 1 - i);
+  return r;
+}
+
+/* opt_n_threads(): largest power of two <= work_size, clamped to [1,512]
+ * (pointnet2/_ext_src/include/cuda_utils.h:18-24; the log() there is exact
+ * enough for every size below 2^24, which is what this restates). */
+int oracle_opt_n_threads(int work_size) {
+  int p = 1;
+  while (p * 2 <= work_size && p < 512) p *= 2;
+  return p;
+}
+
+/* ---------------------------------------------------------------- K1: FPS  */
+
+/*
+ * Literal simulation of furthest_point_sampling_kernel<BS>
+ * (sampling_gpu.cu:74-178): BS "threads" each scan k = tid, tid+BS, ... and
+ * keep their first strict maximum; then the stride-halving tree of __update()
+ * (sampling_gpu.cu:64-70) where slot idx1 survives unless v2 > v1.
+ * temp[] starts at 1e10 (sampling.cpp:78-80).  Points whose squared norm,
+ * promoted to double, is <= 1e-3 are skipped entirely (sampling_gpu.cu:105-106).
+ */
+HOT void oracle_fps_tree(const float *xyz, int b, int n, int m, int32_t *idx) {
+  if (m <= 0) return;
+  const int BS = oracle_opt_n_threads(n);
+  float *temp = (float *)malloc(sizeof(float) * (size_t)(n > 0 ? n : 1));
+  float *dists = (float *)malloc(sizeof(float) * 512);
+  int *dists_i = (int *)malloc(sizeof(int) * 512);
+  for (int bi = 0; bi < b; ++bi) {
+    const float *p = xyz + (size_t)bi * n * 3;
+    int32_t *out = idx + (size_t)bi * m;
+    for (int k = 0; k < n; ++k) temp[k] = 1e10f;
+    int old = 0;
+    out[0] = 0;
+    for (int j = 1; j < m; ++j) {
+      const float x1 = p[old * 3 + 0], y1 = p[old * 3 + 1], z1 = p[old * 3 + 2];
+      for (int tid = 0; tid < BS; ++tid) {
+        int besti = 0;
+        float best = -1.f;
+        for (int k = tid; k < n; k += BS) {
+          const float x2 = p[k * 3 + 0], y2 = p[k * 3 + 1], z2 = p[k * 3 + 2];
+          const float mag = sq3_p2(x2, y2, z2);
+          if ((double)mag <= 1e-3) continue;
+          const float d = sq3_p2(x2 - x1, y2 - y1, z2 - z1);
+          const float d2 = fminf(d, temp[k]);
+          temp[k] = d2;
+          besti = d2 > best ? k : besti;
+          best = d2 > best ? d2 : best;
+        }
+        dists[tid] = best;
+        dists_i[tid] = besti;
+      }
+      for (int s = BS / 2; s >= 1; s /= 2) {
+        for (int tid = 0; tid < s; ++tid) {
+          const float v1 = dists[tid], v2 = dists[tid + s];
+          const int i1 = dists_i[tid], i2 = dists_i[tid + s];
+          dists[tid] = fmaxf(v1, v2);
+          dists_i[tid] = v2 > v1 ? i2 : i1;
+        }
+      }
+      old = dists_i[0];
+      out[j] = old;
+    }
+  }
+  free(temp);
+  free(dists);
+  free(dists_i);
+}
+
+/*
+ * Same result through the closed-form winner rule the tree implies:
+ * maximise d2, break ties by the smallest bit-reversed (k mod BS) over
+ * log2(BS) bits, then by the smallest k.  This is the statement the CUDA
+ * kernel implements with a different thread mapping; tests check
+ * oracle_fps == oracle_fps_tree on tie-heavy inputs.
+ */
+HOT void oracle_fps(const float *xyz, int b, int n, int m, int32_t *idx) {
+  if (m <= 0) return;
+  const int BS = oracle_opt_n_threads(n);
+  int bits = 0;
+  while ((1 << bits) < BS) ++bits;
+  float *temp = (float *)malloc(sizeof(float) * (size_t)(n > 0 ? n : 1));
+  unsigned char *skip = (unsigned char *)malloc((size_t)(n > 0 ? n : 1));
+  uint32_t *prio = (uint32_t *)malloc(sizeof(uint32_t) * (size_t)(n > 0 ? n : 1));
+  for (int k = 0; k < n; ++k)
+    prio[k] = (bitrev((unsigned)k & (unsigned)(BS - 1), bits) << 22) | ((unsigned)k >> bits);
+  for (int bi = 0; bi < b; ++bi) {
+    const float *p = xyz + (size_t)bi * n * 3;
+    int32_t *out = idx + (size_t)bi * m;
+    for (int k = 0; k < n; ++k) {
+      temp[k] = 1e10f;
+      skip[k] = (double)sq3_p2(p[k * 3], p[k * 3 + 1], p[k * 3 + 2]) <= 1e-3;
+    }
+    int old = 0;
+    out[0] = 0;
+    for (int j = 1; j < m; ++j) {
+      const float x1 = p[old * 3 + 0], y1 = p[old * 3 + 1], z1 = p[old * 3 + 2];
+      float best = -1.f;
+      uint32_t bestp = 0xffffffffu;
+      int besti = 0;
+      for (int k = 0; k < n; ++k) {
+        if (skip[k]) continue;
+        const float d = sq3_p2(p[k * 3] - x1, p[k * 3 + 1] - y1, p[k * 3 + 2] - z1);
+        const float d2 = fminf(d, temp[k]);
+        temp[k] = d2;
+        if (d2 > best || (d2 == best && prio[k] < bestp)) {
+          best = d2;
+          bestp = prio[k];
+          besti = k;
+        }
+      }
+      old = besti;
+      out[j] = old;
+    }
+  }
+  free(temp);
+  free(skip);
+  free(prio);
+}
+
+/* ------------------------------------------------------- K2/K3: gather(+grad) */
+
+/* out[b,c,j] = points[b,c,idx[b,j]]           (sampling_gpu.cu:13-25) */
+void oracle_gather_points(const float *points, const int32_t *idx, int b, int c, int n, int m,
+                          float *out) {
+  for (int i = 0; i < b; ++i)
+    for (int l = 0; l < c; ++l)
+      for (int j = 0; j < m; ++j)
+        out[((size_t)i * c + l) * m + j] = points[((size_t)i * c + l) * n + idx[(size_t)i * m + j]];
+}
+
+/* grad_points[b,c,idx[b,j]] += grad_out[b,c,j], zero-initialised
+ * (sampling_gpu.cu:39-52, sampling.cpp:56-58).  The legacy kernel uses f32
+ * atomicAdd in nondeterministic order; the oracle accumulates in fp64 and
+ * rounds once, tests compare within 1e-5 relative. */
+void oracle_gather_points_grad(const float *grad_out, const int32_t *idx, int b, int c, int n,
+                               int m, float *grad_points) {
+  double *acc = (double *)calloc((size_t)(n > 0 ? n : 1), sizeof(double));
+  for (int i = 0; i < b; ++i)
+    for (int l = 0; l < c; ++l) {
+      memset(acc, 0, sizeof(double) * (size_t)n);
+      for (int j = 0; j < m; ++j)
+        acc[idx[(size_t)i * m + j]] += (double)grad_out[((size_t)i * c + l) * m + j];
+      for (int k = 0; k < n; ++k) grad_points[((size_t)i * c + l) * n + k] = (float)acc[k];
+    }
+  free(acc);
+}
+
+/* ---------------------------------------------------------- K4: ball query */
+
+/* ball_query_gpu.cu:14-49 + zero-init of idx in ball_query.cpp:24-26.
+ * radius2 = radius*radius in f32; strict d2 < radius2; scan in index order;
+ * first hit pre-fills all nsample slots; stop after nsample hits. */
+HOT void oracle_ball_query(const float *new_xyz, const float *xyz, int b, int n, int m,
+                           float radius, int nsample, int32_t *idx) {
+  const float radius2 = radius * radius;
+  memset(idx, 0, sizeof(int32_t) * (size_t)b * m * nsample);
+#pragma omp parallel for collapse(2) schedule(static)
+  for (int bi = 0; bi < b; ++bi)
+    for (int j = 0; j < m; ++j) {
+      const float *c = new_xyz + ((size_t)bi * m + j) * 3;
+      const float *p = xyz + (size_t)bi * n * 3;
+      int32_t *o = idx + ((size_t)bi * m + j) * nsample;
+      const float cx = c[0], cy = c[1], cz = c[2];
+      int cnt = 0;
+      for (int k = 0; k < n && cnt < nsample; ++k) {
+        const float d2 = sq3_p2(cx - p[k * 3], cy - p[k * 3 + 1], cz - p[k * 3 + 2]);
+        if (d2 < radius2) {
+          if (cnt == 0)
+            for (int l = 0; l < nsample; ++l) o[l] = k;
+          o[cnt++] = k;
+        }
+      }
+    }
+}
+
+/* ------------------------------------------------------ K5: cylinder query */
+
+/* cylinder_query_gpu.cu:9-57.  p = xyz[k] - new_xyz[j];
+ * x_rot = fma(r6,z, fma(r0,x, r3*y)), y_rot = fma(r7,z, fma(r1,x, r4*y)),
+ * z_rot = fma(r8,z, fma(r2,x, r5*y)), d2 = fma(y_rot,y_rot, z_rot*z_rot);
+ * accept iff d2 < r^2 && x_rot > hmin && x_rot < hmax (all strict). */
+HOT void oracle_cylinder_query(const float *new_xyz, const float *xyz, const float *rot, int b,
+                               int n, int m, float radius, float hmin, float hmax, int nsample,
+                               int32_t *idx) {
+  const float radius2 = radius * radius;
+  memset(idx, 0, sizeof(int32_t) * (size_t)b * m * nsample);
+#pragma omp parallel for collapse(2) schedule(static)
+  for (int bi = 0; bi < b; ++bi)
+    for (int j = 0; j < m; ++j) {
+      const float *c = new_xyz + ((size_t)bi * m + j) * 3;
+      const float *r = rot + ((size_t)bi * m + j) * 9;
+      const float *p = xyz + (size_t)bi * n * 3;
+      int32_t *o = idx + ((size_t)bi * m + j) * nsample;
+      int cnt = 0;
+      for (int k = 0; k < n && cnt < nsample; ++k) {
+        const float x = p[k * 3] - c[0], y = p[k * 3 + 1] - c[1], z = p[k * 3 + 2] - c[2];
+        const float xr = fmaf(r[6], z, fmaf(r[0], x, r[3] * y));
+        const float yr = fmaf(r[7], z, fmaf(r[1], x, r[4] * y));
+        const float zr = fmaf(r[8], z, fmaf(r[2], x, r[5] * y));
+        const float d2 = fmaf(yr, yr, zr * zr);
+        if (d2 < radius2 && xr > hmin && xr < hmax) {
+          if (cnt == 0)
+            for (int l = 0; l < nsample; ++l) o[l] = k;
+          o[cnt++] = k;
+        }
+      }
+    }
+}
+
+/* ------------------------------------------------------ K6/K7: group(+grad) */
+
+/* out[b,l,j,k] = points[b,l,idx[b,j,k]]     (group_points_gpu.cu:13-33) */
+void oracle_group_points(const float *points, const int32_t *idx, int b, int c, int n, int m,
+                         int ns, float *out) {
+#pragma omp parallel for collapse(2) schedule(static)
+  for (int i = 0; i < b; ++i)
+    for (int l = 0; l < c; ++l) {
+      const float *src = points + ((size_t)i * c + l) * n;
+      const int32_t *id = idx + (size_t)i * m * ns;
+      float *dst = out + ((size_t)i * c + l) * m * ns;
+      for (size_t t = 0; t < (size_t)m * ns; ++t) dst[t] = src[id[t]];
+    }
+}
+
+/* grad_points[b,l,idx[b,j,k]] += grad_out[b,l,j,k]  (group_points_gpu.cu:48-69),
+ * fp64 accumulation (legacy: f32 atomics, unordered) -> tolerance compare. */
+void oracle_group_points_grad(const float *grad_out, const int32_t *idx, int b, int c, int n,
+                              int m, int ns, float *grad_points) {
+#pragma omp parallel for collapse(2) schedule(static)
+  for (int i = 0; i < b; ++i)
+    for (int l = 0; l < c; ++l) {
+      double *acc = (double *)calloc((size_t)(n > 0 ? n : 1), sizeof(double));
+      const float *g = grad_out + ((size_t)i * c + l) * m * ns;
+      const int32_t *id = idx + (size_t)i * m * ns;
+      for (size_t t = 0; t < (size_t)m * ns; ++t) acc[id[t]] += (double)g[t];
+      for (int k = 0; k < n; ++k) grad_points[((size_t)i * c + l) * n + k] = (float)acc[k];
+      free(acc);
+    }
+}
+
+/* ------------------------------------------------------------ K8: three_nn */
+
+/* interpolate_gpu.cu:14-64.  d = f32 squared distance (contracted as sq3_p2 of
+ * (u - k)); running bests are double initialised 1e40, comparisons strict,
+ * index-order scan; outputs stored as f32 (1e40 -> +inf) and int. */
+HOT void oracle_three_nn(const float *unknown, const float *known, int b, int n, int m,
+                         float *dist2, int32_t *idx) {
+#pragma omp parallel for collapse(2) schedule(static)
+  for (int bi = 0; bi < b; ++bi)
+    for (int j = 0; j < n; ++j) {
+      const float *u = unknown + ((size_t)bi * n + j) * 3;
+      const float *kn = known + (size_t)bi * m * 3;
+      double best1 = 1e40, best2 = 1e40, best3 = 1e40;
+      int i1 = 0, i2 = 0, i3 = 0;
+      for (int k = 0; k < m; ++k) {
+        const float d = sq3_p2(u[0] - kn[k * 3], u[1] - kn[k * 3 + 1], u[2] - kn[k * 3 + 2]);
+        if (d < best1) {
+          best3 = best2; i3 = i2;
+          best2 = best1; i2 = i1;
+          best1 = d; i1 = k;
+        } else if (d < best2) {
+          best3 = best2; i3 = i2;
+          best2 = d; i2 = k;
+        } else if (d < best3) {
+          best3 = d; i3 = k;
+        }
+      }
+      float *od = dist2 + ((size_t)bi * n + j) * 3;
+      int32_t *oi = idx + ((size_t)bi * n + j) * 3;
+      od[0] = (float)best1; od[1] = (float)best2; od[2] = (float)best3;
+      oi[0] = i1; oi[1] = i2; oi[2] = i3;
+    }
+}
+
+/* ------------------------------------------- K9/K10: three_interpolate(+grad) */
+
+/* out[b,l,j] = sum_t points[b,l,idx[b,j,t]] * w[b,j,t]  (interpolate_gpu.cu:77-106).
+ * nvcc contracts to one multiply and two FMAs, the leading term varies
+ * across unrolled copies, so this is a 1e-5-relative quantity; the oracle
+ * evaluates it in fp64 and rounds once. */
+void oracle_three_interpolate(const float *points, const int32_t *idx, const float *weight, int b,
+                              int c, int m, int n, float *out) {
+#pragma omp parallel for collapse(2) schedule(static)
+  for (int i = 0; i < b; ++i)
+    for (int l = 0; l < c; ++l) {
+      const float *src = points + ((size_t)i * c + l) * m;
+      for (int j = 0; j < n; ++j) {
+        const int32_t *id = idx + ((size_t)i * n + j) * 3;
+        const float *w = weight + ((size_t)i * n + j) * 3;
+        out[((size_t)i * c + l) * n + j] =
+            (float)((double)src[id[0]] * w[0] + (double)src[id[1]] * w[1] + (double)src[id[2]] * w[2]);
+      }
+    }
+}
+
+/* grad_points[b,l,idx_t] += grad_out[b,l,j] * w_t  (interpolate_gpu.cu:121-148) */
+void oracle_three_interpolate_grad(const float *grad_out, const int32_t *idx, const float *weight,
+                                   int b, int c, int n, int m, float *grad_points) {
+#pragma omp parallel for collapse(2) schedule(static)
+  for (int i = 0; i < b; ++i)
+    for (int l = 0; l < c; ++l) {
+      double *acc = (double *)calloc((size_t)(m > 0 ? m : 1), sizeof(double));
+      const float *g = grad_out + ((size_t)i * c + l) * n;
+      for (int j = 0; j < n; ++j) {
+        const int32_t *id = idx + ((size_t)i * n + j) * 3;
+        const float *w = weight + ((size_t)i * n + j) * 3;
+        for (int t = 0; t < 3; ++t) acc[id[t]] += (double)(g[j] * w[t]);
+      }
+      for (int k = 0; k < m; ++k) grad_points[((size_t)i * c + l) * m + k] = (float)acc[k];
+      free(acc);
+    }
+}
+
+/* ---------------------------------------------------------------- K11/K12: knn */
+
+/*
+ * knn/src/cuda/knn.cu:36-176 (+ knn.h:12-65).  ref (b,dim,nr), query (b,dim,nq)
+ * channel-major; out ind (b,k,nq) int64, 1-BASED.  Distance = fma chain from 0
+ * in dim order (ssd = fma(t,t,ssd), t = ref - query; zero padding to 16 adds
+ * exact zeros).  Selection = stable top-k: smallest distance first, ties keep
+ * the lower reference index (strict '<' / first 'p_dist[a] > curr', knn.cu:131-171).
+ * `fma_chain` = 1 restates the GPU kernel; 0 restates knn_cpu.cpp:12-14
+ * (separate multiply and add as g++ emits for baseline x86-64).
+ */
+HOT void oracle_knn(const float *ref, const float *query, int b, int dim, int nr, int nq, int k,
+                    int fma_chain, int64_t *ind) {
+#pragma omp parallel for collapse(2) schedule(static)
+  for (int bi = 0; bi < b; ++bi)
+    for (int q = 0; q < nq; ++q) {
+      const float *R = ref + (size_t)bi * dim * nr;
+      const float *Q = query + (size_t)bi * dim * nq;
+      int64_t *o = ind + (size_t)bi * k * nq + q;
+      const int kk = k < nr ? k : nr;
+      float *bd = (float *)malloc(sizeof(float) * (size_t)(kk > 0 ? kk : 1));
+      int64_t *bi_ = (int64_t *)malloc(sizeof(int64_t) * (size_t)(kk > 0 ? kk : 1));
+      int have = 0;
+      for (int r = 0; r < nr; ++r) {
+        float ssd = 0.f;
+        for (int h = 0; h < dim; ++h) {
+          const float t = R[(size_t)h * nr + r] - Q[(size_t)h * nq + q];
+          if (fma_chain) ssd = fmaf(t, t, ssd);
+          else { const float sq = t * t; ssd = ssd + sq; }
+        }
+        if (have < kk) {
+          int pos = have;
+          while (pos > 0 && bd[pos - 1] > ssd) { bd[pos] = bd[pos - 1]; bi_[pos] = bi_[pos - 1]; --pos; }
+          bd[pos] = ssd; bi_[pos] = r + 1;
+          ++have;
+        } else if (kk > 0 && ssd < bd[kk - 1]) {
+          int pos = kk - 1;
+          while (pos > 0 && bd[pos - 1] > ssd) { bd[pos] = bd[pos - 1]; bi_[pos] = bi_[pos - 1]; --pos; }
+          bd[pos] = ssd; bi_[pos] = r + 1;
+        }
+      }
+      for (int t = 0; t < kk; ++t) o[(size_t)t * nq] = bi_[t];
+      free(bd);
+      free(bi_);
+    }
+}
+
+/* ------------------------------------------------------ C5: collision counts */
+
+/*
+ * Integer part of ModelFreeCollisionDetector.detect
+ * (utils/collision_detector.py:69-100,119): for every grasp g and scene point
+ * p (fp64): t = (p - T_g) . R_g  evaluated as numpy's matmul evaluates it for
+ * a (N,3)x(3,3) fp64 product -- tests/golden/collision_*.npz pins which
+ * association that is (see oracle/collision_oracle.py) -- then the eight
+ * half-space masks against per-grasp thresholds that the HOST computed with
+ * the reference's own dtype rules (thr[g][0..9], fp64 holding f32-rounded
+ * values where the reference rounds to f32).  Outputs six counts per grasp:
+ * global, left, right, bottom, shifting, inner.
+ *   thr: 0 -h/2   1 h/2   2 d-fl   3 d   4 -(w/2+fw)   5 -w/2   6 w/2+fw   7 w/2
+ *        8 d-fl-fw   9 d-fl-fw-ad
+ * `mode` selects the product association: 0 = ((x*r0 + y*r1) + z*r2) plain
+ * multiply/add, 1 = fma(z,r2, fma(y,r1, x*r0)).
+ */
+HOT void oracle_collision_counts(const double *scene, int n, const double *T, const double *R,
+                                 const double *thr, int m, int mode, int32_t *counts) {
+#pragma omp parallel for schedule(static)
+  for (int g = 0; g < m; ++g) {
+    const double *t = T + (size_t)g * 3, *r = R + (size_t)g * 9, *h = thr + (size_t)g * 10;
+    int cg = 0, cl = 0, cr = 0, cb = 0, cs = 0, ci = 0;
+    for (int k = 0; k < n; ++k) {
+      const double x = scene[k * 3] - t[0], y = scene[k * 3 + 1] - t[1], z = scene[k * 3 + 2] - t[2];
+      double tx, ty, tz;
+      if (mode == 0) {
+        tx = (x * r[0] + y * r[3]) + z * r[6];
+        ty = (x * r[1] + y * r[4]) + z * r[7];
+        tz = (x * r[2] + y * r[5]) + z * r[8];
+      } else {
+        tx = fma(z, r[6], fma(y, r[3], x * r[0]));
+        ty = fma(z, r[7], fma(y, r[4], x * r[1]));
+        tz = fma(z, r[8], fma(y, r[5], x * r[2]));
+      }
+      const int m1 = (tz > h[0]) & (tz < h[1]);
+      const int m2 = (tx > h[2]) & (tx < h[3]);
+      const int m3 = ty > h[4];
+      const int m4 = ty < h[5];
+      const int m5 = ty < h[6];
+      const int m6 = ty > h[7];
+      const int m7 = (tx <= h[2]) & (tx > h[8]);
+      const int m8 = (tx <= h[8]) & (tx > h[9]);
+      const int left = m1 & m2 & m3 & m4;
+      const int right = m1 & m2 & m5 & m6;
+      const int bottom = m1 & m3 & m5 & m7;
+      const int shifting = m1 & m3 & m5 & m8;
+      cg += left | right | bottom | shifting;
+      cl += left; cr += right; cb += bottom; cs += shifting;
+      ci += m1 & m2 & (!m4) & (!m6);
+    }
+    int32_t *o = counts + (size_t)g * 6;
+    o[0] = cg; o[1] = cl; o[2] = cr; o[3] = cb; o[4] = cs; o[5] = ci;
+  }
+}
+
+/* ------------------------------------------------------------------ C6: NMS */
+
+/*
+ * Restatement of graspnetAPI GraspGroup.nms -> grasp_nms.nms_grasp (third-party,
+ * NOT under /root/reference: parity UNPINNED).  grasps (m,17)
+ * fp32 rows [score,w,h,d,R(9),t(3),obj]; order = stable descending score;
+ * greedy sweep: a kept grasp i suppresses every later j with
+ *   sqrt(|t_i-t_j|^2) < translation_thresh  AND  (trace(R_i R_j^T)-1)/2 > cos_rot_thresh
+ * evaluated in fp64 with fixed association (sums left to right, no fma).
+ * (angle < thr  <=>  cos(angle) > cos(thr); cos_rot_thresh is computed once
+ * by the host so both sides use only exactly-rounded operations.)
+ * keep[] receives the original row numbers of the survivors in score order;
+ * returns their count.
+ */
+static int cmp_desc_stable(const void *a, const void *b, void *ctx) {
+  const float *g = (const float *)ctx;
+  const int ia = *(const int *)a, ib = *(const int *)b;
+  const float sa = g[(size_t)ia * 17], sb = g[(size_t)ib * 17];
+  if (sa > sb) return -1;
+  if (sa < sb) return 1;
+  return ia < ib ? -1 : (ia > ib);
+}
+
+int oracle_grasp_nms(const float *grasps, int m, double translation_thresh, double cos_rot_thresh,
+                     int32_t *keep) {
+  int *order = (int *)malloc(sizeof(int) * (size_t)(m > 0 ? m : 1));
+  unsigned char *dead = (unsigned char *)calloc((size_t)(m > 0 ? m : 1), 1);
+  for (int i = 0; i < m; ++i) order[i] = i;
+  qsort_r(order, (size_t)m, sizeof(int), cmp_desc_stable, (void *)grasps);
+  int nk = 0;
+  for (int a = 0; a < m; ++a) {
+    if (dead[a]) continue;
+    const float *gi = grasps + (size_t)order[a] * 17;
+    keep[nk++] = order[a];
+    for (int c = a + 1; c < m; ++c) {
+      if (dead[c]) continue;
+      const float *gj = grasps + (size_t)order[c] * 17;
+      const double dx = (double)gi[13] - (double)gj[13];
+      const double dy = (double)gi[14] - (double)gj[14];
+      const double dz = (double)gi[15] - (double)gj[15];
+      const double dist = sqrt((dx * dx + dy * dy) + dz * dz);
+      if (!(dist < translation_thresh)) continue;
+      double tr = 0.0;
+      for (int e = 0; e < 9; ++e) tr = tr + (double)gi[4 + e] * (double)gj[4 + e];
+      const double c_ang = (tr - 1.0) / 2.0;
+      if (c_ang > cos_rot_thresh) dead[c] = 1;
+    }
+  }
+  free(order);
+  free(dead);
+  return nk;
+}

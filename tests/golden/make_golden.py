@@ -1,0 +1,144 @@
+#!/usr/bin/env python
+"""Generates tests/golden/*.npz by RUNNING THE REFERENCE in the build container.
+
+Needs /root/reference (read-only) and oracle/_ref (python oracle/build_ref.py);
+neither exists on the GPU box, which only reads the committed .npz files.
+
+  collision_*.npz : utils/collision_detector.py::ModelFreeCollisionDetector.detect run
+                    VERBATIM (module imported from /root/reference with a stub `open3d`
+                    whose voxel_down_sample is the identity -- the module only touches
+                    open3d in __init__, collision_detector.py:32-35) on small seeded
+                    scenes + grasps; stores inputs and every output of detect().
+  knn_*.npz       : the reference's own CPU knn (knn/src/cpu/knn_cpu.cpp through
+                    knn/src/knn.h:53-63, compiled unmodified into oracle/_ref) on seeded
+                    inputs; stores inputs and the 1-based int64 indices.
+No pointnet2 fixture can be produced here: every pointnet2 op of the reference is
+CUDA-only and this container has no GPU -- those are pinned on the GPU box against
+oracle/_ref directly (tests/test_gpu_vs_legacy.py).
+"""
+import os
+import sys
+import types
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+REF = "/root/reference"
+
+
+def _stub_open3d():
+    o3d = types.ModuleType("open3d")
+
+    class _PC:
+        def __init__(self):
+            self.points = None
+
+        def voxel_down_sample(self, voxel_size):
+            return self
+
+    o3d.geometry = types.SimpleNamespace(PointCloud=_PC)
+    o3d.utility = types.SimpleNamespace(Vector3dVector=lambda a: np.asarray(a, dtype=np.float64))
+    sys.modules["open3d"] = o3d
+
+
+class _GG:
+    """Minimal stand-in exposing exactly the accessors detect() reads
+    (collision_detector.py:70-74) over a (M,17) array, dtype preserved."""
+
+    def __init__(self, arr):
+        self.a = arr
+
+    translations = property(lambda s: s.a[:, 13:16])
+    rotation_matrices = property(lambda s: s.a[:, 4:13].reshape(-1, 3, 3))
+    heights = property(lambda s: s.a[:, 2])
+    depths = property(lambda s: s.a[:, 3])
+    widths = property(lambda s: s.a[:, 1])
+
+
+def synth_scene(rng, n):
+    """table plane + a few blobs, camera frame, metres, fp64."""
+    npl = n * 6 // 10
+    plane = np.stack([rng.uniform(-0.3, 0.3, npl), rng.uniform(-0.3, 0.3, npl),
+                      0.6 + rng.normal(0, 0.001, npl)], 1)
+    blobs = []
+    for _ in range(8):
+        c = np.array([rng.uniform(-0.2, 0.2), rng.uniform(-0.2, 0.2), rng.uniform(0.5, 0.58)])
+        blobs.append(c + rng.uniform(-0.04, 0.04, ((n - npl) // 8 + 1, 3)))
+    return np.concatenate([plane] + blobs)[:n]
+
+
+def rot_from_view(towards, angle):
+    """orthonormal frame whose x axis is `towards`, rotated in-plane by `angle`
+    (own construction; only needs to yield realistic proper rotations)."""
+    ax = towards / np.linalg.norm(towards)
+    ay = np.array([-ax[1], ax[0], 0.0])
+    if np.linalg.norm(ay) < 1e-9:
+        ay = np.array([0.0, 1.0, 0.0])
+    ay /= np.linalg.norm(ay)
+    az = np.cross(ax, ay)
+    R1 = np.array([[1, 0, 0], [0, np.cos(angle), -np.sin(angle)], [0, np.sin(angle), np.cos(angle)]])
+    return np.stack([ax, ay, az], 1) @ R1
+
+
+def synth_grasps(rng, scene, m, dtype=np.float32):
+    g = np.zeros((m, 17), np.float64)
+    g[:, 0] = rng.uniform(0, 1, m)
+    g[:, 1] = rng.uniform(0, 0.1, m)
+    g[:, 2] = 0.02
+    g[:, 3] = rng.integers(1, 5, m) * 0.01
+    for i in range(m):
+        v = rng.normal(size=3)
+        v[2] = abs(v[2]) + 0.3
+        g[i, 4:13] = rot_from_view(v, rng.integers(0, 12) * np.pi / 12).reshape(-1)
+    g[:, 13:16] = scene[rng.choice(len(scene), m, replace=len(scene) < m)]
+    g[:, 16] = -1
+    return g.astype(dtype)
+
+
+def make_collision():
+    _stub_open3d()
+    sys.path.insert(0, os.path.join(REF, "utils"))
+    import collision_detector as cd
+    cases = [("a", 0, 3000, 200, np.float32, 0.01, 0.05, 0.01),
+             ("b", 1, 1500, 64, np.float32, 0.005, 0.03, 0.05),
+             ("c", 2, 800, 33, np.float64, 0.01, 0.005, 0.01),   # approach_dist < finger_width
+             ("d", 3, 1, 5, np.float32, 0.01, 0.05, 0.01)]       # single scene point
+    for name, seed, n, m, dt, voxel, ad, thr in cases:
+        rng = np.random.default_rng(seed)
+        scene = synth_scene(rng, max(n, 16))[:n]
+        grasps = synth_grasps(rng, scene, m, dt)
+        det = cd.ModelFreeCollisionDetector(scene, voxel_size=voxel)
+        mask, empty, ious = det.detect(_GG(grasps), approach_dist=ad, collision_thresh=thr,
+                                       return_empty_grasp=True, empty_thresh=0.01, return_ious=True)
+        mask_only = det.detect(_GG(grasps), approach_dist=ad, collision_thresh=thr)
+        assert (mask_only == mask).all()
+        np.savez_compressed(os.path.join(HERE, f"collision_{name}.npz"), scene=scene, grasps=grasps,
+                            voxel_size=voxel, approach_dist=ad, collision_thresh=thr,
+                            empty_thresh=0.01, mask=mask, empty=empty, ious=np.stack(ious))
+        print("collision", name, scene.shape, grasps.shape, grasps.dtype, int(mask.sum()), int(empty.sum()))
+
+
+def make_knn():
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "oracle", "_ref"))
+    from knn_pytorch import knn_pytorch
+    cases = [("a", 0, 1, 3, 300, 300, 1), ("b", 1, 2, 3, 700, 128, 1), ("c", 2, 1, 3, 50, 7, 4),
+             ("d", 3, 1, 5, 64, 33, 3), ("e", 4, 1, 3, 200, 64, 1)]
+    for name, seed, b, d, nr, nq, k in cases:
+        g = torch.Generator().manual_seed(seed)
+        ref = torch.randn(b, d, nr, generator=g)
+        query = torch.randn(b, d, nq, generator=g)
+        if name == "e":  # grid-snapped: exact distance ties
+            ref = torch.round(ref * 2) / 2
+            query = torch.round(query * 2) / 2
+        inds = torch.empty(b, k, nq).long()
+        knn_pytorch.knn(ref.contiguous(), query.contiguous(), inds)
+        np.savez_compressed(os.path.join(HERE, f"knn_{name}.npz"), ref=ref.numpy(), query=query.numpy(),
+                            k=k, inds=inds.numpy())
+        print("knn", name, tuple(ref.shape), tuple(query.shape), k)
+
+
+if __name__ == "__main__":
+    make_collision()
+    make_knn()
