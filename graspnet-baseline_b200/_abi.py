@@ -1,0 +1,56 @@
+"""ctypes binding of libb200grasp.so (include/b200grasp.h).
+
+The CUDA library is the ONLY implementation: if it is missing this module raises
+at import, there is no CPU or PyTorch fallback anywhere in the package.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libb200grasp.so")
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        "b200grasp: %s not found -- build it with `python graspnet-baseline_b200/build.py` "
+        "(nvcc, sm_100a). There is no fallback path." % LIB_PATH)
+
+lib = ctypes.CDLL(LIB_PATH)
+
+_vp, _i, _f, _d, _sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_double, ctypes.c_size_t
+
+# name -> argtypes, in the order of include/b200grasp.h
+SIGNATURES = {
+    "b200_furthest_point_sampling": [_vp, _i, _i, _i, _vp, _vp],
+    "b200_gather_points": [_vp, _vp, _i, _i, _i, _i, _vp, _vp],
+    "b200_gather_points_grad": [_vp, _vp, _i, _i, _i, _i, _vp, _vp],
+    "b200_ball_query": [_vp, _vp, _i, _i, _i, _f, _i, _vp, _vp],
+    "b200_cylinder_query": [_vp, _vp, _vp, _i, _i, _i, _f, _f, _f, _i, _vp, _vp],
+    "b200_cylinder_query_multi": [_vp, _vp, _vp, _i, _i, _i, _f, _f, ctypes.POINTER(_f), _i, _i, _vp, _vp],
+    "b200_group_points": [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp],
+    "b200_group_points_grad": [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp],
+    "b200_three_nn": [_vp, _vp, _i, _i, _i, _vp, _vp, _vp],
+    "b200_three_interpolate": [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp],
+    "b200_three_interpolate_grad": [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp],
+    "b200_knn": [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp],
+    "b200_collision_counts": [_vp, _i, _vp, _vp, _vp, _i, _vp, _vp],
+    "b200_grasp_nms": [_vp, _i, _d, _d, _vp, _vp, _vp, _sz, _vp],
+}
+for _name, _args in SIGNATURES.items():
+    _fn = getattr(lib, _name)
+    _fn.argtypes = _args
+    _fn.restype = _i
+lib.b200_grasp_nms_workspace.argtypes = [_i]
+lib.b200_grasp_nms_workspace.restype = _sz
+lib.b200_error_string.argtypes = [_i]
+lib.b200_error_string.restype = ctypes.c_char_p
+lib.b200_version.restype = _i
+lib.b200_fps_set_cluster.argtypes = [_i]
+lib.b200_fps_set_cluster.restype = None
+
+EXPORTS = sorted(list(SIGNATURES) + ["b200_grasp_nms_workspace", "b200_error_string", "b200_version"])
+
+
+def check(code, what):
+    """Non-zero status -> RuntimeError (the reference exit(-1)s instead, cuda_utils.h:35-44)."""
+    if code != 0:
+        raise RuntimeError("%s failed: %s (code %d)" % (what, lib.b200_error_string(code).decode(), code))

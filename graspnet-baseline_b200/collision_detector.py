@@ -1,0 +1,64 @@
+"""Drop-in for the reference's utils/collision_detector.py (ModelFreeCollisionDetector).
+
+Same constructor and detect() signature / return conventions
+(collision_detector.py:28-35, 37-129); numpy in, numpy out, CUDA inside.
+The M x N point-in-gripper tests run in libb200grasp.so (fp64, integer counts);
+the per-grasp thresholds and the count -> IoU -> mask arithmetic are M-length
+numpy expressions with the reference's own dtype rules, so results are
+bit-identical to the reference (tests/golden/collision_*.npz).
+"""
+import numpy as np
+import torch
+
+from . import ops as _ext
+from .voxel import voxel_down_sample
+
+
+class ModelFreeCollisionDetector():
+    def __init__(self, scene_points, voxel_size=0.005, device=None):
+        self.finger_width = 0.01
+        self.finger_length = 0.06
+        self.voxel_size = voxel_size
+        self.device = torch.device(device if device is not None else "cuda")
+        # open3d voxel_down_sample in the reference (:32-35)
+        self.scene_points = voxel_down_sample(np.asarray(scene_points), voxel_size)
+        self._scene_dev = torch.from_numpy(np.ascontiguousarray(self.scene_points, dtype=np.float64)).to(self.device)
+
+    def _thresholds(self, grasp_group, approach_dist):
+        h = grasp_group.heights
+        d = grasp_group.depths
+        w = grasp_group.widths
+        fl, fw = self.finger_length, self.finger_width
+        cols = [-h / 2, h / 2, d - fl, d, -(w / 2 + fw), -w / 2, (w / 2 + fw), w / 2,
+                d - fl - fw, d - fl - fw - approach_dist]
+        return np.stack([np.asarray(c, dtype=np.float64) for c in cols], axis=1)
+
+    def detect(self, grasp_group, approach_dist=0.03, collision_thresh=0.05, return_empty_grasp=False,
+               empty_thresh=0.01, return_ious=False):
+        approach_dist = max(approach_dist, self.finger_width)
+        T = np.ascontiguousarray(grasp_group.translations, dtype=np.float64)
+        R = np.ascontiguousarray(grasp_group.rotation_matrices, dtype=np.float64).reshape(-1, 9)
+        thr = np.ascontiguousarray(self._thresholds(grasp_group, approach_dist))
+        dev = self.device
+        counts = _ext.collision_counts(self._scene_dev, torch.from_numpy(T).to(dev), torch.from_numpy(R).to(dev),
+                                       torch.from_numpy(thr).to(dev)).cpu().numpy().astype(np.int64)
+        heights = grasp_group.heights[:, np.newaxis]
+        widths = grasp_group.widths[:, np.newaxis]
+        vox3 = self.voxel_size ** 3
+        left_right_volume = (heights * self.finger_length * self.finger_width / vox3).reshape(-1)
+        bottom_volume = (heights * (widths + 2 * self.finger_width) * self.finger_width / vox3).reshape(-1)
+        shifting_volume = (heights * (widths + 2 * self.finger_width) * approach_dist / vox3).reshape(-1)
+        volume = left_right_volume * 2 + bottom_volume + shifting_volume
+        global_iou = counts[:, 0] / (volume + 1e-6)
+        collision_mask = (global_iou > collision_thresh)
+        if not (return_empty_grasp or return_ious):
+            return collision_mask
+        ret_value = [collision_mask, ]
+        if return_empty_grasp:
+            inner_volume = (heights * self.finger_length * widths / vox3).reshape(-1)
+            ret_value.append(counts[:, 5] / inner_volume < empty_thresh)
+        if return_ious:
+            ret_value.append([global_iou, counts[:, 1] / (left_right_volume + 1e-6),
+                              counts[:, 2] / (left_right_volume + 1e-6), counts[:, 3] / (bottom_volume + 1e-6),
+                              counts[:, 4] / (shifting_volume + 1e-6)])
+        return ret_value

@@ -1,0 +1,93 @@
+// collision.cu -- model-free gripper/scene collision counting for sm_100a.
+//
+// Integer core of ModelFreeCollisionDetector.detect (reference
+// utils/collision_detector.py:69-100,119), which on the CPU materialises an
+// (M,N,3) fp64 tensor, a batched matmul and ~20 (M,N) boolean temporaries.
+//
+// Mapping: grid over (grasp-tiles x point-tiles).  A thread owns ONE grasp: its
+// translation, rotation and ten half-space bounds stay in fp64 registers; the
+// CTA's slice of the scene is staged through shared memory and read back as
+// warp-wide broadcasts; the eight masks of the reference are evaluated in fp64
+// and accumulated into six per-thread integer counters, added to counts[M,6]
+// with one integer atomic per counter per CTA slice.  Integer counts make the
+// result independent of summation order, so masks/IoUs derived from them on the
+// host are bit-identical to the reference's.
+//
+// Rounding: numpy evaluates (p - T) . R for an (N,3)x(3,3) fp64 product with the
+// BLAS micro-kernel's FMA chain  t_c = fma(z, R[2][c], fma(y, R[1][c], x * R[0][c]))
+// (pinned against the reference itself in tests/golden/collision_*.npz).
+#include "common.cuh"
+
+namespace {
+
+constexpr int CTH = 128;    // grasps per CTA (one per thread)
+constexpr int CPT = 1024;   // scene points per CTA slice (24 KB of fp64 xyz)
+
+__global__ void __launch_bounds__(CTH)
+collision_kernel(const double *__restrict__ scene, int n, const double *__restrict__ T,
+                 const double *__restrict__ R, const double *__restrict__ thr, int m,
+                 int32_t *__restrict__ counts) {
+  __shared__ double pts[CPT * 3];
+  const int g = blockIdx.x * CTH + threadIdx.x;
+  const int p0 = blockIdx.y * CPT;
+  const int pn = min(CPT, n - p0);
+  for (int i = threadIdx.x; i < pn * 3; i += CTH) pts[i] = __ldg(scene + (size_t)p0 * 3 + i);
+  __syncthreads();
+  if (g >= m) return;
+  const double *t = T + (size_t)g * 3, *r = R + (size_t)g * 9, *h = thr + (size_t)g * 10;
+  const double t0 = t[0], t1 = t[1], t2 = t[2];
+  const double r0 = r[0], r1 = r[1], r2 = r[2], r3 = r[3], r4 = r[4], r5 = r[5], r6 = r[6],
+               r7 = r[7], r8 = r[8];
+  const double h0 = h[0], h1 = h[1], h2 = h[2], h3 = h[3], h4 = h[4], h5 = h[5], h6 = h[6],
+               h7 = h[7], h8 = h[8], h9 = h[9];
+  int cg_ = 0, cl = 0, cr = 0, cb = 0, cs = 0, ci = 0;
+#pragma unroll 2
+  for (int k = 0; k < pn; ++k) {
+    const double x = __dsub_rn(pts[3 * k], t0), y = __dsub_rn(pts[3 * k + 1], t1),
+                 z = __dsub_rn(pts[3 * k + 2], t2);
+    const double tz = __fma_rn(z, r8, __fma_rn(y, r5, __dmul_rn(x, r2)));
+    const bool m1 = (tz > h0) & (tz < h1);
+    if (!__any_sync(__activemask(), m1)) continue;     // every mask below needs the height slab
+    const double tx = __fma_rn(z, r6, __fma_rn(y, r3, __dmul_rn(x, r0)));
+    const double ty = __fma_rn(z, r7, __fma_rn(y, r4, __dmul_rn(x, r1)));
+    const bool m2 = (tx > h2) & (tx < h3);
+    const bool m3 = ty > h4;
+    const bool m4 = ty < h5;
+    const bool m5 = ty < h6;
+    const bool m6 = ty > h7;
+    const bool m7 = (tx <= h2) & (tx > h8);
+    const bool m8 = (tx <= h8) & (tx > h9);
+    const bool left = m1 & m2 & m3 & m4;
+    const bool right = m1 & m2 & m5 & m6;
+    const bool bottom = m1 & m3 & m5 & m7;
+    const bool shifting = m1 & m3 & m5 & m8;
+    cg_ += (left | right | bottom | shifting);
+    cl += left; cr += right; cb += bottom; cs += shifting;
+    ci += (m1 & m2 & (!m4) & (!m6));
+  }
+  int32_t *o = counts + (size_t)g * 6;
+  if (cg_) atomicAdd(o + 0, cg_);
+  if (cl) atomicAdd(o + 1, cl);
+  if (cr) atomicAdd(o + 2, cr);
+  if (cb) atomicAdd(o + 3, cb);
+  if (cs) atomicAdd(o + 4, cs);
+  if (ci) atomicAdd(o + 5, ci);
+}
+
+}  // namespace
+
+extern "C" int b200_collision_counts(const double *scene, int n, const double *T, const double *R,
+                                     const double *thr, int m, int32_t *counts, void *stream) {
+  if (n < 0 || m < 0) return B200_EINVAL;
+  if (m == 0) return 0;
+  if (!counts) return B200_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA(cudaMemsetAsync(counts, 0, sizeof(int32_t) * 6 * (size_t)m, st));
+  if (n == 0) return 0;
+  if (!scene || !T || !R || !thr) return B200_EINVAL;
+  if (ceil_div(n, CPT) > 65535) return B200_ECAPACITY;
+  dim3 grid((unsigned)ceil_div(m, CTH), (unsigned)ceil_div(n, CPT));
+  collision_kernel<<<grid, CTH, 0, st>>>(scene, n, T, R, thr, m, counts);
+  B200_LAUNCH_CHECK();
+  return 0;
+}

@@ -1,0 +1,189 @@
+// nms.cu -- pairwise translation/rotation grasp NMS as a bitmask kernel (sm_100a).
+//
+// Replaces GraspGroup.nms -> grasp_nms.nms_grasp (graspnetAPI / grasp_nms, third
+// party, not in the reference tree; call sites demo_pointcloud.py:249,
+// grasp_service.py:276).  Semantics = oracle/geom_oracle.c:oracle_grasp_nms:
+// stable descending score order; a kept grasp i suppresses every later j with
+//   sqrt(|t_i - t_j|^2) < translation_thresh  and  (trace(R_i R_j^T) - 1)/2 > cos(rot_thresh)
+// evaluated in fp64 with a fixed association, so the keep set is bit-exact.
+//
+// Three launches, no host round trip:
+//   1. rank kernel   : rank[i] = #{j : s_j > s_i or (s_j == s_i and j < i)}  -> order[]
+//   2. mask kernel   : 64x64 tiles of the upper triangle; thread = row, 64-bit word
+//                      of "row suppresses column" bits (the torchvision-NMS layout)
+//   3. sweep kernel  : one CTA; per 64-row block the diagonal word chain is resolved
+//                      serially from shared memory by one thread, then all threads OR
+//                      the kept rows into the remaining removed-words in parallel;
+//                      finally a popc prefix compacts the survivors.
+#include "common.cuh"
+
+namespace {
+
+constexpr int G = 17;       // floats per grasp row (models/graspnet.py:131-133)
+constexpr int RT = 256;
+
+__global__ void __launch_bounds__(RT)
+nms_rank_kernel(const float *__restrict__ grasps, int m, int32_t *__restrict__ order) {
+  __shared__ float sc[RT];
+  const int i = blockIdx.x * RT + threadIdx.x;
+  const float si = i < m ? __ldg(grasps + (size_t)i * G) : 0.f;
+  int rank = 0;
+  for (int j0 = 0; j0 < m; j0 += RT) {
+    const int j = j0 + threadIdx.x;
+    __syncthreads();
+    sc[threadIdx.x] = j < m ? __ldg(grasps + (size_t)j * G) : 0.f;
+    __syncthreads();
+    const int jn = min(RT, m - j0);
+    for (int t = 0; t < jn; ++t) {
+      const float sj = sc[t];
+      rank += (sj > si) | ((sj == si) & (j0 + t < i));
+    }
+  }
+  if (i < m) order[rank] = i;
+}
+
+__global__ void __launch_bounds__(64)
+nms_mask_kernel(const float *__restrict__ grasps, const int32_t *__restrict__ order, int m, int W,
+                double tthr, double cthr, unsigned long long *__restrict__ mask) {
+  const int rb = blockIdx.y, cb = blockIdx.x;
+  if (cb < rb) return;                       // lower triangle never read by the sweep
+  __shared__ double ct[64][3];
+  __shared__ double cr[64][9];
+  const int t = threadIdx.x;
+  const int c = cb * 64 + t;
+  if (c < m) {
+    const float *g = grasps + (size_t)__ldg(order + c) * G;
+#pragma unroll
+    for (int e = 0; e < 3; ++e) ct[t][e] = (double)__ldg(g + 13 + e);
+#pragma unroll
+    for (int e = 0; e < 9; ++e) cr[t][e] = (double)__ldg(g + 4 + e);
+  }
+  __syncthreads();
+  const int a = rb * 64 + t;
+  if (a >= m) return;
+  const float *g = grasps + (size_t)__ldg(order + a) * G;
+  double at[3], ar[9];
+#pragma unroll
+  for (int e = 0; e < 3; ++e) at[e] = (double)__ldg(g + 13 + e);
+#pragma unroll
+  for (int e = 0; e < 9; ++e) ar[e] = (double)__ldg(g + 4 + e);
+  unsigned long long bits = 0ull;
+  const int cn = min(64, m - cb * 64);
+  for (int k = 0; k < cn; ++k) {
+    if (cb * 64 + k <= a) continue;          // only later (lower-score) grasps
+    const double dx = __dsub_rn(at[0], ct[k][0]), dy = __dsub_rn(at[1], ct[k][1]),
+                 dz = __dsub_rn(at[2], ct[k][2]);
+    const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+    if (!(__dsqrt_rn(d2) < tthr)) continue;
+    double tr = 0.0;
+#pragma unroll
+    for (int e = 0; e < 9; ++e) tr = __dadd_rn(tr, __dmul_rn(ar[e], cr[k][e]));
+    const double ca = __ddiv_rn(__dsub_rn(tr, 1.0), 2.0);
+    if (ca > cthr) bits |= 1ull << k;
+  }
+  mask[(size_t)a * W + cb] = bits;
+}
+
+constexpr int ST = 256;
+
+__global__ void __launch_bounds__(ST)
+nms_sweep_kernel(const unsigned long long *__restrict__ mask, const int32_t *__restrict__ order, int m,
+                 int W, unsigned long long *__restrict__ removed /* W words, global scratch */,
+                 int32_t *__restrict__ keep, int32_t *__restrict__ nkeep) {
+  __shared__ unsigned long long diag[64];
+  __shared__ unsigned long long s_keep;
+  __shared__ int s_prefix[ST];
+  const int tid = threadIdx.x;
+  for (int w = tid; w < W; w += ST) removed[w] = 0ull;
+  __syncthreads();
+  for (int wb = 0; wb < W; ++wb) {
+    if (tid < 64) {
+      const int a = wb * 64 + tid;
+      diag[tid] = a < m ? mask[(size_t)a * W + wb] : 0ull;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      unsigned long long rem = removed[wb], kb = 0ull;
+      const int rn = min(64, m - wb * 64);
+      for (int bit = 0; bit < rn; ++bit) {
+        if (!((rem >> bit) & 1ull)) { kb |= 1ull << bit; rem |= diag[bit]; }
+      }
+      s_keep = kb;
+      removed[wb] = ~kb;                     // final: bit set = not kept (padding bits too)
+    }
+    __syncthreads();
+    const unsigned long long kb = s_keep;
+    for (int w = wb + 1 + tid; w < W; w += ST) {
+      unsigned long long acc = 0ull, bitsleft = kb;
+      while (bitsleft) {
+        const int bit = __ffsll((long long)bitsleft) - 1;
+        bitsleft &= bitsleft - 1;
+        acc |= mask[(size_t)(wb * 64 + bit) * W + w];
+      }
+      removed[w] |= acc;
+    }
+    __syncthreads();
+  }
+  // compaction: survivors in sorted order
+  // each thread owns a contiguous range of words
+  const int per = (W + ST - 1) / ST;
+  const int w0 = min(W, tid * per), w1 = min(W, w0 + per);
+  int cnt = 0;
+  for (int w = w0; w < w1; ++w) cnt += __popcll(~removed[w]);
+  s_prefix[tid] = cnt;
+  __syncthreads();
+  if (tid == 0) {
+    int run = 0;
+    for (int t = 0; t < ST; ++t) { const int c = s_prefix[t]; s_prefix[t] = run; run += c; }
+    *nkeep = run;
+  }
+  __syncthreads();
+  int pos = s_prefix[tid];
+  for (int w = w0; w < w1; ++w) {
+    unsigned long long kb = ~removed[w];
+    while (kb) {
+      const int bit = __ffsll((long long)kb) - 1;
+      kb &= kb - 1;
+      keep[pos++] = __ldg(order + w * 64 + bit);
+    }
+  }
+}
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+}  // namespace
+
+extern "C" size_t b200_grasp_nms_workspace(int m) {
+  if (m <= 0) return 256;
+  const size_t W = (size_t)(m + 63) / 64;
+  return align_up(sizeof(int32_t) * (size_t)m, 256) + align_up(8 * W, 256) + align_up(8 * W * (size_t)m, 256);
+}
+
+extern "C" int b200_grasp_nms(const float *grasps, int m, double translation_thresh,
+                              double cos_rotation_thresh, int32_t *keep, int32_t *nkeep,
+                              void *workspace, size_t workspace_bytes, void *stream) {
+  if (m < 0 || !nkeep) return B200_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (m == 0) {
+    B200_CUDA(cudaMemsetAsync(nkeep, 0, sizeof(int32_t), st));
+    return 0;
+  }
+  if (!grasps || !keep || !workspace) return B200_EINVAL;
+  if (m > 32768) return B200_ECAPACITY;
+  if (workspace_bytes < b200_grasp_nms_workspace(m)) return B200_EWORKSPACE;
+  const int W = (m + 63) / 64;
+  char *ws = (char *)workspace;
+  int32_t *order = (int32_t *)ws;
+  ws += align_up(sizeof(int32_t) * (size_t)m, 256);
+  unsigned long long *removed = (unsigned long long *)ws;
+  ws += align_up(8 * (size_t)W, 256);
+  unsigned long long *mask = (unsigned long long *)ws;
+  nms_rank_kernel<<<ceil_div(m, RT), RT, 0, st>>>(grasps, m, order);
+  B200_LAUNCH_CHECK();
+  nms_mask_kernel<<<dim3((unsigned)W, (unsigned)W), 64, 0, st>>>(grasps, order, m, W, translation_thresh,
+                                                                cos_rotation_thresh, mask);
+  B200_LAUNCH_CHECK();
+  nms_sweep_kernel<<<1, ST, 0, st>>>(mask, order, m, W, removed, keep, nkeep);
+  B200_LAUNCH_CHECK();
+  return 0;
+}

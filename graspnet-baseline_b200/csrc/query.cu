@@ -1,0 +1,177 @@
+// query.cu -- ball query and (multi-depth) cylinder query for sm_100a.
+//
+// Replaces query_ball_point_kernel (reference pointnet2/_ext_src/src/ball_query_gpu.cu:14-49)
+// and query_cylinder_point_kernel (cylinder_query_gpu.cu:9-57).
+//
+// The legacy kernels run ONE block per batch element with a thread per centre
+// doing a private serial scan of all n points (stride-3 scalar loads).  Here:
+// grid over (batch x centre-tiles); one WARP per centre; the point stream is
+// staged through shared memory in tiles shared by the CTA's 8 centres (raw
+// xyz floats, read back at stride 3 = conflict free); lanes test 32 consecutive
+// points at once and __ballot_sync + popc of the lower lanes gives every hit its
+// slot in index order -- the same "first nsample hits in index order, remaining
+// slots = first hit, no hit = zeros" result (ball_query_gpu.cu:38-46 and the
+// torch::zeros of ball_query.cpp:24-26).  A warp stops scanning once its lists
+// are full; the CTA stops loading tiles once all its warps have.
+#include "common.cuh"
+
+namespace {
+
+constexpr int QT = 256;          // threads per CTA
+constexpr int QW = QT / 32;      // centres per CTA
+constexpr int TP = 1024;         // points per shared-memory tile (12 KB)
+constexpr int MAXH = 8;
+
+struct HList { float v[MAXH]; };
+
+struct BallPred {
+  float cx, cy, cz, r2;
+  __device__ __forceinline__ void init(const float *c, const float *, float radius, float) {
+    cx = c[0]; cy = c[1]; cz = c[2];
+    r2 = __fmul_rn(radius, radius);
+  }
+  // returns whether the point passes every test that does not depend on the list;
+  // `h` receives the value compared against each list's upper bound.
+  __device__ __forceinline__ bool test(float x, float y, float z, float &h) const {
+    h = 0.f;
+    return sq3_p2(__fsub_rn(cx, x), __fsub_rn(cy, y), __fsub_rn(cz, z)) < r2;
+  }
+};
+
+struct CylPred {
+  float cx, cy, cz, r2, hmin;
+  float r0, r1, r2_, r3, r4, r5, r6, r7, r8;
+  __device__ __forceinline__ void init(const float *c, const float *rot, float radius, float hmin_) {
+    cx = c[0]; cy = c[1]; cz = c[2];
+    r2 = __fmul_rn(radius, radius);
+    hmin = hmin_;
+    r0 = rot[0]; r1 = rot[1]; r2_ = rot[2]; r3 = rot[3]; r4 = rot[4];
+    r5 = rot[5]; r6 = rot[6]; r7 = rot[7]; r8 = rot[8];
+  }
+  __device__ __forceinline__ bool test(float px, float py, float pz, float &h) const {
+    const float x = __fsub_rn(px, cx), y = __fsub_rn(py, cy), z = __fsub_rn(pz, cz);
+    const float xr = __fmaf_rn(r6, z, __fmaf_rn(r0, x, __fmul_rn(r3, y)));
+    const float yr = __fmaf_rn(r7, z, __fmaf_rn(r1, x, __fmul_rn(r4, y)));
+    const float zr = __fmaf_rn(r8, z, __fmaf_rn(r2_, x, __fmul_rn(r5, y)));
+    const float d2 = __fmaf_rn(yr, yr, __fmul_rn(zr, zr));
+    h = xr;
+    return d2 < r2 && xr > hmin;
+  }
+};
+
+// NH = number of output lists (1 for ball query / single cylinder query).
+// BALL: lists have no upper bound test.
+template <class Pred, int NH, bool BALL>
+__global__ void __launch_bounds__(QT)
+query_kernel(const float *__restrict__ new_xyz, const float *__restrict__ xyz,
+             const float *__restrict__ rot, int b, int n, int m, float radius, float hmin,
+             HList hmax, int nsample, int32_t *__restrict__ idx) {
+  __shared__ float tile[TP * 3];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tiles_per_batch = (m + QW - 1) / QW;
+  const int bi = blockIdx.x / tiles_per_batch;
+  const int j = (blockIdx.x % tiles_per_batch) * QW + warp;
+  const bool active = j < m;
+  const float *pts = xyz + (size_t)bi * n * 3;
+
+  Pred pred;
+  if (active) {
+    pred.init(new_xyz + ((size_t)bi * m + j) * 3, BALL ? nullptr : rot + ((size_t)bi * m + j) * 9,
+              radius, hmin);
+  }
+  int cnt[NH], first[NH];
+#pragma unroll
+  for (int h = 0; h < NH; ++h) { cnt[h] = 0; first[h] = 0; }
+  const size_t list_stride = (size_t)b * m * nsample;
+  int32_t *out = idx + ((size_t)bi * m + (active ? j : 0)) * nsample;
+  bool done = !active;
+
+  for (int t0 = 0; t0 < n; t0 += TP) {
+    const int tn = min(TP, n - t0);
+    const float *src = pts + (size_t)t0 * 3;
+    for (int i = tid; i < tn * 3; i += QT) tile[i] = __ldg(src + i);
+    __syncthreads();
+    if (!done) {
+      for (int i0 = 0; i0 < tn; i0 += 32) {
+        const int k = i0 + lane;
+        bool ok = false;
+        float hv = 0.f;
+        if (k < tn) ok = pred.test(tile[3 * k], tile[3 * k + 1], tile[3 * k + 2], hv);
+        bool all_full = true;
+#pragma unroll
+        for (int h = 0; h < NH; ++h) {
+          if (cnt[h] < nsample) {                       // warp-uniform
+            const bool hit = BALL ? ok : (ok && hv < hmax.v[h]);
+            const unsigned bal = __ballot_sync(0xffffffffu, hit);
+            if (bal) {
+              if (cnt[h] == 0) first[h] = t0 + i0 + __ffs(bal) - 1;
+              const int pos = cnt[h] + __popc(bal & lanemask_lt());
+              if (hit && pos < nsample) out[h * list_stride + pos] = t0 + k;
+              cnt[h] += __popc(bal);
+            }
+            if (cnt[h] < nsample) all_full = false;
+          }
+        }
+        if (all_full) { done = true; break; }
+      }
+    }
+    if (__syncthreads_and(done)) break;
+  }
+  if (active) {
+#pragma unroll
+    for (int h = 0; h < NH; ++h) {
+      const int fill = cnt[h] > 0 ? first[h] : 0;
+      for (int s = min(cnt[h], nsample) + lane; s < nsample; s += 32) out[h * list_stride + s] = fill;
+    }
+  }
+}
+
+template <class Pred, int NH, bool BALL>
+int launch_query(const float *new_xyz, const float *xyz, const float *rot, int b, int n, int m,
+                 float radius, float hmin, const HList &hmax, int nsample, int32_t *idx,
+                 cudaStream_t st) {
+  const long long grid = (long long)b * ceil_div(m, QW);
+  if (grid > 0x7fffffffLL) return B200_ECAPACITY;
+  query_kernel<Pred, NH, BALL><<<(unsigned)grid, QT, 0, st>>>(new_xyz, xyz, rot, b, n, m, radius,
+                                                              hmin, hmax, nsample, idx);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int b200_ball_query(const float *new_xyz, const float *xyz, int b, int n, int m,
+                               float radius, int nsample, int32_t *idx, void *stream) {
+  if (b < 0 || n < 0 || m < 0 || nsample < 0) return B200_EINVAL;
+  if (b == 0 || m == 0 || nsample == 0) return 0;
+  if (!new_xyz || !idx || (n > 0 && !xyz)) return B200_EINVAL;
+  HList h = {};
+  return launch_query<BallPred, 1, true>(new_xyz, xyz, nullptr, b, n, m, radius, 0.f, h, nsample,
+                                         idx, (cudaStream_t)stream);
+}
+
+extern "C" int b200_cylinder_query_multi(const float *new_xyz, const float *xyz, const float *rot,
+                                         int b, int n, int m, float radius, float hmin,
+                                         const float *hmax, int nh, int nsample, int32_t *idx,
+                                         void *stream) {
+  if (b < 0 || n < 0 || m < 0 || nsample < 0 || nh < 0) return B200_EINVAL;
+  if (nh > MAXH) return B200_ECAPACITY;
+  if (b == 0 || m == 0 || nsample == 0 || nh == 0) return 0;
+  if (!new_xyz || !rot || !idx || !hmax || (n > 0 && !xyz)) return B200_EINVAL;
+  HList h = {};
+  for (int i = 0; i < nh; ++i) h.v[i] = hmax[i];
+  cudaStream_t st = (cudaStream_t)stream;
+#define CYL_CASE(N) case N: return launch_query<CylPred, N, false>(new_xyz, xyz, rot, b, n, m, radius, hmin, h, nsample, idx, st);
+  switch (nh) {
+    CYL_CASE(1) CYL_CASE(2) CYL_CASE(3) CYL_CASE(4) CYL_CASE(5) CYL_CASE(6) CYL_CASE(7) CYL_CASE(8)
+  }
+#undef CYL_CASE
+  return B200_EINVAL;
+}
+
+extern "C" int b200_cylinder_query(const float *new_xyz, const float *xyz, const float *rot, int b,
+                                   int n, int m, float radius, float hmin, float hmax, int nsample,
+                                   int32_t *idx, void *stream) {
+  return b200_cylinder_query_multi(new_xyz, xyz, rot, b, n, m, radius, hmin, &hmax, 1, nsample, idx,
+                                   stream);
+}

@@ -1,0 +1,222 @@
+"""Tensor-level entry points: checks + output allocation + current stream + C-ABI call.
+
+These mirror the ten pybind functions of the reference's `pointnet2._ext`
+(pointnet2/_ext_src/src/bindings.cpp:13-26) and `knn_pytorch.knn`
+(knn/src/vision.cpp:3-5) -- same names, argument order and error behaviour
+(non-contiguous / wrong dtype / non-CUDA input -> RuntimeError, as the
+reference's CHECK_* macros in include/utils.h:10-30 do) -- plus the two
+post-processing ops.  PyTorch is used for device memory and streams only.
+"""
+import ctypes
+
+import torch
+
+from . import _abi
+
+_lib = _abi.lib
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr())
+
+
+def _chk(t, name, dtype):
+    if not isinstance(t, torch.Tensor):
+        raise RuntimeError("%s must be a tensor" % name)
+    if not t.is_cuda:
+        raise RuntimeError("%s must be a CUDA tensor (b200grasp has no CPU path)" % name)
+    if not t.is_contiguous():
+        raise RuntimeError("%s must be a contiguous tensor" % name)
+    if t.dtype != dtype:
+        raise RuntimeError("%s must be a %s tensor" % (name, str(dtype).replace("torch.", "")))
+
+
+def furthest_point_sampling(points, nsamples):
+    """points (B,N,3) f32 -> (B,nsamples) i32   [sampling.cpp:70-91]"""
+    _chk(points, "points", torch.float32)
+    b, n, _ = points.shape
+    out = torch.empty((b, nsamples), dtype=torch.int32, device=points.device)
+    with torch.cuda.device(points.device):
+        _abi.check(_lib.b200_furthest_point_sampling(_ptr(points), b, n, nsamples, _ptr(out), _stream()),
+                   "furthest_point_sampling")
+    return out
+
+
+def gather_points(points, idx):
+    """points (B,C,N) f32, idx (B,M) i32 -> (B,C,M)   [sampling.cpp:20-43]"""
+    _chk(points, "points", torch.float32)
+    _chk(idx, "idx", torch.int32)
+    b, c, n = points.shape
+    m = idx.shape[1]
+    out = torch.empty((b, c, m), dtype=torch.float32, device=points.device)
+    with torch.cuda.device(points.device):
+        _abi.check(_lib.b200_gather_points(_ptr(points), _ptr(idx), b, c, n, m, _ptr(out), _stream()),
+                   "gather_points")
+    return out
+
+
+def gather_points_grad(grad_out, idx, n):
+    """grad_out (B,C,M) f32, idx (B,M) i32 -> (B,C,n)   [sampling.cpp:45-69]"""
+    _chk(grad_out, "grad_out", torch.float32)
+    _chk(idx, "idx", torch.int32)
+    b, c, m = grad_out.shape
+    out = torch.empty((b, c, n), dtype=torch.float32, device=grad_out.device)
+    with torch.cuda.device(grad_out.device):
+        _abi.check(_lib.b200_gather_points_grad(_ptr(grad_out), _ptr(idx), b, c, n, m, _ptr(out), _stream()),
+                   "gather_points_grad")
+    return out
+
+
+def ball_query(new_xyz, xyz, radius, nsample):
+    """new_xyz (B,M,3), xyz (B,N,3) -> (B,M,nsample) i32   [ball_query.cpp:13-37]"""
+    _chk(new_xyz, "new_xyz", torch.float32)
+    _chk(xyz, "xyz", torch.float32)
+    b, m, _ = new_xyz.shape
+    n = xyz.shape[1]
+    out = torch.empty((b, m, nsample), dtype=torch.int32, device=xyz.device)
+    with torch.cuda.device(xyz.device):
+        _abi.check(_lib.b200_ball_query(_ptr(new_xyz), _ptr(xyz), b, n, m, float(radius), int(nsample),
+                                        _ptr(out), _stream()), "ball_query")
+    return out
+
+
+def cylinder_query(new_xyz, xyz, rot, radius, hmin, hmax, nsample):
+    """new_xyz (B,M,3), xyz (B,N,3), rot (B,M,9) -> (B,M,nsample) i32   [cylinder_query.cpp:10-37]"""
+    _chk(new_xyz, "new_xyz", torch.float32)
+    _chk(xyz, "xyz", torch.float32)
+    _chk(rot, "rot", torch.float32)
+    b, m, _ = new_xyz.shape
+    n = xyz.shape[1]
+    out = torch.empty((b, m, nsample), dtype=torch.int32, device=xyz.device)
+    with torch.cuda.device(xyz.device):
+        _abi.check(_lib.b200_cylinder_query(_ptr(new_xyz), _ptr(xyz), _ptr(rot), b, n, m, float(radius),
+                                            float(hmin), float(hmax), int(nsample), _ptr(out), _stream()),
+                   "cylinder_query")
+    return out
+
+
+def cylinder_query_multi(new_xyz, xyz, rot, radius, hmin, hmax_list, nsample):
+    """One scan for all hmax of CloudCrop (models/modules.py:127-130) -> (H,B,M,nsample) i32."""
+    _chk(new_xyz, "new_xyz", torch.float32)
+    _chk(xyz, "xyz", torch.float32)
+    _chk(rot, "rot", torch.float32)
+    b, m, _ = new_xyz.shape
+    n = xyz.shape[1]
+    nh = len(hmax_list)
+    hm = (ctypes.c_float * max(nh, 1))(*[float(h) for h in hmax_list])
+    out = torch.empty((nh, b, m, nsample), dtype=torch.int32, device=xyz.device)
+    with torch.cuda.device(xyz.device):
+        _abi.check(_lib.b200_cylinder_query_multi(_ptr(new_xyz), _ptr(xyz), _ptr(rot), b, n, m, float(radius),
+                                                  float(hmin), hm, nh, int(nsample), _ptr(out), _stream()),
+                   "cylinder_query_multi")
+    return out
+
+
+def group_points(points, idx):
+    """points (B,C,N) f32, idx (B,M,ns) i32 -> (B,C,M,ns)   [group_points.cpp:17-40]"""
+    _chk(points, "points", torch.float32)
+    _chk(idx, "idx", torch.int32)
+    b, c, n = points.shape
+    _, m, ns = idx.shape
+    out = torch.empty((b, c, m, ns), dtype=torch.float32, device=points.device)
+    with torch.cuda.device(points.device):
+        _abi.check(_lib.b200_group_points(_ptr(points), _ptr(idx), b, c, n, m, ns, _ptr(out), _stream()),
+                   "group_points")
+    return out
+
+
+def group_points_grad(grad_out, idx, n):
+    """grad_out (B,C,M,ns) f32, idx (B,M,ns) i32 -> (B,C,n)   [group_points.cpp:42-65]"""
+    _chk(grad_out, "grad_out", torch.float32)
+    _chk(idx, "idx", torch.int32)
+    b, c, m, ns = grad_out.shape
+    out = torch.empty((b, c, n), dtype=torch.float32, device=grad_out.device)
+    with torch.cuda.device(grad_out.device):
+        _abi.check(_lib.b200_group_points_grad(_ptr(grad_out), _ptr(idx), b, c, n, m, ns, _ptr(out), _stream()),
+                   "group_points_grad")
+    return out
+
+
+def three_nn(unknowns, knows):
+    """unknowns (B,n,3), knows (B,m,3) -> (dist2 (B,n,3) f32, idx (B,n,3) i32)   [interpolate.cpp:19-45]"""
+    _chk(unknowns, "unknowns", torch.float32)
+    _chk(knows, "knows", torch.float32)
+    b, n, _ = unknowns.shape
+    m = knows.shape[1]
+    dist2 = torch.empty((b, n, 3), dtype=torch.float32, device=unknowns.device)
+    idx = torch.empty((b, n, 3), dtype=torch.int32, device=unknowns.device)
+    with torch.cuda.device(unknowns.device):
+        _abi.check(_lib.b200_three_nn(_ptr(unknowns), _ptr(knows), b, n, m, _ptr(dist2), _ptr(idx), _stream()),
+                   "three_nn")
+    return dist2, idx
+
+
+def three_interpolate(points, idx, weight):
+    """points (B,c,m), idx (B,n,3) i32, weight (B,n,3) -> (B,c,n)   [interpolate.cpp:47-75]"""
+    _chk(points, "points", torch.float32)
+    _chk(idx, "idx", torch.int32)
+    _chk(weight, "weight", torch.float32)
+    b, c, m = points.shape
+    n = idx.shape[1]
+    out = torch.empty((b, c, n), dtype=torch.float32, device=points.device)
+    with torch.cuda.device(points.device):
+        _abi.check(_lib.b200_three_interpolate(_ptr(points), _ptr(idx), _ptr(weight), b, c, m, n, _ptr(out),
+                                               _stream()), "three_interpolate")
+    return out
+
+
+def three_interpolate_grad(grad_out, idx, weight, m):
+    """grad_out (B,c,n), idx, weight (B,n,3) -> (B,c,m)   [interpolate.cpp:76-104]"""
+    _chk(grad_out, "grad_out", torch.float32)
+    _chk(idx, "idx", torch.int32)
+    _chk(weight, "weight", torch.float32)
+    b, c, n = grad_out.shape
+    out = torch.empty((b, c, m), dtype=torch.float32, device=grad_out.device)
+    with torch.cuda.device(grad_out.device):
+        _abi.check(_lib.b200_three_interpolate_grad(_ptr(grad_out), _ptr(idx), _ptr(weight), b, c, n, m,
+                                                    _ptr(out), _stream()), "three_interpolate_grad")
+    return out
+
+
+def knn(ref, query, idx):
+    """ref (B,D,Nr), query (B,D,Nq), idx (B,k,Nq) i64 OUT, caller-allocated -> 1   [knn.h:12-65]"""
+    _chk(ref, "ref", torch.float32)
+    _chk(query, "query", torch.float32)
+    _chk(idx, "idx", torch.int64)
+    b, d, nr = ref.shape
+    nq = query.shape[2]
+    k = idx.shape[1]
+    with torch.cuda.device(ref.device):
+        _abi.check(_lib.b200_knn(_ptr(ref), _ptr(query), b, d, nr, nq, k, _ptr(idx), _stream()), "knn")
+    return 1
+
+
+def collision_counts(scene, T, R, thr):
+    """scene (N,3) f64, T (M,3), R (M,9), thr (M,10) f64 -> counts (M,6) i32
+    [utils/collision_detector.py:75-100,119]"""
+    for t, nm in ((scene, "scene"), (T, "T"), (R, "R"), (thr, "thr")):
+        _chk(t, nm, torch.float64)
+    n, m = scene.shape[0], T.shape[0]
+    counts = torch.empty((m, 6), dtype=torch.int32, device=scene.device)
+    with torch.cuda.device(scene.device):
+        _abi.check(_lib.b200_collision_counts(_ptr(scene), n, _ptr(T), _ptr(R), _ptr(thr), m, _ptr(counts),
+                                              _stream()), "collision_counts")
+    return counts
+
+
+def grasp_nms(grasps, translation_thresh, cos_rotation_thresh):
+    """grasps (M,17) f32 -> (keep (M,) i32 row numbers in score order, nkeep (1,) i32), both on device."""
+    _chk(grasps, "grasps", torch.float32)
+    m = grasps.shape[0]
+    keep = torch.empty((max(m, 1),), dtype=torch.int32, device=grasps.device)
+    nkeep = torch.empty((1,), dtype=torch.int32, device=grasps.device)
+    nbytes = _lib.b200_grasp_nms_workspace(m)
+    ws = torch.empty((nbytes,), dtype=torch.uint8, device=grasps.device)
+    with torch.cuda.device(grasps.device):
+        _abi.check(_lib.b200_grasp_nms(_ptr(grasps), m, float(translation_thresh), float(cos_rotation_thresh),
+                                       _ptr(keep), _ptr(nkeep), _ptr(ws), nbytes, _stream()), "grasp_nms")
+    return keep, nkeep

@@ -1,0 +1,142 @@
+"""The geometry hot path of ONE GraspNet inference scene, as a sequence of C-ABI calls.
+
+Order and shapes follow the reference forward pass:
+  SA1..SA4  (models/backbone.py:30-64 via pointnet2_modules.py:210-272):
+            furthest_point_sample -> gather_operation -> ball_query -> grouping_operation(xyz[,features])
+  FP1, FP2  (pointnet2_modules.py:371-416): three_nn -> three_interpolate
+  CloudCrop (models/modules.py:127-130): cylinder_query x4 hmax -> grouping_operation(xyz)
+  post      (demo_pointcloud.py:220-250): ModelFreeCollisionDetector.detect counts -> GraspGroup.nms
+The SharedMLP / conv stacks between these ops are cuDNN work outside this path
+(SURVEY.md section 2.1 #6); the feature tensors they would produce are seeded
+random tensors of the right shape, created once, resident in HBM.
+"""
+import math
+
+import numpy as np
+import torch
+
+from . import ops, synth
+
+# (npoint, radius, nsample, C_in features grouped at this level)  -- models/backbone.py:30-64
+SA_CFG = [(2048, 0.04, 64, 0), (1024, 0.1, 32, 128), (512, 0.2, 16, 256), (256, 0.3, 16, 256)]
+CYL = dict(radius=0.05, hmin=-0.02, hmax_list=[0.01, 0.02, 0.03, 0.04], nsample=64)   # models/graspnet.py:39,44
+
+
+class GeometryScene:
+    """Device-resident inputs of `batch` scenes + run() = one pass of the hot path."""
+
+    def __init__(self, batch=1, num_point=20000, num_grasp=1024, seed=1234, device="cuda",
+                 fused_cylinder=True, sa_cfg=None, voxel_size=0.01):
+        self.B, self.N, self.M = batch, num_point, num_grasp
+        self.dev = torch.device(device)
+        self.fused_cylinder = fused_cylinder
+        self.sa_cfg = sa_cfg or SA_CFG
+        self.voxel_size = voxel_size
+        self.host = self.make_host_inputs(seed)
+        self.launches = 0
+        self.glue = 0
+        self.timer = None
+        g = torch.Generator(device="cpu").manual_seed(seed)
+        # stand-ins for MLP outputs (resident, never regenerated)
+        self.feat = {}
+        npts = [s[0] for s in self.sa_cfg]
+        for lvl, (_, _, _, cin) in enumerate(self.sa_cfg):
+            if cin:
+                self.feat["sa%d_in" % (lvl + 1)] = torch.randn(batch, cin, npts[lvl - 1], generator=g).to(self.dev)
+        self.feat["fp1_known"] = torch.randn(batch, 256, npts[3], generator=g).to(self.dev)
+        self.feat["fp2_known"] = torch.randn(batch, 256, npts[2], generator=g).to(self.dev)
+        self.upload()
+
+    # ---- inputs a caller would hand over from the host
+    def make_host_inputs(self, seed):
+        from .voxel import voxel_down_sample
+        h = {"cloud": np.stack([synth.tabletop_cloud(self.N, seed + s) for s in range(self.B)])}
+        nseed = self.sa_cfg[1][0]
+        h["rot"] = np.stack([synth.seed_rotations(nseed, seed + s) for s in range(self.B)])
+        h["grasps"] = [synth.synthetic_grasps(h["cloud"][s], self.M, seed + s) for s in range(self.B)]
+        h["scene64"] = [voxel_down_sample(h["cloud"][s].astype(np.float64), self.voxel_size) for s in range(self.B)]
+        return h
+
+    def upload(self):
+        h, d = self.host, self.dev
+        self.cloud = torch.from_numpy(h["cloud"]).to(d)
+        self.rot = torch.from_numpy(h["rot"]).to(d)
+        self.grasps = [torch.from_numpy(g).to(d) for g in h["grasps"]]
+        self.scene64 = [torch.from_numpy(s).to(d) for s in h["scene64"]]
+        self.coll_in = [self.collision_inputs(g) for g in h["grasps"]]
+
+    def collision_inputs(self, g, approach_dist=0.05):
+        """T, R, thr (fp64, device) for one scene's grasp rows -- the host half of detect()."""
+        from .collision_detector import ModelFreeCollisionDetector as D
+        from .grasp import GraspGroup
+        det = D.__new__(D)
+        det.finger_width, det.finger_length = 0.01, 0.06
+        gg = GraspGroup(g)
+        thr = det._thresholds(gg, max(approach_dist, 0.01))
+        f = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(self.dev)
+        return f(gg.translations), f(gg.rotation_matrices.reshape(-1, 9)), f(thr)
+
+    # ---- optional per-op CUDA-event timing (bench.py's roofline pass)
+    def _op(self, name, fn, *args):
+        if self.timer is None:
+            return fn(*args)
+        st = torch.cuda.current_stream()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        r = fn(*args)
+        e1.record(st)
+        self.timer.append((name, e0, e1))
+        return r
+
+    # ---- one pass
+    def run(self):
+        out = {}
+        L = 0
+        xyz = self.cloud
+        for lvl, (npoint, radius, nsample, cin) in enumerate(self.sa_cfg):
+            xyz_t = xyz.transpose(1, 2).contiguous(); self.glue += 1
+            inds = self._op('fps_sa%d' % (lvl + 1), ops.furthest_point_sampling, xyz, npoint)
+            new_xyz = self._op('gather_sa%d' % (lvl + 1), ops.gather_points, xyz_t, inds).transpose(1, 2).contiguous(); self.glue += 1
+            idx = self._op('ball_sa%d' % (lvl + 1), ops.ball_query, new_xyz, xyz, radius, nsample)
+            out["sa%d_grouped_xyz" % (lvl + 1)] = self._op('group_xyz_sa%d' % (lvl + 1), ops.group_points, xyz_t, idx)
+            L += 4
+            if cin:
+                out["sa%d_grouped_feat" % (lvl + 1)] = self._op('group_feat_sa%d' % (lvl + 1), ops.group_points, self.feat["sa%d_in" % (lvl + 1)], idx)
+                L += 1
+            out["sa%d_inds" % (lvl + 1)], out["sa%d_xyz" % (lvl + 1)], out["sa%d_idx" % (lvl + 1)] = inds, new_xyz, idx
+            xyz = new_xyz
+        for name, unknown, known in (("fp1", out["sa3_xyz"], out["sa4_xyz"]), ("fp2", out["sa2_xyz"], out["sa3_xyz"])):
+            d2, idx3 = self._op('three_nn_' + name, ops.three_nn, unknown, known)
+            w = torch.full_like(d2, 1.0 / 3.0)            # weights are caller arithmetic (pointnet2_modules.py:395-397)
+            self.glue += 1
+            out[name + "_idx"] = idx3
+            out[name + "_interp"] = self._op('three_interp_' + name, ops.three_interpolate, self.feat[name + "_known"], idx3, w)
+            L += 2
+        seed_xyz = out["sa2_xyz"]
+        rot9 = self.rot.view(self.B, -1, 9)
+        cloud_t = self.cloud.transpose(1, 2).contiguous(); self.glue += 1
+        if self.fused_cylinder:
+            cidx = self._op('cylinder_multi', ops.cylinder_query_multi, seed_xyz, self.cloud, rot9, CYL["radius"],
+                            CYL["hmin"], CYL["hmax_list"], CYL["nsample"])
+            L += 1
+        else:
+            cidx = torch.stack([self._op('cylinder_%g' % h, ops.cylinder_query, seed_xyz, self.cloud, rot9, CYL["radius"],
+                                         CYL["hmin"], h, CYL["nsample"]) for h in CYL["hmax_list"]])
+            L += len(CYL["hmax_list"]); self.glue += 1
+        out["crop_idx"] = cidx
+        nh = cidx.shape[0]
+        # (H,B,M,ns) -> per batch one (B, H*M, ns) index tensor = one grouping launch for all depths
+        cat = cidx.permute(1, 0, 2, 3).reshape(self.B, nh * cidx.shape[2], cidx.shape[3])
+        if self.B > 1:
+            cat = cat.contiguous(); self.glue += 1
+        out["crop_grouped_xyz"] = self._op('group_xyz_crop', ops.group_points, cloud_t, cat)
+        L += 1
+        counts, keeps = [], []
+        for s in range(self.B):
+            T, R, thr = self.coll_in[s]
+            counts.append(self._op('collision', ops.collision_counts, self.scene64[s], T, R, thr))
+            keeps.append(self._op('nms', ops.grasp_nms, self.grasps[s], 0.03, math.cos(30.0 / 180.0 * math.pi)))
+            L += 1 + 3
+        out["collision_counts"], out["nms"] = counts, keeps
+        self.launches = L
+        return out

@@ -1,0 +1,131 @@
+/*
+ * b200grasp.h -- C ABI of libb200grasp.so: the B200 (sm_100a) implementation of
+ * GraspNet-baseline's point-cloud geometry hot path.
+ *
+ * Conventions (all entry points):
+ *   - plain pointers and sizes only; every pointer is a DEVICE pointer unless
+ *     the comment says HOST; tensors are contiguous, row-major, fp32 / int32
+ *     unless stated;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default
+ *     stream); launches are asynchronous, nothing synchronises, nothing
+ *     allocates (scratch is caller-provided), nothing calls exit();
+ *   - return 0 on success, a positive cudaError_t value if a launch failed, or
+ *     a negative B200_E* code for bad arguments.  b200_error_string() renders
+ *     either.  (The reference prints and exit(-1)s on a launch failure,
+ *     pointnet2/_ext_src/include/cuda_utils.h:35-44; knn prints and carries on,
+ *     knn/src/knn.h:40-46.  Here the host wrapper raises RuntimeError.)
+ *   - outputs the reference zero-fills (torch::zeros) are fully written by the
+ *     callee, so the caller may pass uninitialised memory.
+ *
+ * Each entry point names the reference interface it replaces (paths relative
+ * to the reference repository root).
+ */
+#ifndef B200GRASP_H_
+#define B200GRASP_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_EINVAL (-1)      /* bad size / null pointer                       */
+#define B200_ECAPACITY (-2)   /* problem larger than this build supports       */
+#define B200_EWORKSPACE (-3)  /* workspace too small                           */
+
+int b200_version(void);
+const char *b200_error_string(int code);
+
+/* Replaces furthest_point_sampling(points[B,N,3], nsamples) -> [B,nsamples] i32
+ * (pointnet2/_ext_src/src/sampling.cpp:70-91, include/sampling.h:11; kernel
+ * sampling_gpu.cu:74-178).  First index 0; points with |p|^2 <= 1e-3 never
+ * selected; ties resolved exactly as the legacy block reduction does.
+ * The legacy (b,n) `temp` buffer is not needed (min-distances live on chip). */
+int b200_furthest_point_sampling(const float *xyz, int b, int n, int m, int32_t *idx, void *stream);
+
+/* Replaces gather_points(points[B,C,N], idx[B,M]) -> [B,C,M]
+ * (sampling.cpp:20-43, sampling.h:9; sampling_gpu.cu:13-25). */
+int b200_gather_points(const float *points, const int32_t *idx, int b, int c, int n, int m,
+                       float *out, void *stream);
+
+/* Replaces gather_points_grad(grad_out[B,C,M], idx[B,M], n) -> [B,C,n]
+ * (sampling.cpp:45-69, sampling.h:10; sampling_gpu.cu:39-52).  grad_points is
+ * zeroed by the callee, then scatter-added. */
+int b200_gather_points_grad(const float *grad_out, const int32_t *idx, int b, int c, int n, int m,
+                            float *grad_points, void *stream);
+
+/* Replaces ball_query(new_xyz[B,M,3], xyz[B,N,3], radius, nsample) -> [B,M,nsample] i32
+ * (ball_query.cpp:13-37, ball_query.h:9-10; ball_query_gpu.cu:14-49). */
+int b200_ball_query(const float *new_xyz, const float *xyz, int b, int n, int m, float radius,
+                    int nsample, int32_t *idx, void *stream);
+
+/* Replaces cylinder_query(new_xyz[B,M,3], xyz[B,N,3], rot[B,M,9], radius, hmin, hmax, nsample)
+ * -> [B,M,nsample] i32  (cylinder_query.cpp:10-37, cylinder_query.h:6-7;
+ * cylinder_query_gpu.cu:9-57). */
+int b200_cylinder_query(const float *new_xyz, const float *xyz, const float *rot, int b, int n,
+                        int m, float radius, float hmin, float hmax, int nsample, int32_t *idx,
+                        void *stream);
+
+/* CloudCrop fast path (models/modules.py:127-130 calls cylinder_query once per
+ * hmax with otherwise identical inputs): one scan emits all `nh` (<= 8) lists.
+ * hmax is a HOST array of nh floats; idx is [nh,B,M,nsample]; slice h equals
+ * b200_cylinder_query(..., hmax[h], ...). */
+int b200_cylinder_query_multi(const float *new_xyz, const float *xyz, const float *rot, int b,
+                              int n, int m, float radius, float hmin, const float *hmax, int nh,
+                              int nsample, int32_t *idx, void *stream);
+
+/* Replaces group_points(points[B,C,N], idx[B,M,ns]) -> [B,C,M,ns]
+ * (group_points.cpp:17-40, group_points.h:9; group_points_gpu.cu:13-33). */
+int b200_group_points(const float *points, const int32_t *idx, int b, int c, int n, int m, int ns,
+                      float *out, void *stream);
+
+/* Replaces group_points_grad(grad_out[B,C,M,ns], idx[B,M,ns], n) -> [B,C,n]
+ * (group_points.cpp:42-65, group_points.h:10; group_points_gpu.cu:48-69). */
+int b200_group_points_grad(const float *grad_out, const int32_t *idx, int b, int c, int n, int m,
+                           int ns, float *grad_points, void *stream);
+
+/* Replaces three_nn(unknowns[B,n,3], knows[B,m,3]) -> {dist2[B,n,3] f32, idx[B,n,3] i32}
+ * (interpolate.cpp:19-45, interpolate.h:11; interpolate_gpu.cu:14-64).  dist2 is
+ * the SQUARED distance; the host wrapper applies sqrt (pointnet2_utils.py:140). */
+int b200_three_nn(const float *unknown, const float *known, int b, int n, int m, float *dist2,
+                  int32_t *idx, void *stream);
+
+/* Replaces three_interpolate(points[B,c,m], idx[B,n,3], weight[B,n,3]) -> [B,c,n]
+ * (interpolate.cpp:47-75, interpolate.h:12-13; interpolate_gpu.cu:77-106). */
+int b200_three_interpolate(const float *points, const int32_t *idx, const float *weight, int b,
+                           int c, int m, int n, float *out, void *stream);
+
+/* Replaces three_interpolate_grad(grad_out[B,c,n], idx, weight, m) -> [B,c,m]
+ * (interpolate.cpp:76-104, interpolate.h:14-15; interpolate_gpu.cu:121-148). */
+int b200_three_interpolate_grad(const float *grad_out, const int32_t *idx, const float *weight,
+                                int b, int c, int n, int m, float *grad_points, void *stream);
+
+/* Replaces knn(ref[B,D,Nr], query[B,D,Nq], idx[B,k,Nq] i64 OUT) (knn/src/knn.h:12-65,
+ * knn/src/cuda/knn.cu:217-263).  1-based indices, stable top-k (ties -> lower
+ * reference index).  No Nr x Nq scratch matrix.  k <= 32; rows k' >= Nr are
+ * left untouched as in the reference. */
+int b200_knn(const float *ref, const float *query, int b, int dim, int nr, int nq, int k,
+             int64_t *ind, void *stream);
+
+/* Integer core of ModelFreeCollisionDetector.detect (utils/collision_detector.py:69-100,119):
+ * scene[N,3] f64, T[M,3] f64, R[M,9] f64 (row-major), thr[M,10] f64 = the ten
+ * half-space bounds the host derives with the reference's dtype rules
+ * (-h/2, h/2, d-fl, d, -(w/2+fw), -w/2, w/2+fw, w/2, d-fl-fw, d-fl-fw-ad).
+ * counts[M,6] i32 = #points in {global, left, right, bottom, shifting, inner}. */
+int b200_collision_counts(const double *scene, int n, const double *T, const double *R,
+                          const double *thr, int m, int32_t *counts, void *stream);
+
+/* GraspGroup.nms (graspnetAPI -> grasp_nms.nms_grasp; call sites demo_pointcloud.py:249,
+ * grasp_service.py:276).  grasps[M,17] f32; keep[M] i32 receives the surviving
+ * row numbers in descending-score order, *nkeep (device int) their count.
+ * workspace: b200_grasp_nms_workspace(m) bytes of device scratch. */
+size_t b200_grasp_nms_workspace(int m);
+int b200_grasp_nms(const float *grasps, int m, double translation_thresh, double cos_rotation_thresh,
+                   int32_t *keep, int32_t *nkeep, void *workspace, size_t workspace_bytes,
+                   void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200GRASP_H_ */
