@@ -1,0 +1,336 @@
+#!/usr/bin/env python
+"""bench.py -- scenes/sec of the GraspNet-baseline geometry hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" = one scene (BASELINE.json configs[1]: batch 1, 20000 points -> 2048/1024/512/256 SA
+points, 1024 seeds x 4 cylinder depths, 1024 grasps collision-checked + NMS) through every
+geometry op of the path in model order (graspnet-baseline_b200/pipeline.py).  Rank r of N
+processes its own scenes, no collective on the data path (scaling = weak).
+
+Prints ONE JSON line on rank 0 (see the round contract): value = scenes/s with inputs
+resident in HBM; e2e = scenes/s through the reference-facing API with HOST buffers (H2D of
+the cloud and grasps, host-side detector construction, D2H of masks/keep-sets inside the
+timed region); roofline = dominant kernel's algorithmic bytes / live CUDA-event duration
+against MEASURED_PEAKS.json; cpu_baseline = the oracle port of the same step on host cores.
+--impl reference times that CPU port alone (the reference has no other CPU implementation of
+the pointnet2 ops: SURVEY.md fact 2; oracle/ is the restatement, pinned to the reference).
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "scenes/sec (20k pts, 1024 seeds, collision+NMS)"
+UNIT = "scenes/s"
+WORKLOAD = ("cfg2: GraspNet inference geometry path, batch 1, 20000 pts -> SA 2048/1024/512/256, "
+            "1024 seeds x 4 cylinder depths, collision 1024 grasps x voxel(0.01) cloud + NMS")
+SA_CFG = [(2048, 0.04, 64, 0), (1024, 0.1, 32, 128), (512, 0.2, 16, 256), (256, 0.3, 16, 256)]
+HMAX = [0.01, 0.02, 0.03, 0.04]
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+# ---------------------------------------------------------------- CPU port of one step (oracle)
+
+def cpu_step(oracle, host, s=0):
+    """The same op sequence as pipeline.GeometryScene.run() for scene s, on the host."""
+    xyz = host["cloud"][s:s + 1]
+    cloud = xyz
+    lv = []
+    for lvl, (npoint, radius, nsample, cin) in enumerate(SA_CFG):
+        xyz_t = np.ascontiguousarray(xyz.transpose(0, 2, 1))
+        inds = oracle.furthest_point_sampling(xyz, npoint)
+        new_xyz = np.ascontiguousarray(oracle.gather_points(xyz_t, inds).transpose(0, 2, 1))
+        idx = oracle.ball_query(new_xyz, xyz, radius, nsample)
+        oracle.group_points(xyz_t, idx)
+        if cin:
+            oracle.group_points(host["feat"]["sa%d_in" % (lvl + 1)][s:s + 1], idx)
+        lv.append(new_xyz)
+        xyz = new_xyz
+    for name, u, k in (("fp1", lv[2], lv[3]), ("fp2", lv[1], lv[2])):
+        d2, i3 = oracle.three_nn(u, k)
+        oracle.three_interpolate(host["feat"][name + "_known"][s:s + 1], i3, np.full_like(d2, 1.0 / 3.0))
+    rot9 = host["rot"][s:s + 1].reshape(1, -1, 9)
+    cloud_t = np.ascontiguousarray(cloud.transpose(0, 2, 1))
+    for h in HMAX:
+        ci = oracle.cylinder_query(lv[1], cloud, rot9, 0.05, -0.02, h, 64)
+        oracle.group_points(cloud_t, ci)
+    counts = oracle.collision_counts(host["scene64"][s], host["grasps"][s], 0.05)
+    keep = oracle.grasp_nms(host["grasps"][s])
+    return counts, keep
+
+
+def host_inputs(batch, seed=1234):
+    """Host copies of everything a step consumes (same generator as GeometryScene)."""
+    import b200grasp
+    from b200grasp import synth
+    from b200grasp.voxel import voxel_down_sample
+    import torch
+    h = {"cloud": np.stack([synth.tabletop_cloud(20000, seed + s) for s in range(batch)])}
+    h["rot"] = np.stack([synth.seed_rotations(1024, seed + s) for s in range(batch)])
+    h["grasps"] = [synth.synthetic_grasps(h["cloud"][s], 1024, seed + s) for s in range(batch)]
+    h["scene64"] = [voxel_down_sample(h["cloud"][s].astype(np.float64), 0.01) for s in range(batch)]
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    npts = [c[0] for c in SA_CFG]
+    feat = {}
+    for lvl, (_, _, _, cin) in enumerate(SA_CFG):
+        if cin:
+            feat["sa%d_in" % (lvl + 1)] = torch.randn(batch, cin, npts[lvl - 1], generator=g).numpy()
+    feat["fp1_known"] = torch.randn(batch, 256, npts[3], generator=g).numpy()
+    feat["fp2_known"] = torch.randn(batch, 256, npts[2], generator=g).numpy()
+    h["feat"] = feat
+    return h
+
+
+def time_cpu(steps, warmup):
+    import oracle
+    oracle.cpu.build()
+    host = host_inputs(1)
+    for _ in range(max(warmup, 1)):
+        cpu_step(oracle, host)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        cpu_step(oracle, host)
+    dt = time.perf_counter() - t0
+    return steps / dt, dt / steps
+
+
+# ---------------------------------------------------------------- clocks sampler
+
+class Clocks(threading.Thread):
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                o = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                    "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([c.strip() for c in o.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        self.stop_flag = True
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+                for nme, v in zip(names, r[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nme)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------- algorithmic bytes
+
+def alg_bytes(name, B=1, N=20000, M=1024, nscene=7000):
+    """Compulsory HBM traffic of one launch: unique inputs read once + outputs written once."""
+    npts = [N] + [c[0] for c in SA_CFG]
+    if name.startswith("fps_sa"):
+        l = int(name[-1]); return B * (npts[l - 1] * 12 + npts[l] * 4)
+    if name.startswith("gather_sa"):
+        l = int(name[-1]); return B * (npts[l - 1] * 12 + npts[l] * 4 + npts[l] * 12)
+    if name.startswith("ball_sa"):
+        l = int(name[-1]); ns = SA_CFG[l - 1][2]
+        return B * (npts[l - 1] * 12 + npts[l] * 12 + npts[l] * ns * 4)
+    if name.startswith("group_xyz_sa"):
+        l = int(name[-1]); ns = SA_CFG[l - 1][2]
+        return B * (npts[l - 1] * 12 + npts[l] * ns * 4 + 3 * npts[l] * ns * 4)
+    if name.startswith("group_feat_sa"):
+        l = int(name[-1]); ns, c = SA_CFG[l - 1][2], SA_CFG[l - 1][3]
+        return B * (c * npts[l - 1] * 4 + npts[l] * ns * 4 + c * npts[l] * ns * 4)
+    if name == "three_nn_fp1": return B * (512 * 12 + 256 * 12 + 512 * 24)
+    if name == "three_nn_fp2": return B * (1024 * 12 + 512 * 12 + 1024 * 24)
+    if name == "three_interp_fp1": return B * (256 * 256 * 4 + 512 * 24 + 256 * 512 * 4)
+    if name == "three_interp_fp2": return B * (256 * 512 * 4 + 1024 * 24 + 256 * 1024 * 4)
+    if name == "cylinder_multi": return B * (N * 12 + 1024 * 12 + 1024 * 36 + 4 * 1024 * 64 * 4)
+    if name.startswith("cylinder_"): return B * (N * 12 + 1024 * 12 + 1024 * 36 + 1024 * 64 * 4)
+    if name == "group_xyz_crop": return B * (N * 12 + 4 * 1024 * 64 * 4 + 3 * 4 * 1024 * 64 * 4)
+    if name == "collision": return nscene * 24 + M * (3 + 9 + 10) * 8 + M * 24
+    if name == "nms": return M * 68 + M * 4 + 4
+    return 0
+
+
+# ---------------------------------------------------------------- our arm
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import b200grasp
+    from b200grasp.pipeline import GeometryScene
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    sc = GeometryScene(batch=1, num_point=20000, num_grasp=1024, seed=1234 + 1000 * rank, device=dev)
+    flush = torch.empty(512 * 1024 * 1024, dtype=torch.uint8, device=dev)      # > 126 MB L2
+    stream = torch.cuda.current_stream()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            flush.zero_(); fn()
+        barrier()
+        evs = []
+        for _ in range(steps):
+            flush.zero_()                                   # L2 flush between timed iterations (untimed)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream); fn(); e1.record(stream)
+            evs.append((e0, e1))
+        barrier()
+        ms = sum(a.elapsed_time(b) for a, b in evs)
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    clocks = Clocks(local_rank); clocks.start()
+    total_ms = timed(sc.run, args.steps, args.warmup)
+    clk = clocks.summary()
+    launches = sc.launches
+    sc.glue = 0
+    sc.run()
+    glue = sc.glue
+
+    # ---- e2e: reference-facing API, host buffers in, host results out
+    host = sc.host
+    pin = {k: torch.from_numpy(host[k]).pin_memory() for k in ("cloud", "rot")}
+    pin_g = torch.from_numpy(host["grasps"][0]).pin_memory()
+    h2d = pin["cloud"].numel() * 4 + pin["rot"].numel() * 4 + pin_g.numel() * 4
+    d2h_box = [0]
+
+    def e2e_step():
+        sc.cloud = pin["cloud"].to(dev, non_blocking=True)
+        sc.rot = pin["rot"].to(dev, non_blocking=True)
+        out = sc.run_geometry()
+        det = b200grasp.ModelFreeCollisionDetector(host["cloud"][0], voxel_size=0.01, device=dev)
+        gg = b200grasp.GraspGroup(host["grasps"][0])
+        mask = det.detect(gg, approach_dist=0.05, collision_thresh=0.01)
+        kept = gg[~mask].nms(device=dev)
+        seeds = out["sa2_inds"].cpu()
+        crop = out["crop_idx"].cpu()
+        d2h_box[0] = seeds.numel() * 4 + crop.numel() * 4 + len(gg) * 24 + len(gg) * 4 + 4
+        return kept, mask
+
+    e2e_ms = timed(e2e_step, args.steps, args.warmup)
+    h2d += len(host["scene64"][0]) * 24 + 1024 * 22 * 8 + 1024 * 68        # detector scene + T/R/thr + nms rows
+
+    if rank != 0:
+        return None
+    # ---- per-kernel pass (rank 0): CUDA events around every launch, L2 flushed before each pass
+    per = {}
+    reps = 5
+    for _ in range(reps):
+        flush.zero_()
+        sc.timer = []
+        sc.run()
+        torch.cuda.synchronize()
+        for name, e0, e1 in sc.timer:
+            per.setdefault(name, []).append(e0.elapsed_time(e1))
+        sc.timer = None
+    peak, which = peaks()
+    nscene = len(host["scene64"][0])
+    kern = []
+    for name, v in per.items():
+        ms = float(np.mean(v))
+        ab = alg_bytes(name, nscene=nscene)
+        kern.append({"kernel": name, "ms": round(ms, 5), "alg_bytes": ab,
+                     "gbs": round(ab / (ms * 1e-3) / 1e9, 3) if ms > 0 else None})
+    kern.sort(key=lambda k: -k["ms"])
+    top = kern[0]
+    roof = {"bound": "hbm", "kernel": top["kernel"], "achieved": top["gbs"], "peak": peak, "unit": "GB/s",
+            "frac": round(top["gbs"] / peak, 6), "traffic": None, "peak_source": which,
+            "note": "FPS is a serial m-step chain (latency-bound, state in registers); see DESIGN.md"}
+    value = world * args.steps / (total_ms * 1e-3)
+    e2e = world * args.steps / (e2e_ms * 1e-3)
+    line = {"metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(total_ms / args.steps, 4), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32 (fp64 collision/NMS, int32 indices)",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "scenes_per_step_per_gpu": 1, "l2": "flushed between timed iterations "
+                       "(512 MiB write)", "glue_torch_launches_per_step": glue},
+            "clocks": clk, "gpu_launches": launches * args.steps,
+            "e2e": {"value": round(e2e, 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+                    "d2h_bytes_per_step": int(d2h_box[0]), "ms_per_step": round(e2e_ms / args.steps, 4)},
+            "roofline": roof, "kernels": kern}
+    return line
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        sps, sec = time_cpu(args.steps, args.warmup)
+        cores = os.cpu_count()
+        cb = {"value": round(sps, 4), "unit": UNIT, "cores": cores, "kind": "port",
+              "sample": "%d whole scenes of the cfg2 workload (oracle/geom_oracle.c, OpenMP over centres/grasps)" % args.steps}
+        print(json.dumps({"metric": METRIC, "value": round(sps, 4), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                          "warmup": args.warmup, "ms_per_step": round(sec * 1e3, 3), "higher_is_better": True,
+                          "scaling": "weak", "vs_baseline": None, "dtype": "f32 (fp64 collision/NMS)", "data": "synthetic",
+                          "config": {"workload": WORKLOAD}, "impl": "reference", "cpu_baseline": cb,
+                          "e2e": {"value": round(sps, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return 0
+
+    line = run_ours(args, rank, world, local_rank)
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            n = 8
+            sps, sec = time_cpu(n, 1)
+            line["cpu_baseline"] = {"value": round(sps, 4), "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
+                                    "sample": "%d whole scenes of the same workload, oracle C port with OpenMP" % n}
+        print(json.dumps(line))
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -90,6 +90,19 @@ class GeometryScene:
 
     # ---- one pass
     def run(self):
+        out = self.run_geometry()
+        L = self.launches
+        counts, keeps = [], []
+        for s in range(self.B):
+            T, R, thr = self.coll_in[s]
+            counts.append(self._op('collision', ops.collision_counts, self.scene64[s], T, R, thr))
+            keeps.append(self._op('nms', ops.grasp_nms, self.grasps[s], 0.03, math.cos(30.0 / 180.0 * math.pi)))
+            L += 1 + 3
+        out["collision_counts"], out["nms"] = counts, keeps
+        self.launches = L
+        return out
+
+    def run_geometry(self):
         out = {}
         L = 0
         xyz = self.cloud
@@ -131,12 +144,5 @@ class GeometryScene:
             cat = cat.contiguous(); self.glue += 1
         out["crop_grouped_xyz"] = self._op('group_xyz_crop', ops.group_points, cloud_t, cat)
         L += 1
-        counts, keeps = [], []
-        for s in range(self.B):
-            T, R, thr = self.coll_in[s]
-            counts.append(self._op('collision', ops.collision_counts, self.scene64[s], T, R, thr))
-            keeps.append(self._op('nms', ops.grasp_nms, self.grasps[s], 0.03, math.cos(30.0 / 180.0 * math.pi)))
-            L += 1 + 3
-        out["collision_counts"], out["nms"] = counts, keeps
         self.launches = L
         return out
