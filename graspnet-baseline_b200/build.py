@@ -53,5 +53,20 @@ def build(force=False, verbose=False):
     return LIB
 
 
+def build_fps_profile():
+    """Instrumented FPS-only library (clock64 stage counters) for tools/fps_prof.py; not shipped."""
+    out = os.path.join(HERE, "lib", "libb200fps_prof.so")
+    cmd = [NVCC, "-shared", "-o", out, os.path.join(CSRC, "fps.cu"), os.path.join(CSRC, "common.cu"),
+           "-DFPS_PROFILE"] + FLAGS
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode:
+        sys.stderr.write(r.stdout + r.stderr)
+        raise RuntimeError("nvcc failed (fps profile build)")
+    return out
+
+
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))
+    if "--fps-profile" in sys.argv:
+        print(build_fps_profile())
+    else:
+        print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))

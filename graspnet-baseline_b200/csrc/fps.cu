@@ -2,42 +2,37 @@
 //
 // Replaces furthest_point_sampling_kernel (reference pointnet2/_ext_src/src/sampling_gpu.cu:74-178).
 //
-// Design: one thread-block CLUSTER of C CTAs per cloud (C = 1 for small clouds).
-// Every thread keeps its points' x,y,z AND their running min-distance in
-// registers for the whole m-step chain, so a step touches no global or shared
-// memory for point data at all (the legacy kernel re-reads 12 B/point from L2 and
-// reads+writes a 4 B/point HBM temp every step).  Per step:
-//   registers: d = |p - last|^2, md = min(md, d), thread-local argmax
-//   warp:      redux.sync max on the float bits, redux.sync min on the tie priority
-//   CTA:       one __syncthreads over 16 per-warp slots (double buffered)
-//   cluster:   the CTA winner {key, prio, x, y, z} is pushed into every peer's
-//              shared memory (DSMEM), one cluster barrier, every CTA picks the
-//              same global winner and already holds its coordinates.
+// FPS is an m-step dependent chain (pick the point furthest from the chosen set, update
+// every point's min-distance, repeat), so its cost is steps x per-step latency, not bytes.
+// Design: one thread-block CLUSTER of C CTAs per cloud (C = 1 for small clouds).  Every
+// thread keeps its points' x,y,z AND their running min-distance in registers for the whole
+// chain: a step touches no global memory and no shared memory for point data (the legacy
+// kernel re-reads 12 B/point from L2 and reads+writes a 4 B/point HBM temp every step).
+// Per step there is exactly ONE exchange stage:
+//   registers: d = |p - last|^2, md = min(md, d), thread-local first strict maximum
+//   warp:      redux.sync max on the float bits (+ a min on the tie priority only when two
+//              lanes hold the same maximum)
+//   exchange:  every warp publishes its winner {key, prio, x, y, z} to ALL CTAs of the
+//              cluster -- st.async into the peers' shared memory, completion counted by an
+//              mbarrier (complete_tx), double buffered by step parity; with C = 1 it is a
+//              plain shared-memory store and one __syncthreads
+//   select:    every warp reduces the C x NW published entries and already holds the
+//              winner's coordinates for the next step.
+// No cluster-wide barrier, no second intra-CTA stage, no global round trip.
 //
-// Exactness: the winner is  max d2, then min bitrev(k mod BS) over log2(BS) bits,
-// then min k, with BS = largest power of two <= n clamped to 512 -- the
-// closed form of the legacy per-thread strided scan + stride-halving tree
-// (oracle/geom_oracle.c: oracle_fps == oracle_fps_tree).  Distances use the
-// legacy FMA association; the skip test `(double)mag <= 1e-3` is done in fp64.
-#include <cooperative_groups.h>
-
+// Exactness: the winner is  max d2, then min bitrev(k mod BS) over log2(BS) bits, then
+// min k, with BS = largest power of two <= n clamped to 512 -- the closed form of the
+// legacy per-thread strided scan + stride-halving tree (oracle/geom_oracle.c:
+// oracle_fps == oracle_fps_tree; tests/test_gpu_vs_legacy.py pins it to the legacy kernel
+// itself).  Distances use the legacy FMA association; the skip test `(double)mag <= 1e-3`
+// is done in fp64.
 #include "common.cuh"
-
-namespace cg = cooperative_groups;
 
 namespace {
 
-constexpr int NT = 512;        // threads per CTA (16 warps)
-constexpr int NW = NT / 32;
-constexpr int MAXC = 16;       // largest cluster supported
-
-struct __align__(16) Slot {
-  int key;          // float bits of the candidate's min-distance (negative => none)
-  unsigned prio;    // tie priority (smaller wins); encodes the point index
-  float x, y;
-  float z;
-  int pad0, pad1, pad2;
-};
+constexpr int MAXC = 16;       // largest cluster supported (non-portable size, opt-in)
+constexpr int MAXE = 256;      // published entries per step: C x warps-per-CTA
+constexpr int ENT_BYTES = 20;  // key, prio, x, y (16 B) + z (4 B)
 
 __device__ __forceinline__ unsigned prio_of(int k, int bits) {
   const unsigned r = bits ? (__brev((unsigned)k) >> (32 - bits)) : 0u;  // bitrev of the low `bits` bits
@@ -49,121 +44,402 @@ __device__ __forceinline__ int index_of(unsigned prio, int bits) {
   return (int)(((prio & 0x3fffffu) << bits) | lo);
 }
 
-template <int PPT, bool CLUSTER>
+// ---- cluster / mbarrier / st.async plumbing (PTX; shared::cluster addresses are 32-bit)
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ uint32_t map_to_rank(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ void st_async_v4(uint32_t addr, int a, unsigned b, float c, float d, uint32_t bar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];"
+               ::"r"(addr), "r"(a), "r"(b), "r"(__float_as_uint(c)), "r"(__float_as_uint(d)), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void st_async_b32(uint32_t addr, float v, uint32_t bar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];"
+               ::"r"(addr), "r"(__float_as_uint(v)), "r"(bar) : "memory");
+}
+
+// order in which a thread visits its 512/NT residues (mod 512): ascending bit-reversed
+// priority, i.e. residue tid + NT * brev(r) with brev over log2(R) bits
+__host__ __device__ constexpr int brev_small(int r, int R) {
+  int out = 0;
+  for (int b = 1, o = R >> 1; b < R; b <<= 1, o >>= 1)
+    if (r & b) out |= o;
+  return out;
+}
+
+// ---- packed fp32x2 arithmetic (FADD2 / FMUL2 / FFMA2 on sm_100): two points per instruction,
+// each half rounded exactly like the scalar op, so the legacy association is preserved
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float &lo, float &hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+
+#ifdef FPS_PROFILE
+// stage cycle counters of (cloud 0, rank 0, thread 0): compute, warp-reduce, publish, wait, select
+__device__ unsigned long long g_fps_prof[8];
+// the clock read is predicated on `dep`, so it cannot issue before that value exists
+#define FPS_TICK(i, dep)                                                                   \
+  do {                                                                                     \
+    long long t__ = tprev;                                                                 \
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %1, 0x7fc0dead;\n\t@q mov.u64 %0, %%clock64;\n\t}" \
+                 : "+l"(t__) : "r"(dep) : "memory");                                       \
+    if (prof_on) prof[i] += (unsigned long long)(t__ - tprev);                             \
+    tprev = t__;                                                                           \
+  } while (0)
+#else
+#define FPS_TICK(i, dep) do { } while (0)
+#endif
+
+struct Entry { int key; unsigned prio; float x, y, z; };
+
+__device__ __forceinline__ void better(Entry &a, const Entry &b) {   // a = the winner of (a, b)
+  if (b.key > a.key || (b.key == a.key && b.prio < a.prio)) a = b;
+}
+
+constexpr int TAB_LIMIT = 200 * 1024;   // bytes of shared memory the per-CTA point table may take
+
+// PP point PAIRS per thread (PPT = 2 PP points), NT threads per CTA.  A CTA owns `chunk` =
+// PPT*NT consecutive points (a multiple of 512); thread `tid` owns the residues tid + NT*b
+// (mod 512) of every 512-block of the chunk, visited so that register slot order ==
+// tie-priority order.
+// ET = 0: one CTA per cloud (entries exchanged through its own shared memory);
+// ET > 0: cluster of C CTAs, C * NW <= 32 * ET entries, ET per lane in the select stage.
+template <int PP, int NT, int ET>
 __global__ void __launch_bounds__(NT, 1)
-fps_kernel(const float *__restrict__ xyz, int n, int m, int C, int chunk, int bits,
-           int32_t *__restrict__ idx) {
-  __shared__ int w_key[2][NW];
-  __shared__ unsigned w_prio[2][NW];
-  __shared__ Slot c_slot[2][MAXC];
+fps_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, int32_t *__restrict__ idx) {
+  constexpr bool CLUSTER = ET > 0;
+  constexpr int PPT = 2 * PP;
+  constexpr int NW = NT / 32;
+  constexpr int R = 512 / NT;
+  constexpr int PPR = PPT / R;
+  constexpr bool TAB = PPT * NT * 16 <= TAB_LIMIT;
+  constexpr bool SOLO = !CLUSTER && TAB;           // one CTA: winner by a shared-memory 64-bit max
+  static_assert(PPT % R == 0 && PPR >= 1, "PPT must cover whole 512-blocks");
+  // slot i of a thread: local point number OFF(i) + tid, tie-priority PRI(i) + prio0
+#define OFF(i) (((i) % PPR) * 512 + NT * brev_small((i) / PPR, R))
+#define PRI(i) (((unsigned)((i) / PPR) << 22) + (unsigned)((i) % PPR))
+#define CODE(i) ((TAB && !SOLO) ? (unsigned)OFF(i) : PRI(i))
+  extern __shared__ float4 tab[];                  // TAB: x, y, z, prio of every point of the chunk
+  __shared__ __align__(16) int4 ent[2][MAXE];      // key, prio, x, y
+  __shared__ float entz[2][MAXE];
+  __shared__ __align__(8) unsigned long long full[2];
+  __shared__ __align__(16) int2 wslot[3][NW];      // SOLO: per warp {~prio, key} = one signed 64-bit value
 
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
-  const int rank = CLUSTER ? (int)(blockIdx.x % C) : 0;
+  const int rank = CLUSTER ? (int)cluster_ctarank() : 0;
   const int cloud = CLUSTER ? (int)(blockIdx.x / C) : (int)blockIdx.x;
   const float *p = xyz + (size_t)cloud * n * 3;
   int32_t *out = idx + (size_t)cloud * m;
+  const int E = C * NW;                            // entries published per step
+  const int base = rank * (PPT * NT);
+#ifdef FPS_PROFILE
+  unsigned long long prof[6] = {0, 0, 0, 0, 0, 0};
+  const bool prof_on = (blockIdx.x == 0 && tid == 0);
+  long long tprev = clock64();
+#endif
+  // tie priority of slot i = prio0 + PRI(i): brev9(tid + NT*brev(r)) == brev9(tid) + r for
+  // r < R, and k >> 9 advances by one per 512-block.  (n < 512 runs with one valid slot.)
+  const unsigned prio0 = prio_of(base + tid, bits);
 
-  // chunk is a multiple of 512, so every point of one thread shares k mod BS and
-  // a lower register slot i always has the smaller tie priority.
-  const int base = rank * chunk;
-  const int hi = min(n, base + chunk);
-
-  float x[PPT], y[PPT], z[PPT], md[PPT];
+  f32x2 X[PP], Y[PP], Z[PP];
+  float md[PPT];
 #pragma unroll
-  for (int i = 0; i < PPT; ++i) {
-    const int k = base + i * NT + tid;
-    if (k < hi) {
-      x[i] = __ldg(p + 3 * (size_t)k);
-      y[i] = __ldg(p + 3 * (size_t)k + 1);
-      z[i] = __ldg(p + 3 * (size_t)k + 2);
-      const float mag = sq3_p2(x[i], y[i], z[i]);
-      md[i] = ((double)mag <= 1e-3) ? -1.0f : 1e10f;   // -1: never updated, never selected
-    } else {
-      x[i] = y[i] = z[i] = 0.f;
-      md[i] = -1.0f;
+  for (int j = 0; j < PP; ++j) {
+    float c[2][3];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int i = 2 * j + h;
+      const int k = base + OFF(i) + tid;
+      if (k < n) {
+        c[h][0] = __ldg(p + 3 * (size_t)k);
+        c[h][1] = __ldg(p + 3 * (size_t)k + 1);
+        c[h][2] = __ldg(p + 3 * (size_t)k + 2);
+        const float mag = sq3_p2(c[h][0], c[h][1], c[h][2]);
+        md[i] = ((double)mag <= 1e-3) ? -1.0f : 1e10f;   // -1: never updated, never selected
+      } else {
+        c[h][0] = c[h][1] = c[h][2] = 0.f;
+        md[i] = -1.0f;
+      }
+      if (TAB) tab[OFF(i) + tid] = make_float4(c[h][0], c[h][1], c[h][2], __uint_as_float(prio0 + PRI(i)));
     }
+    X[j] = pack2(c[0][0], c[1][0]);
+    Y[j] = pack2(c[0][1], c[1][1]);
+    Z[j] = pack2(c[0][2], c[1][2]);
   }
 
   float ox = __ldg(p), oy = __ldg(p + 1), oz = __ldg(p + 2);
   if (rank == 0 && tid == 0) out[0] = 0;
-
-  for (int j = 1; j < m; ++j) {
-    const int par = j & 1;
-    // ---- registers: update min-distances, thread-local first strict maximum
-    float best = -1.0f;
-    int bi = 0;
-#pragma unroll
-    for (int i = 0; i < PPT; ++i) {
-      const float d = sq3_p2(__fsub_rn(x[i], ox), __fsub_rn(y[i], oy), __fsub_rn(z[i], oz));
-      const float d2 = fminf(d, md[i]);     // md = -1 stays -1 (d >= 0 or NaN)
-      md[i] = d2;
-      if (d2 > best) { best = d2; bi = i; }
-    }
-    // ---- warp: max key, then min priority among the lanes holding it
-    const int lkey = __float_as_int(best);            // >= 0 for real candidates, < 0 for none
-    const int wkey = __reduce_max_sync(0xffffffffu, lkey);
-    const unsigned lprio = (lkey == wkey && lkey >= 0) ? prio_of(base + bi * NT + tid, bits) : 0xffffffffu;
-    const unsigned wprio = __reduce_min_sync(0xffffffffu, lprio);
-    if (lane == 0) { w_key[par][warp] = wkey; w_prio[par][warp] = wprio; }
-    __syncthreads();
-    // ---- CTA: every warp reduces the 16 per-warp slots
-    const int skey = lane < NW ? w_key[par][lane] : (int)0x80000000;
-    const unsigned sprio = lane < NW ? w_prio[par][lane] : 0xffffffffu;
-    const int ckey = __reduce_max_sync(0xffffffffu, skey);
-    const unsigned cprio = __reduce_min_sync(0xffffffffu, skey == ckey ? sprio : 0xffffffffu);
-    // ---- publish the CTA winner (with its coordinates) to every CTA of the cluster
-    const bool owner = (ckey >= 0) ? (lprio == cprio && lkey == ckey) : (tid == 0);
-    const unsigned own_mask = __ballot_sync(0xffffffffu, owner);
-    if (own_mask) {                                   // warp-uniform: exactly one warp of the CTA
-      float sx = 0.f, sy = 0.f, sz = 0.f;
-      if (owner && ckey >= 0) {
-#pragma unroll
-        for (int i = 0; i < PPT; ++i)
-          if (i == bi) { sx = x[i]; sy = y[i]; sz = z[i]; }
-      }
-      const int src = __ffs(own_mask) - 1;
-      sx = __shfl_sync(0xffffffffu, sx, src);
-      sy = __shfl_sync(0xffffffffu, sy, src);
-      sz = __shfl_sync(0xffffffffu, sz, src);
-      if (lane < C) {
-        Slot s;
-        s.key = ckey; s.prio = cprio; s.x = sx; s.y = sy; s.z = sz;
-        s.pad0 = s.pad1 = s.pad2 = 0;
-        Slot *dst = &c_slot[par][rank];
-        if (CLUSTER) dst = cg::this_cluster().map_shared_rank(dst, lane);
-        *dst = s;
-      }
-    }
-    if (CLUSTER) cg::this_cluster().sync(); else __syncthreads();
-    // ---- every CTA picks the same global winner
-    const int gk = lane < C ? c_slot[par][lane].key : (int)0x80000000;
-    const unsigned gp = lane < C ? c_slot[par][lane].prio : 0xffffffffu;
-    const int gkey = __reduce_max_sync(0xffffffffu, gk);
-    const unsigned gprio = __reduce_min_sync(0xffffffffu, gk == gkey ? gp : 0xffffffffu);
-    const unsigned wmask = __ballot_sync(0xffffffffu, gk == gkey && gp == gprio);
-    const int wr = __ffs(wmask) - 1;
-    int sel = 0;
-    if (gkey >= 0) {
-      ox = c_slot[par][wr].x; oy = c_slot[par][wr].y; oz = c_slot[par][wr].z;
-      sel = index_of(gprio, bits);
-    }  // else: every point is skipped -> legacy yields index 0 and nothing is ever updated
-    if (rank == 0 && tid == 0) out[j] = sel;
+  if (SOLO) {
+    if (tid < 3 * NW) wslot[tid / NW][tid % NW] = make_int2(0, (int)0x80000000);
+    __syncthreads();                               // table and slots written
   }
+  int cur = 0;                                     // SOLO: slot of this step (rotates over 3)
+
+  // shared::cluster addresses of buffer 0 (buffer 1 is a fixed byte offset further on);
+  // lane l < C publishes this warp's entry into CTA l
+  uint32_t bar_local = 0, ent_remote = 0, z_remote = 0, bar_remote = 0;
+  if (CLUSTER) {
+    bar_local = smem_u32(&full[0]);
+    if (tid == 0) {
+      mbar_init(bar_local, 1);
+      mbar_init(bar_local + 8, 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      mbar_arrive_expect_tx(bar_local, (uint32_t)E * ENT_BYTES);
+      mbar_arrive_expect_tx(bar_local + 8, (uint32_t)E * ENT_BYTES);
+    }
+    const uint32_t peer = (uint32_t)(lane < C ? lane : 0);
+    ent_remote = map_to_rank(smem_u32(&ent[0][rank * NW + warp]), peer);
+    z_remote = map_to_rank(smem_u32(&entz[0][rank * NW + warp]), peer);
+    bar_remote = map_to_rank(bar_local, peer);
+    cluster_sync_all();                            // barriers initialised before any peer sends
+  }
+
+  for (int s = 0; s + 1 < m; ++s) {
+    const int par = s & 1;
+    FPS_TICK(5, s);
+    // ---- registers: update min-distances, thread-local first strict maximum
+    const f32x2 OX = pack2(ox, ox), OY = pack2(oy, oy), OZ = pack2(oz, oz);
+    float best = -1.0f;
+    unsigned bc = 0;
+#pragma unroll
+    for (int j = 0; j < PP; ++j) {
+      const f32x2 dx = sub2(X[j], OX), dy = sub2(Y[j], OY), dz = sub2(Z[j], OZ);
+      const f32x2 d = fma2(dz, dz, fma2(dx, dx, mul2(dy, dy)));    // legacy association, per half
+      float d0, d1;
+      unpack2(d, d0, d1);
+      const float m0 = fminf(d0, md[2 * j]);       // md = -1 stays -1 (d >= 0 or NaN)
+      md[2 * j] = m0;
+      if (m0 > best) { best = m0; bc = CODE(2 * j); }
+      const float m1 = fminf(d1, md[2 * j + 1]);
+      md[2 * j + 1] = m1;
+      if (m1 > best) { best = m1; bc = CODE(2 * j + 1); }
+    }
+    FPS_TICK(0, __float_as_uint(best));
+    if (SOLO) {
+      // ---- one CTA: per warp, lane 0 stores the warp's maximum key and the lanes holding it
+      // post ~prio with a native 32-bit shared max (no unique owner needed); after the barrier
+      // everybody takes the signed 64-bit max {key, ~prio} over the warps and looks the
+      // winner's coordinates up in the point table.  The slot of step s+1 is cleared now: its
+      // last readers (step s-2) are all past barrier s-1.
+      const int lkey = __float_as_int(best);       // >= 0 for real candidates, < 0 for none
+      const int wkey = __reduce_max_sync(0xffffffffu, lkey);
+      const int nxt = cur == 2 ? 0 : cur + 1;
+      if (lane == 0) {
+        wslot[cur][warp].y = wkey;
+        wslot[nxt][warp].x = 0;
+      }
+      if (lkey == wkey && wkey >= 0) atomicMax((unsigned *)&wslot[cur][warp].x, ~(prio0 + bc));
+      FPS_TICK(1, (unsigned)wkey);
+      __syncthreads();
+      long long v;
+      {
+        long long e[NW];
+        const longlong2 *row = reinterpret_cast<const longlong2 *>(&wslot[cur][0]);
+#pragma unroll
+        for (int t = 0; t < NW / 2; ++t) {
+          const longlong2 q = row[t];
+          e[2 * t] = q.x; e[2 * t + 1] = q.y;
+        }
+#pragma unroll
+        for (int st = 1; st < NW; st *= 2)
+#pragma unroll
+          for (int t = 0; t + st < NW; t += 2 * st) e[t] = e[t] > e[t + st] ? e[t] : e[t + st];
+        v = e[0];
+      }
+      cur = nxt;
+      FPS_TICK(3, (unsigned)v);
+      int sel = 0;
+      if (v >= 0) {
+        sel = index_of(~(unsigned)v, bits);
+        const float4 t = tab[sel];
+        ox = t.x; oy = t.y; oz = t.z;
+      }  // else: every point is skipped -> legacy yields index 0 and nothing is ever updated
+      FPS_TICK(4, __float_as_uint(ox));
+      if (tid == 0) out[s + 1] = sel;
+      continue;
+    }
+    // ---- this thread's candidate: coordinates and tie priority
+    float cx = 0.f, cy = 0.f, cz = 0.f;
+    unsigned cprio;
+    if (TAB) {
+      const float4 t = tab[bc + tid];
+      cx = t.x; cy = t.y; cz = t.z; cprio = __float_as_uint(t.w);
+    } else {
+      cprio = prio0 + bc;
+#pragma unroll
+      for (int j = 0; j < PP; ++j) {
+        float a0, a1, b0, b1, c0, c1;
+        unpack2(X[j], a0, a1); unpack2(Y[j], b0, b1); unpack2(Z[j], c0, c1);
+        if (bc == PRI(2 * j)) { cx = a0; cy = b0; cz = c0; }
+        if (bc == PRI(2 * j + 1)) { cx = a1; cy = b1; cz = c1; }
+      }
+    }
+    // ---- warp winner: max key, then min tie priority among the lanes holding it (unique);
+    // its coordinates reach every lane as an unsigned max against zeros
+    const int lkey = __float_as_int(best);         // >= 0 for real candidates, < 0 for none
+    const int wkey = __reduce_max_sync(0xffffffffu, lkey);
+    const bool cand = (lkey == wkey) && (wkey >= 0);
+    const unsigned lprio = cand ? cprio : 0xffffffffu;
+    const unsigned wprio = __reduce_min_sync(0xffffffffu, lprio);
+    const bool own = cand && (lprio == wprio);
+    const float sx = __uint_as_float(__reduce_max_sync(0xffffffffu, own ? __float_as_uint(cx) : 0u));
+    const float sy = __uint_as_float(__reduce_max_sync(0xffffffffu, own ? __float_as_uint(cy) : 0u));
+    const float sz = __uint_as_float(__reduce_max_sync(0xffffffffu, own ? __float_as_uint(cz) : 0u));
+    FPS_TICK(1, __float_as_uint(sz));
+    if (CLUSTER) {
+      // push the entry into every CTA of the cluster (own CTA included); each store carries
+      // its completion bytes to the destination CTA's mbarrier
+      if (lane < C) {
+        st_async_v4(ent_remote + par * (MAXE * 16), wkey, wprio, sx, sy, bar_remote + par * 8);
+        st_async_b32(z_remote + par * (MAXE * 4), sz, bar_remote + par * 8);
+      }
+      FPS_TICK(2, s);
+      mbar_wait(bar_local + par * 8, (uint32_t)(s >> 1) & 1u);
+      // re-arm this buffer for step s+2; peers cannot complete it before every warp of this
+      // CTA has published step s+1, which happens after this point in program order
+      if (tid == 0 && s + 3 < m) mbar_arrive_expect_tx(bar_local + par * 8, (uint32_t)E * ENT_BYTES);
+    } else {
+      if (lane == 0) {
+        ent[par][warp] = make_int4(wkey, (int)wprio, __float_as_int(sx), __float_as_int(sy));
+        entz[par][warp] = sz;
+      }
+      FPS_TICK(2, s);
+      __syncthreads();
+    }
+    FPS_TICK(3, (unsigned)ent[par][0].x);
+    // ---- select the global winner among the E published entries
+    Entry w;
+    constexpr bool SCAN = !CLUSTER && NW <= 8;     // few entries: private scan beats the redux rounds
+    constexpr int ETL = CLUSTER ? ET : 1;
+    if (SCAN) {
+      // one entry per warp: every thread scans them all (broadcast reads), no shuffles
+      Entry e[NW];
+#pragma unroll
+      for (int t = 0; t < NW; ++t) {
+        const int4 v = ent[par][t];
+        e[t].key = v.x; e[t].prio = (unsigned)v.y; e[t].x = __int_as_float(v.z); e[t].y = __int_as_float(v.w);
+        e[t].z = entz[par][t];
+      }
+#pragma unroll
+      for (int st = 1; st < NW; st *= 2)
+#pragma unroll
+        for (int t = 0; t + st < NW; t += 2 * st) better(e[t], e[t + st]);
+      w = e[0];
+    } else {
+      // ETL entries per lane, then three redux rounds: key, tie priority, coordinates
+      w.key = (int)0x80000000; w.prio = 0xffffffffu; w.x = w.y = w.z = 0.f;
+#pragma unroll
+      for (int t = 0; t < ETL; ++t) {
+        const int e = t * 32 + lane;
+        const int ee = e < E ? e : 0;
+        const int4 v = ent[par][ee];
+        Entry c;
+        c.key = e < E ? v.x : (int)0x80000000; c.prio = (unsigned)v.y;
+        c.x = __int_as_float(v.z); c.y = __int_as_float(v.w); c.z = entz[par][ee];
+        better(w, c);
+      }
+      const int gkey = __reduce_max_sync(0xffffffffu, w.key);
+      const unsigned cp = (w.key == gkey) ? w.prio : 0xffffffffu;
+      const unsigned gprio = __reduce_min_sync(0xffffffffu, cp);
+      const bool win = (cp == gprio) && (w.key == gkey) && (gkey >= 0);   // exactly one lane
+      w.x = __uint_as_float(__reduce_max_sync(0xffffffffu, win ? __float_as_uint(w.x) : 0u));
+      w.y = __uint_as_float(__reduce_max_sync(0xffffffffu, win ? __float_as_uint(w.y) : 0u));
+      w.z = __uint_as_float(__reduce_max_sync(0xffffffffu, win ? __float_as_uint(w.z) : 0u));
+      w.key = gkey; w.prio = gprio;
+    }
+    FPS_TICK(4, __float_as_uint(w.x));
+    if (w.key >= 0) { ox = w.x; oy = w.y; oz = w.z; }
+    // else: every point is skipped -> legacy yields index 0 and nothing is ever updated
+    // the raw tie priority is stored now (one predicated store), turned into the point
+    // index after the chain: keeps the bit-reversal off every step's critical path
+    if (rank == 0 && tid == 0) out[s + 1] = w.key >= 0 ? (int)w.prio : -1;
+  }
+  if (!SOLO && rank == 0) {
+    __syncthreads();
+    for (int j = 1 + tid; j < m; j += NT) {
+      const int v = out[j];
+      out[j] = v == -1 ? 0 : index_of((unsigned)v, bits);
+    }
+  }
+  if (CLUSTER) cluster_sync_all();                 // no CTA leaves while peers may still address it
+#ifdef FPS_PROFILE
+  if (prof_on && cloud == 0 && rank == 0)
+    for (int i = 0; i < 6; ++i) g_fps_prof[i] = prof[i];
+#endif
+#undef OFF
+#undef PRI
+#undef CODE
 }
 
-template <int PPT>
-int launch(const float *xyz, int b, int n, int m, int C, int chunk, int bits, int32_t *idx,
-           cudaStream_t st) {
-  if (C == 1) {
-    fps_kernel<PPT, false><<<b, NT, 0, st>>>(xyz, n, m, 1, chunk, bits, idx);
+template <int PP, int NT, int ET>
+int launch(const float *xyz, int b, int n, int m, int C, int bits, int32_t *idx, cudaStream_t st) {
+  constexpr int tab_bytes = (2 * PP * NT * 16 <= TAB_LIMIT) ? 2 * PP * NT * 16 : 0;
+  auto kern = fps_kernel<PP, NT, ET>;
+  static bool configured = false;                  // per instantiation
+  if (!configured) {
+    if (tab_bytes > 32 * 1024)
+      B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tab_bytes));
+    if (ET > 0) B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    configured = true;
+  }
+  if (ET == 0) {
+    kern<<<b, NT, tab_bytes, st>>>(xyz, n, m, 1, bits, idx);
     B200_LAUNCH_CHECK();
     return 0;
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(b * C), 1, 1);
   cfg.blockDim = dim3(NT, 1, 1);
-  cfg.dynamicSmemBytes = 0;
+  cfg.dynamicSmemBytes = tab_bytes;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -172,17 +448,73 @@ int launch(const float *xyz, int b, int n, int m, int C, int chunk, int bits, in
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  if (C > 8)
-    B200_CUDA(cudaFuncSetAttribute(fps_kernel<PPT, true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-  B200_CUDA(cudaLaunchKernelEx(&cfg, fps_kernel<PPT, true>, xyz, n, m, C, chunk, bits, idx));
+  B200_CUDA(cudaLaunchKernelEx(&cfg, kern, xyz, n, m, C, bits, idx));
   return 0;
+}
+
+template <int PP, int NT>
+int launch_et(const float *xyz, int b, int n, int m, int C, int bits, int32_t *idx, cudaStream_t st) {
+  const int E = C * (NT / 32);
+  if (C == 1) return launch<PP, NT, 0>(xyz, b, n, m, C, bits, idx, st);
+  if (E <= 32) return launch<PP, NT, 1>(xyz, b, n, m, C, bits, idx, st);
+  if (E <= 64) return launch<PP, NT, 2>(xyz, b, n, m, C, bits, idx, st);
+  if (E <= 128) return launch<PP, NT, 4>(xyz, b, n, m, C, bits, idx, st);
+  return B200_ECAPACITY;
+}
+
+// smallest supported points-per-thread >= want (0 if none)
+int round_ppt(int want, int nt) {
+  static const int p512[] = {2, 4, 6, 8, 10, 12, 16, 20, 24};
+  static const int p256[] = {2, 4, 6, 8, 10, 12, 16, 20, 24, 32, 40, 48, 52};
+  static const int p128[] = {4, 8, 12, 16, 20, 24, 32, 40, 48};
+  if (nt == 512) {
+    for (int v : p512) if (v >= want) return v;
+  } else if (nt == 256) {
+    for (int v : p256) if (v >= want) return v;
+  } else {
+    for (int v : p128) if (v >= want) return v;
+  }
+  return 0;
+}
+
+int g_force_cluster = 0, g_force_threads = 0;
+
+// Largest cluster size the device will co-schedule for this kernel family (16 needs the
+// non-portable opt-in and a GPC with 16 free SMs; fall back to the portable 8).
+template <int NT>
+int max_cluster() {
+  static int cached = 0;
+  if (cached) return cached;
+  auto kern = fps_kernel<(NT == 128 ? 2 : 1), NT, 2>;
+  cached = 8;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(MAXC, 1, 1);
+    cfg.blockDim = dim3(NT, 1, 1);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = MAXC;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int nclusters = 0;
+    if (cudaOccupancyMaxActiveClusters(&nclusters, kern, &cfg) == cudaSuccess && nclusters >= 1) cached = MAXC;
+  }
+  (void)cudaGetLastError();
+  return cached;
 }
 
 }  // namespace
 
-// Test / tuning hook: force the cluster size (0 = automatic).
-static int g_force_cluster = 0;
+// Test / tuning hooks: force the cluster size and the CTA size (0 = automatic).
 extern "C" void b200_fps_set_cluster(int c) { g_force_cluster = c; }
+extern "C" void b200_fps_set_threads(int t) { g_force_threads = t; }
+#ifdef FPS_PROFILE
+extern "C" int b200_fps_read_profile(unsigned long long *out5) {
+  return (int)cudaMemcpyFromSymbol(out5, g_fps_prof, 6 * sizeof(unsigned long long));
+}
+#endif
 
 extern "C" int b200_furthest_point_sampling(const float *xyz, int b, int n, int m, int32_t *idx,
                                             void *stream) {
@@ -193,19 +525,41 @@ extern "C" int b200_furthest_point_sampling(const float *xyz, int b, int n, int 
   int bs = 1, bits = 0;
   while (bs * 2 <= n && bs < 512) { bs *= 2; ++bits; }
 
-  // cluster size: as many CTAs per cloud as keep >= 2048 points per CTA, at most 8,
-  // and no more than what lets every cloud of the batch be resident at once.
-  int C = 1;
-  const int sms = b200_sm_count();
-  while (C < 8 && n / (C * 2) >= 2048 && (long long)b * (C * 2) <= sms) C *= 2;
-  while (ceil_div(ceil_div(n, C), NT) > 24 && C < MAXC) C *= 2;   // capacity: 24 points/thread
-  if (g_force_cluster > 0) C = g_force_cluster;
-  int chunk = ceil_div(ceil_div(n, C), 512) * 512;
-  const int ppt = chunk / NT;
-  if (ppt > 24) return B200_ECAPACITY;
-#define FPS_CASE(P) if (ppt <= P) return launch<P>(xyz, b, n, m, C, chunk, bits, idx, st);
-  FPS_CASE(1) FPS_CASE(2) FPS_CASE(3) FPS_CASE(4) FPS_CASE(5) FPS_CASE(6) FPS_CASE(8)
-  FPS_CASE(10) FPS_CASE(12) FPS_CASE(16) FPS_CASE(20) FPS_CASE(24)
+  int C = 1, NT = 512;
+  if (bits == 9) {
+    // Per-step cost on B200 (tools/fps_prof.py): ~9 cycles per 128 points of a CTA's share plus
+    // an exchange of ~340 cycles alone, ~520 in a cluster of 2-4, ~720 in a cluster of 8 and
+    // >1000 in a cluster of 16 (message fan-in).  So: one CTA up to ~3k points, 4 CTAs up to
+    // ~22k, 8 beyond -- but never more CTAs than let every cloud of the batch be resident.
+    const int sms = b200_sm_count();
+    int want = n <= 3072 ? 1 : n <= 22528 ? 4 : 8;
+    while (want > 1 && (long long)b * want > sms) want /= 2;
+    if (g_force_cluster > 0) want = g_force_cluster;
+    NT = 128;
+    if (g_force_threads == 128 || g_force_threads == 256 || g_force_threads == 512) NT = g_force_threads;
+    const int cmax = NT == 128 ? max_cluster<128>() : NT == 256 ? max_cluster<256>() : max_cluster<512>();
+    C = want > cmax ? cmax : want;
+    if (g_force_threads == 0) {
+      // automatic CTA size: the smallest that holds a CTA's share in registers
+      const int share = ceil_div(ceil_div(n, C), 512) * 512;
+      NT = share <= 128 * 48 ? 128 : share <= 256 * 48 ? 256 : 512;
+    }
+    while (C > 1 && C * (NT / 32) > 128) C /= 2;               // at most 4 entries per lane
+    // capacity: grow the cluster until a CTA's share fits the largest register tile
+    while (C < cmax && C * 2 * (NT / 32) <= 128 &&
+           round_ppt(ceil_div(ceil_div(n, C), 512) * 512 / NT, NT) == 0) C *= 2;
+  }
+  const int blocks = ceil_div(ceil_div(n, C), 512);            // 512-blocks per CTA
+  const int ppt = round_ppt(blocks * 512 / NT, NT);
+  if (ppt == 0) return B200_ECAPACITY;
+#define FPS_CASE(P, T) if (NT == T && ppt == P) return launch_et<P / 2, T>(xyz, b, n, m, C, bits, idx, st);
+  FPS_CASE(2, 512) FPS_CASE(4, 512) FPS_CASE(6, 512) FPS_CASE(8, 512) FPS_CASE(10, 512) FPS_CASE(12, 512)
+  FPS_CASE(16, 512) FPS_CASE(20, 512) FPS_CASE(24, 512)
+  FPS_CASE(2, 256) FPS_CASE(4, 256) FPS_CASE(6, 256) FPS_CASE(8, 256) FPS_CASE(10, 256) FPS_CASE(12, 256)
+  FPS_CASE(16, 256) FPS_CASE(20, 256) FPS_CASE(24, 256) FPS_CASE(32, 256) FPS_CASE(40, 256) FPS_CASE(48, 256)
+  FPS_CASE(52, 256)
+  FPS_CASE(4, 128) FPS_CASE(8, 128) FPS_CASE(12, 128) FPS_CASE(16, 128) FPS_CASE(20, 128) FPS_CASE(24, 128)
+  FPS_CASE(32, 128) FPS_CASE(40, 128) FPS_CASE(48, 128)
 #undef FPS_CASE
   return B200_ECAPACITY;
 }
