@@ -48,6 +48,8 @@ lib.b200_fps_set_cluster.argtypes = [_i]
 lib.b200_fps_set_cluster.restype = None
 lib.b200_fps_set_threads.argtypes = [_i]
 lib.b200_fps_set_threads.restype = None
+lib.b200_fps_set_speculation.argtypes = [_i]
+lib.b200_fps_set_speculation.restype = None
 
 EXPORTS = sorted(list(SIGNATURES) + ["b200_grasp_nms_workspace", "b200_error_string", "b200_version"])
 

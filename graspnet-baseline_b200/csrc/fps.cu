@@ -154,7 +154,7 @@ constexpr int TAB_LIMIT = 200 * 1024;   // bytes of shared memory the per-CTA po
 // ET > 0: cluster of C CTAs, C * NW <= 32 * ET entries, ET per lane in the select stage.
 template <int PP, int NT, int ET>
 __global__ void __launch_bounds__(NT, 1)
-fps_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, int32_t *__restrict__ idx) {
+fps_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, int spec, int32_t *idx) {
   constexpr bool CLUSTER = ET > 0;
   constexpr int PPT = 2 * PP;
   constexpr int NW = NT / 32;
@@ -181,6 +181,14 @@ fps_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, int32_t
   int32_t *out = idx + (size_t)cloud * m;
   const int E = C * NW;                            // entries published per step
   const int base = rank * (PPT * NT);
+  // Speculative mode: the prefix-check kernels below left out[0] == 0 iff the answer is the
+  // identity permutation (the input is already in furthest-point order); then nothing is left
+  // to do but write it.  The test is uniform over the cluster, so every CTA leaves together.
+  if (spec && out[0] == 0) {
+    if (rank == 0)
+      for (int j = tid; j < m; j += NT) out[j] = j;
+    return;
+  }
 #ifdef FPS_PROFILE
   unsigned long long prof[6] = {0, 0, 0, 0, 0, 0};
   const bool prof_on = (blockIdx.x == 0 && tid == 0);
@@ -421,7 +429,7 @@ fps_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, int32_t
 }
 
 template <int PP, int NT, int ET>
-int launch(const float *xyz, int b, int n, int m, int C, int bits, int32_t *idx, cudaStream_t st) {
+int launch(const float *xyz, int b, int n, int m, int C, int bits, int spec, int32_t *idx, cudaStream_t st) {
   constexpr int tab_bytes = (2 * PP * NT * 16 <= TAB_LIMIT) ? 2 * PP * NT * 16 : 0;
   auto kern = fps_kernel<PP, NT, ET>;
   static bool configured = false;                  // per instantiation
@@ -432,7 +440,7 @@ int launch(const float *xyz, int b, int n, int m, int C, int bits, int32_t *idx,
     configured = true;
   }
   if (ET == 0) {
-    kern<<<b, NT, tab_bytes, st>>>(xyz, n, m, 1, bits, idx);
+    kern<<<b, NT, tab_bytes, st>>>(xyz, n, m, 1, bits, spec, idx);
     B200_LAUNCH_CHECK();
     return 0;
   }
@@ -448,18 +456,98 @@ int launch(const float *xyz, int b, int n, int m, int C, int bits, int32_t *idx,
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  B200_CUDA(cudaLaunchKernelEx(&cfg, kern, xyz, n, m, C, bits, idx));
+  B200_CUDA(cudaLaunchKernelEx(&cfg, kern, xyz, n, m, C, bits, spec, idx));
   return 0;
 }
 
 template <int PP, int NT>
-int launch_et(const float *xyz, int b, int n, int m, int C, int bits, int32_t *idx, cudaStream_t st) {
+int launch_et(const float *xyz, int b, int n, int m, int C, int bits, int spec, int32_t *idx, cudaStream_t st) {
   const int E = C * (NT / 32);
-  if (C == 1) return launch<PP, NT, 0>(xyz, b, n, m, C, bits, idx, st);
-  if (E <= 32) return launch<PP, NT, 1>(xyz, b, n, m, C, bits, idx, st);
-  if (E <= 64) return launch<PP, NT, 2>(xyz, b, n, m, C, bits, idx, st);
-  if (E <= 128) return launch<PP, NT, 4>(xyz, b, n, m, C, bits, idx, st);
+  if (C == 1) return launch<PP, NT, 0>(xyz, b, n, m, C, bits, spec, idx, st);
+  if (E <= 32) return launch<PP, NT, 1>(xyz, b, n, m, C, bits, spec, idx, st);
+  if (E <= 64) return launch<PP, NT, 2>(xyz, b, n, m, C, bits, spec, idx, st);
+  if (E <= 128) return launch<PP, NT, 4>(xyz, b, n, m, C, bits, spec, idx, st);
   return B200_ECAPACITY;
+}
+
+// ---------------------------------------------------------------------------------------
+// Speculative prefix check.  PointNet++ feeds SA2..SA4 the points SA1's FPS chose, in the
+// order it chose them (reference models/backbone.py:110-119), and FPS over an FPS-ordered
+// prefix returns 0,1,2,... -- unless a tie or the skip rule says otherwise.  Whether the
+// identity IS the legacy answer can be decided without the serial chain: it is iff for
+// every step j, point j beats every other point under (min-distance to points 0..j-1, tie
+// priority).  Two flat kernels decide it (n*m + m*m/2 distance evaluations, no step-to-step
+// synchronisation); the chain kernel then only runs when the check failed.  No scratch: the
+// check keeps D_j (bits of point j's min-distance at step j) in idx[j] and its verdict in
+// idx[0] (0 = identity holds, -1 = run the chain).
+constexpr int SPEC_NT = 128;
+constexpr int SPEC_MAX_M = 2048;       // prefix length the check supports (32 KB of shared memory)
+constexpr int SPEC_MAX_N = 4096;
+
+// D_j = min(1e10, min_{i<j} |p_j - p_i|^2) for 1 <= j < m, thread per j.
+__global__ void __launch_bounds__(SPEC_NT)
+fps_prefix_dist_kernel(const float *__restrict__ xyz, int n, int m, int32_t *__restrict__ idx) {
+  __shared__ float4 tile[SPEC_NT];
+  const int cloud = blockIdx.y;
+  const float *p = xyz + (size_t)cloud * n * 3;
+  int32_t *out = idx + (size_t)cloud * m;
+  const int j = blockIdx.x * SPEC_NT + threadIdx.x;
+  const bool active = j < m;
+  float x = 0.f, y = 0.f, z = 0.f;
+  if (active) { x = __ldg(p + 3 * (size_t)j); y = __ldg(p + 3 * (size_t)j + 1); z = __ldg(p + 3 * (size_t)j + 2); }
+  float md = 1e10f;
+  const int jmax = min(m, (int)(blockIdx.x + 1) * SPEC_NT);     // i < j <= jmax - 1
+  for (int i0 = 0; i0 < jmax; i0 += SPEC_NT) {
+    const int i = i0 + threadIdx.x;
+    __syncthreads();
+    if (i < m) tile[threadIdx.x] = make_float4(__ldg(p + 3 * (size_t)i), __ldg(p + 3 * (size_t)i + 1),
+                                               __ldg(p + 3 * (size_t)i + 2), 0.f);
+    __syncthreads();
+    const int cnt = min(SPEC_NT, j - i0);                       // only i < j
+#pragma unroll 4
+    for (int t = 0; t < cnt; ++t) {
+      const float4 c = tile[t];
+      md = fminf(sq3_p2(__fsub_rn(x, c.x), __fsub_rn(y, c.y), __fsub_rn(z, c.z)), md);
+    }
+  }
+  if (!active) return;
+  if (j == 0) { out[0] = 0; return; }                           // verdict starts as "identity holds"
+  out[j] = __float_as_int(md);
+}
+
+// Thread per point k: running min-distance against points 0..j-1, compared with D_j at every
+// step j.  A violation (k would have been picked instead of j) or a skipped j clears the verdict.
+__global__ void __launch_bounds__(SPEC_NT)
+fps_prefix_check_kernel(const float *__restrict__ xyz, int n, int m, int bits, int32_t *idx) {
+  __shared__ float4 sel[SPEC_MAX_M];                            // x, y, z of point j, D_j in .w
+  const int cloud = blockIdx.y;
+  const float *p = xyz + (size_t)cloud * n * 3;
+  int32_t *out = idx + (size_t)cloud * m;
+  bool bad = false;
+  for (int j = threadIdx.x; j < m; j += SPEC_NT) {
+    const float a = __ldg(p + 3 * (size_t)j), b = __ldg(p + 3 * (size_t)j + 1), c = __ldg(p + 3 * (size_t)j + 2);
+    sel[j] = make_float4(a, b, c, j ? __int_as_float(out[j]) : 0.f);
+    if (j && (double)sq3_p2(a, b, c) <= 1e-3) bad = true;       // a skipped point is never picked
+  }
+  __syncthreads();
+  const int k = blockIdx.x * SPEC_NT + threadIdx.x;
+  if (k < n && !bad) {
+    const float x = __ldg(p + 3 * (size_t)k), y = __ldg(p + 3 * (size_t)k + 1), z = __ldg(p + 3 * (size_t)k + 2);
+    if (!((double)sq3_p2(x, y, z) <= 1e-3)) {                   // skipped points never compete
+      const unsigned pk = prio_of(k, bits);
+      float md = 1e10f;
+      float4 prev = sel[0];
+      for (int j = 1; j < m; ++j) {
+        md = fminf(sq3_p2(__fsub_rn(x, prev.x), __fsub_rn(y, prev.y), __fsub_rn(z, prev.z)), md);
+        const float4 cur = sel[j];
+        if (md >= cur.w && k != j) {                            // rare: decide with the tie priority
+          if (md > cur.w || pk < prio_of(j, bits)) { bad = true; break; }
+        }
+        prev = cur;
+      }
+    }
+  }
+  if (bad) out[0] = -1;
 }
 
 // smallest supported points-per-thread >= want (0 if none)
@@ -477,7 +565,7 @@ int round_ppt(int want, int nt) {
   return 0;
 }
 
-int g_force_cluster = 0, g_force_threads = 0;
+int g_force_cluster = 0, g_force_threads = 0, g_spec_enabled = 1;
 
 // Largest cluster size the device will co-schedule for this kernel family (16 needs the
 // non-portable opt-in and a GPC with 16 free SMs; fall back to the portable 8).
@@ -510,6 +598,7 @@ int max_cluster() {
 // Test / tuning hooks: force the cluster size and the CTA size (0 = automatic).
 extern "C" void b200_fps_set_cluster(int c) { g_force_cluster = c; }
 extern "C" void b200_fps_set_threads(int t) { g_force_threads = t; }
+extern "C" void b200_fps_set_speculation(int on) { g_spec_enabled = on; }
 #ifdef FPS_PROFILE
 extern "C" int b200_fps_read_profile(unsigned long long *out5) {
   return (int)cudaMemcpyFromSymbol(out5, g_fps_prof, 6 * sizeof(unsigned long long));
@@ -552,7 +641,15 @@ extern "C" int b200_furthest_point_sampling(const float *xyz, int b, int n, int 
   const int blocks = ceil_div(ceil_div(n, C), 512);            // 512-blocks per CTA
   const int ppt = round_ppt(blocks * 512 / NT, NT);
   if (ppt == 0) return B200_ECAPACITY;
-#define FPS_CASE(P, T) if (NT == T && ppt == P) return launch_et<P / 2, T>(xyz, b, n, m, C, bits, idx, st);
+  // small clouds may be FPS-ordered already (SA2..SA4): decide that first, flat and parallel
+  const int spec = (g_spec_enabled && m >= 2 && m <= n && m <= SPEC_MAX_M && n <= SPEC_MAX_N && b <= 65535) ? 1 : 0;
+  if (spec) {
+    fps_prefix_dist_kernel<<<dim3((unsigned)ceil_div(m, SPEC_NT), (unsigned)b), SPEC_NT, 0, st>>>(xyz, n, m, idx);
+    B200_LAUNCH_CHECK();
+    fps_prefix_check_kernel<<<dim3((unsigned)ceil_div(n, SPEC_NT), (unsigned)b), SPEC_NT, 0, st>>>(xyz, n, m, bits, idx);
+    B200_LAUNCH_CHECK();
+  }
+#define FPS_CASE(P, T) if (NT == T && ppt == P) return launch_et<P / 2, T>(xyz, b, n, m, C, bits, spec, idx, st);
   FPS_CASE(2, 512) FPS_CASE(4, 512) FPS_CASE(6, 512) FPS_CASE(8, 512) FPS_CASE(10, 512) FPS_CASE(12, 512)
   FPS_CASE(16, 512) FPS_CASE(20, 512) FPS_CASE(24, 512)
   FPS_CASE(2, 256) FPS_CASE(4, 256) FPS_CASE(6, 256) FPS_CASE(8, 256) FPS_CASE(10, 256) FPS_CASE(12, 256)

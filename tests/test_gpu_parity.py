@@ -52,6 +52,29 @@ def test_fps_all_skipped_and_more_samples_than_points(b200, oracle_mod):
     assert (got == oracle_mod.furthest_point_sampling(y, 80)).all()
 
 
+@pytest.mark.parametrize("kind,n0,n,m", [("table", 20000, 2048, 1024), ("adv", 20000, 2048, 1024), ("table", 6000, 1024, 512),
+                                         ("adv", 3000, 512, 256), ("adv", 900, 300, 300), ("table", 4000, 4096, 2048)])
+def test_fps_on_fps_ordered_prefix(b200, oracle_mod, kind, n0, n, m):
+    """SA2..SA4 inputs: the points a previous FPS chose, in that order (backbone.py:110-119).  The
+    speculative identity check must agree with the chain (and with the oracle) whether it holds or not."""
+    x0 = clouds(b200, 2, max(n0, n), kind, 77)
+    first = oracle_mod.furthest_point_sampling(x0, n)
+    x = np.stack([x0[i][first[i]] for i in range(2)])
+    x[1] = x[1][::-1]                                        # second cloud: not a prefix at all
+    x = np.ascontiguousarray(x)
+    want = oracle_mod.furthest_point_sampling(x, m)
+    got = b200.ops.furthest_point_sampling(dev(x), m).cpu().numpy()
+    assert (got == want).all()
+    if kind == "table":
+        assert (got[0] == np.arange(m)).all()                # no ties on a generic cloud: identity
+    b200._abi.lib.b200_fps_set_speculation(0)
+    try:
+        chain = b200.ops.furthest_point_sampling(dev(x), m).cpu().numpy()
+    finally:
+        b200._abi.lib.b200_fps_set_speculation(1)
+    assert (chain == want).all()
+
+
 # ------------------------------------------------------------------ queries
 
 @pytest.mark.parametrize("b,n,m,r,ns,kind", [
