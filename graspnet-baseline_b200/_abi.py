@@ -44,6 +44,7 @@ lib.b200_grasp_nms_workspace.restype = _sz
 lib.b200_error_string.argtypes = [_i]
 lib.b200_error_string.restype = ctypes.c_char_p
 lib.b200_version.restype = _i
+lib.b200_launch_count.restype = ctypes.c_ulonglong
 lib.b200_fps_set_cluster.argtypes = [_i]
 lib.b200_fps_set_cluster.restype = None
 lib.b200_fps_set_threads.argtypes = [_i]
@@ -51,7 +52,7 @@ lib.b200_fps_set_threads.restype = None
 lib.b200_fps_set_speculation.argtypes = [_i]
 lib.b200_fps_set_speculation.restype = None
 
-EXPORTS = sorted(list(SIGNATURES) + ["b200_grasp_nms_workspace", "b200_error_string", "b200_version"])
+EXPORTS = sorted(list(SIGNATURES) + ["b200_grasp_nms_workspace", "b200_error_string", "b200_version", "b200_launch_count"])
 
 
 def check(code, what):

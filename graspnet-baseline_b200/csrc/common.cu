@@ -14,6 +14,10 @@ int b200_sm_count() {
   return sms;
 }
 
+unsigned long long g_b200_launches = 0;
+
+extern "C" unsigned long long b200_launch_count(void) { return g_b200_launches; }
+
 extern "C" int b200_version(void) { return 100; }
 
 extern "C" const char *b200_error_string(int code) {

@@ -5,10 +5,14 @@
 
 #include "../../include/b200grasp.h"
 
+// number of kernels this library has launched in this process (bench.py's gpu_launches)
+extern unsigned long long g_b200_launches;
+
 #define B200_LAUNCH_CHECK()                         \
   do {                                              \
     cudaError_t e__ = cudaGetLastError();           \
     if (e__ != cudaSuccess) return (int)e__;        \
+    ++g_b200_launches;                              \
   } while (0)
 
 #define B200_CUDA(call)                             \

@@ -457,6 +457,7 @@ int launch(const float *xyz, int b, int n, int m, int C, int bits, int spec, int
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   B200_CUDA(cudaLaunchKernelEx(&cfg, kern, xyz, n, m, C, bits, spec, idx));
+  ++g_b200_launches;
   return 0;
 }
 

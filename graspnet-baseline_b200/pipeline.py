@@ -36,6 +36,10 @@ class GeometryScene:
         self.launches = 0
         self.glue = 0
         self.timer = None
+        self._graph = None
+        self._graph_out = None
+        self._graph_launches = 0
+        self._streams = None
         g = torch.Generator(device="cpu").manual_seed(seed)
         # stand-ins for MLP outputs (resident, never regenerated)
         self.feat = {}
@@ -88,7 +92,102 @@ class GeometryScene:
         self.timer.append((name, e0, e1))
         return r
 
-    # ---- one pass
+    # ---- one pass, as a CUDA graph over several streams
+    def run_graph(self):
+        """One pass as a single graph launch.  The pass is captured once: the FPS chain of the four SA
+        levels (which only ever occupies a cluster's worth of SMs) runs on its own stream and every
+        other op starts on a side stream as soon as the level it needs exists, so the pass costs
+        about the FPS chain instead of the sum of all kernels.  Inputs (self.cloud, self.rot,
+        self.grasps, ...) are static device buffers: refresh them with copy_() and replay."""
+        if self._graph is None:
+            side = torch.cuda.Stream(device=self.dev)
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):              # lazy one-time setup must not be captured
+                self.run_streams()
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            from . import _abi
+            n0 = _abi.lib.b200_launch_count()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._graph_out = self.run_streams()
+            self._graph_launches = int(_abi.lib.b200_launch_count() - n0)
+            self._graph = g
+        self._graph.replay()
+        self.launches = self._graph_launches
+        return self._graph_out
+
+    def run_streams(self):
+        """The same ops as run(), forked over streams by data dependence (joins back before returning)."""
+        main = torch.cuda.current_stream()
+        if self._streams is None:
+            self._streams = [torch.cuda.Stream(device=self.dev) for _ in range(4)]
+        s_q, s_c, s_f, s_p = self._streams
+
+        def after(stream, *deps):
+            for d in deps:
+                stream.wait_stream(d)
+
+        out = {}
+        B = self.B
+        # every temporary stays referenced until the streams have joined: a block freed on the
+        # stream that allocated it could otherwise be handed out again while a side stream still reads it
+        hold = []
+        after(s_p, main)
+        with torch.cuda.stream(s_p):                  # post-processing: independent of the backbone
+            counts, keeps = [], []
+            for s in range(B):
+                T, R, thr = self.coll_in[s]
+                counts.append(ops.collision_counts(self.scene64[s], T, R, thr))
+                keeps.append(ops.grasp_nms(self.grasps[s], 0.03, math.cos(30.0 / 180.0 * math.pi)))
+            out["collision_counts"], out["nms"] = counts, keeps
+        after(s_c, main)
+        with torch.cuda.stream(s_c):
+            cloud_t = self.cloud.transpose(1, 2).contiguous()
+        xyz, xyz_t = self.cloud, None
+        for lvl, (npoint, radius, nsample, cin) in enumerate(self.sa_cfg):
+            name = "sa%d" % (lvl + 1)
+            # main stream = the serial chain: FPS -> gather -> next level's FPS
+            inds = ops.furthest_point_sampling(xyz, npoint)
+            if xyz_t is None:
+                xyz_t = xyz.transpose(1, 2).contiguous()
+            new_xyz_t = ops.gather_points(xyz_t, inds)
+            new_xyz = new_xyz_t.transpose(1, 2).contiguous()
+            hold += [xyz_t, new_xyz_t]
+            out[name + "_inds"], out[name + "_xyz"] = inds, new_xyz
+            after(s_q, main)
+            with torch.cuda.stream(s_q):              # neighbourhood queries + grouping of this level
+                idx = ops.ball_query(new_xyz, xyz, radius, nsample)
+                out[name + "_idx"] = idx
+                out[name + "_grouped_xyz"] = ops.group_points(xyz_t, idx)
+                if cin:
+                    out[name + "_grouped_feat"] = ops.group_points(self.feat[name + "_in"], idx)
+            if lvl == 1:                              # seeds exist: CloudCrop's cylinder queries
+                after(s_c, main)
+                with torch.cuda.stream(s_c):
+                    rot9 = self.rot.view(B, -1, 9)
+                    cidx = ops.cylinder_query_multi(new_xyz, self.cloud, rot9, CYL["radius"], CYL["hmin"],
+                                                    CYL["hmax_list"], CYL["nsample"])
+                    out["crop_idx"] = cidx
+                    cat = cidx.permute(1, 0, 2, 3).reshape(B, cidx.shape[0] * cidx.shape[2], cidx.shape[3])
+                    if B > 1:
+                        cat = cat.contiguous()
+                    hold += [cat, cloud_t]
+                    out["crop_grouped_xyz"] = ops.group_points(cloud_t, cat)
+            xyz, xyz_t = new_xyz, new_xyz_t
+        after(s_f, main)
+        with torch.cuda.stream(s_f):                  # feature propagation
+            for name, unknown, known in (("fp1", out["sa3_xyz"], out["sa4_xyz"]), ("fp2", out["sa2_xyz"], out["sa3_xyz"])):
+                d2, idx3 = ops.three_nn(unknown, known)
+                w = torch.full_like(d2, 1.0 / 3.0)
+                hold += [d2, w]
+                out[name + "_idx"] = idx3
+                out[name + "_interp"] = ops.three_interpolate(self.feat[name + "_known"], idx3, w)
+        after(main, s_q, s_c, s_f, s_p)
+        self._hold = hold
+        return out
+
+    # ---- one pass, one stream
     def run(self):
         out = self.run_geometry()
         L = self.launches

@@ -36,6 +36,8 @@ extern "C" {
 
 int b200_version(void);
 const char *b200_error_string(int code);
+/* Number of kernels the library has launched so far in this process (diagnostic). */
+unsigned long long b200_launch_count(void);
 
 /* Replaces furthest_point_sampling(points[B,N,3], nsamples) -> [B,nsamples] i32
  * (pointnet2/_ext_src/src/sampling.cpp:70-91, include/sampling.h:11; kernel
