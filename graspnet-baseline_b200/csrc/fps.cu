@@ -482,42 +482,43 @@ int launch_et(const float *xyz, int b, int n, int m, int C, int bits, int spec, 
 // check keeps D_j (bits of point j's min-distance at step j) in idx[j] and its verdict in
 // idx[0] (0 = identity holds, -1 = run the chain).
 constexpr int SPEC_NT = 128;
+constexpr int SPEC_SUB = 8;            // lanes cooperating on one point
+constexpr int SPEC_PTS = SPEC_NT / SPEC_SUB;
 constexpr int SPEC_MAX_M = 2048;       // prefix length the check supports (32 KB of shared memory)
 constexpr int SPEC_MAX_N = 4096;
 
-// D_j = min(1e10, min_{i<j} |p_j - p_i|^2) for 1 <= j < m, thread per j.
+// D_j = min(1e10, min_{i<j} |p_j - p_i|^2) for 1 <= j < m.  Eight lanes per j, each takes every
+// eighth i; min is order-independent, so the result equals the chain's running minimum.
 __global__ void __launch_bounds__(SPEC_NT)
 fps_prefix_dist_kernel(const float *__restrict__ xyz, int n, int m, int32_t *__restrict__ idx) {
-  __shared__ float4 tile[SPEC_NT];
+  __shared__ float4 sel[SPEC_MAX_M];
   const int cloud = blockIdx.y;
   const float *p = xyz + (size_t)cloud * n * 3;
   int32_t *out = idx + (size_t)cloud * m;
-  const int j = blockIdx.x * SPEC_NT + threadIdx.x;
-  const bool active = j < m;
-  float x = 0.f, y = 0.f, z = 0.f;
-  if (active) { x = __ldg(p + 3 * (size_t)j); y = __ldg(p + 3 * (size_t)j + 1); z = __ldg(p + 3 * (size_t)j + 2); }
+  const int sub = threadIdx.x & (SPEC_SUB - 1);
+  const int j = blockIdx.x * SPEC_PTS + (threadIdx.x >> 3);
+  const int jhi = min(m, (int)(blockIdx.x + 1) * SPEC_PTS);     // this CTA needs points i < jhi - 1
+  for (int i = threadIdx.x; i < jhi; i += SPEC_NT)
+    sel[i] = make_float4(__ldg(p + 3 * (size_t)i), __ldg(p + 3 * (size_t)i + 1), __ldg(p + 3 * (size_t)i + 2), 0.f);
+  __syncthreads();
   float md = 1e10f;
-  const int jmax = min(m, (int)(blockIdx.x + 1) * SPEC_NT);     // i < j <= jmax - 1
-  for (int i0 = 0; i0 < jmax; i0 += SPEC_NT) {
-    const int i = i0 + threadIdx.x;
-    __syncthreads();
-    if (i < m) tile[threadIdx.x] = make_float4(__ldg(p + 3 * (size_t)i), __ldg(p + 3 * (size_t)i + 1),
-                                               __ldg(p + 3 * (size_t)i + 2), 0.f);
-    __syncthreads();
-    const int cnt = min(SPEC_NT, j - i0);                       // only i < j
+  if (j < m) {
+    const float4 q = sel[j];
 #pragma unroll 4
-    for (int t = 0; t < cnt; ++t) {
-      const float4 c = tile[t];
-      md = fminf(sq3_p2(__fsub_rn(x, c.x), __fsub_rn(y, c.y), __fsub_rn(z, c.z)), md);
+    for (int i = sub; i < j; i += SPEC_SUB) {
+      const float4 c = sel[i];
+      md = fminf(sq3_p2(__fsub_rn(q.x, c.x), __fsub_rn(q.y, c.y), __fsub_rn(q.z, c.z)), md);
     }
   }
-  if (!active) return;
-  if (j == 0) { out[0] = 0; return; }                           // verdict starts as "identity holds"
-  out[j] = __float_as_int(md);
+#pragma unroll
+  for (int o = SPEC_SUB / 2; o >= 1; o >>= 1) md = fminf(md, __shfl_xor_sync(0xffffffffu, md, o));
+  if (j < m && sub == 0) out[j] = j ? __float_as_int(md) : 0;   // idx[0] = verdict, starts as "identity holds"
 }
 
-// Thread per point k: running min-distance against points 0..j-1, compared with D_j at every
-// step j.  A violation (k would have been picked instead of j) or a skipped j clears the verdict.
+// Eight lanes per point k, each owning a contiguous range of steps j.  Pass 1: minimum of the
+// distances in the lane's range; an exclusive prefix-min over the eight lanes gives the running
+// min-distance at the start of each range; pass 2 walks the range again comparing with D_j.
+// A violation (k would have been picked instead of j) or a skipped j clears the verdict.
 __global__ void __launch_bounds__(SPEC_NT)
 fps_prefix_check_kernel(const float *__restrict__ xyz, int n, int m, int bits, int32_t *idx) {
   __shared__ float4 sel[SPEC_MAX_M];                            // x, y, z of point j, D_j in .w
@@ -531,20 +532,39 @@ fps_prefix_check_kernel(const float *__restrict__ xyz, int n, int m, int bits, i
     if (j && (double)sq3_p2(a, b, c) <= 1e-3) bad = true;       // a skipped point is never picked
   }
   __syncthreads();
-  const int k = blockIdx.x * SPEC_NT + threadIdx.x;
-  if (k < n && !bad) {
-    const float x = __ldg(p + 3 * (size_t)k), y = __ldg(p + 3 * (size_t)k + 1), z = __ldg(p + 3 * (size_t)k + 2);
-    if (!((double)sq3_p2(x, y, z) <= 1e-3)) {                   // skipped points never compete
-      const unsigned pk = prio_of(k, bits);
-      float md = 1e10f;
-      float4 prev = sel[0];
-      for (int j = 1; j < m; ++j) {
-        md = fminf(sq3_p2(__fsub_rn(x, prev.x), __fsub_rn(y, prev.y), __fsub_rn(z, prev.z)), md);
-        const float4 cur = sel[j];
-        if (md >= cur.w && k != j) {                            // rare: decide with the tie priority
-          if (md > cur.w || pk < prio_of(j, bits)) { bad = true; break; }
-        }
-        prev = cur;
+  const int sub = threadIdx.x & (SPEC_SUB - 1);
+  const int k = blockIdx.x * SPEC_PTS + (threadIdx.x >> 3);
+  const int len = (m - 1 + SPEC_SUB - 1) / SPEC_SUB;            // steps per lane
+  const int j0 = 1 + sub * len, j1 = min(m, j0 + len);
+  float x = 0.f, y = 0.f, z = 0.f;
+  bool live = false;
+  if (k < n) {
+    x = __ldg(p + 3 * (size_t)k); y = __ldg(p + 3 * (size_t)k + 1); z = __ldg(p + 3 * (size_t)k + 2);
+    live = !((double)sq3_p2(x, y, z) <= 1e-3);                  // skipped points never compete
+  }
+  float mn = 1e10f;
+#pragma unroll 4
+  for (int j = j0; j < j1; ++j) {
+    const float4 c = sel[j - 1];
+    mn = fminf(sq3_p2(__fsub_rn(x, c.x), __fsub_rn(y, c.y), __fsub_rn(z, c.z)), mn);
+  }
+  // exclusive prefix-min over the 8 lanes of the group
+  float run = mn;
+#pragma unroll
+  for (int o = 1; o < SPEC_SUB; o <<= 1) {
+    const float t = __shfl_up_sync(0xffffffffu, run, o, SPEC_SUB);
+    if (sub >= o) run = fminf(run, t);
+  }
+  float md = __shfl_up_sync(0xffffffffu, run, 1, SPEC_SUB);
+  if (sub == 0) md = 1e10f;
+  if (live && !bad) {
+    const unsigned pk = prio_of(k, bits);
+    for (int j = j0; j < j1; ++j) {
+      const float4 c = sel[j - 1];
+      md = fminf(sq3_p2(__fsub_rn(x, c.x), __fsub_rn(y, c.y), __fsub_rn(z, c.z)), md);
+      const float dj = sel[j].w;
+      if (md >= dj && k != j) {                                 // rare: decide with the tie priority
+        if (md > dj || pk < prio_of(j, bits)) { bad = true; break; }
       }
     }
   }
@@ -645,9 +665,9 @@ extern "C" int b200_furthest_point_sampling(const float *xyz, int b, int n, int 
   // small clouds may be FPS-ordered already (SA2..SA4): decide that first, flat and parallel
   const int spec = (g_spec_enabled && m >= 2 && m <= n && m <= SPEC_MAX_M && n <= SPEC_MAX_N && b <= 65535) ? 1 : 0;
   if (spec) {
-    fps_prefix_dist_kernel<<<dim3((unsigned)ceil_div(m, SPEC_NT), (unsigned)b), SPEC_NT, 0, st>>>(xyz, n, m, idx);
+    fps_prefix_dist_kernel<<<dim3((unsigned)ceil_div(m, SPEC_PTS), (unsigned)b), SPEC_NT, 0, st>>>(xyz, n, m, idx);
     B200_LAUNCH_CHECK();
-    fps_prefix_check_kernel<<<dim3((unsigned)ceil_div(n, SPEC_NT), (unsigned)b), SPEC_NT, 0, st>>>(xyz, n, m, bits, idx);
+    fps_prefix_check_kernel<<<dim3((unsigned)ceil_div(n, SPEC_PTS), (unsigned)b), SPEC_NT, 0, st>>>(xyz, n, m, bits, idx);
     B200_LAUNCH_CHECK();
   }
 #define FPS_CASE(P, T) if (NT == T && ppt == P) return launch_et<P / 2, T>(xyz, b, n, m, C, bits, spec, idx, st);

@@ -36,9 +36,8 @@ class GeometryScene:
         self.launches = 0
         self.glue = 0
         self.timer = None
-        self._graph = None
-        self._graph_out = None
-        self._graph_launches = 0
+        self._graphs = {}
+        self._hold = None
         self._streams = None
         g = torch.Generator(device="cpu").manual_seed(seed)
         # stand-ins for MLP outputs (resident, never regenerated)
@@ -93,31 +92,31 @@ class GeometryScene:
         return r
 
     # ---- one pass, as a CUDA graph over several streams
-    def run_graph(self):
+    def run_graph(self, post=True):
         """One pass as a single graph launch.  The pass is captured once: the FPS chain of the four SA
         levels (which only ever occupies a cluster's worth of SMs) runs on its own stream and every
         other op starts on a side stream as soon as the level it needs exists, so the pass costs
         about the FPS chain instead of the sum of all kernels.  Inputs (self.cloud, self.rot,
         self.grasps, ...) are static device buffers: refresh them with copy_() and replay."""
-        if self._graph is None:
+        if post not in self._graphs:
             side = torch.cuda.Stream(device=self.dev)
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):              # lazy one-time setup must not be captured
-                self.run_streams()
+                self.run_streams(post)
             torch.cuda.current_stream().wait_stream(side)
             torch.cuda.synchronize()
             from . import _abi
             n0 = _abi.lib.b200_launch_count()
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
-                self._graph_out = self.run_streams()
-            self._graph_launches = int(_abi.lib.b200_launch_count() - n0)
-            self._graph = g
-        self._graph.replay()
-        self.launches = self._graph_launches
-        return self._graph_out
+                out = self.run_streams(post)
+            self._graphs[post] = (g, out, int(_abi.lib.b200_launch_count() - n0), self._hold)
+        g, out, nl, _ = self._graphs[post]
+        g.replay()
+        self.launches = nl
+        return out
 
-    def run_streams(self):
+    def run_streams(self, post=True):
         """The same ops as run(), forked over streams by data dependence (joins back before returning)."""
         main = torch.cuda.current_stream()
         if self._streams is None:
@@ -136,11 +135,12 @@ class GeometryScene:
         after(s_p, main)
         with torch.cuda.stream(s_p):                  # post-processing: independent of the backbone
             counts, keeps = [], []
-            for s in range(B):
+            for s in range(B if post else 0):
                 T, R, thr = self.coll_in[s]
                 counts.append(ops.collision_counts(self.scene64[s], T, R, thr))
                 keeps.append(ops.grasp_nms(self.grasps[s], 0.03, math.cos(30.0 / 180.0 * math.pi)))
-            out["collision_counts"], out["nms"] = counts, keeps
+            if post:
+                out["collision_counts"], out["nms"] = counts, keeps
         after(s_c, main)
         with torch.cuda.stream(s_c):
             cloud_t = self.cloud.transpose(1, 2).contiguous()
