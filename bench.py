@@ -255,10 +255,8 @@ def run_ours(args, rank, world, local_rank):
             evs.append((e0, e1))
         barrier()
         ms = sum(a.elapsed_time(b) for a, b in evs)
-        t = torch.tensor([ms], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+        # whole job: MAX of the elapsed device time over ranks (each rank ran `steps` scenes of its own shard)
+        return b200grasp.sharding.whole_job_throughput(steps, ms, device=dev)[1]
 
     sc.run_graph()                                          # capture (untimed, once)
     torch.cuda.synchronize()
