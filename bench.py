@@ -103,6 +103,8 @@ def host_inputs(batch, seed=1234):
 
 
 def time_cpu(steps, warmup):
+    # the C port is OpenMP-parallel; torchrun exports OMP_NUM_THREADS=1, which would make this a 1-thread run
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
     import oracle
     oracle.cpu.build()
     host = host_inputs(1)

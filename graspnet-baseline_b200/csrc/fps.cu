@@ -162,11 +162,16 @@ fps_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, int spe
   constexpr int PPR = PPT / R;
   constexpr bool TAB = PPT * NT * 16 <= TAB_LIMIT;
   constexpr bool SOLO = !CLUSTER && TAB;           // one CTA: winner by a shared-memory 64-bit max
+  // cluster alternative: CTA winner as in SOLO, then ONE entry per CTA.  Measured on B200 it ties the flat
+  // per-warp exchange (442 ns/step at C=16 vs 434 at C=8: the wait is straggler-bound, not message-bound)
+  // while occupying twice the SMs, so it is compiled out.
+  constexpr bool HIER = false && CLUSTER && TAB;
+  constexpr bool WSLOT = SOLO || HIER;
   static_assert(PPT % R == 0 && PPR >= 1, "PPT must cover whole 512-blocks");
   // slot i of a thread: local point number OFF(i) + tid, tie-priority PRI(i) + prio0
 #define OFF(i) (((i) % PPR) * 512 + NT * brev_small((i) / PPR, R))
 #define PRI(i) (((unsigned)((i) / PPR) << 22) + (unsigned)((i) % PPR))
-#define CODE(i) ((TAB && !SOLO) ? (unsigned)OFF(i) : PRI(i))
+#define CODE(i) ((TAB && !WSLOT) ? (unsigned)OFF(i) : PRI(i))
   extern __shared__ float4 tab[];                  // TAB: x, y, z, prio of every point of the chunk
   __shared__ __align__(16) int4 ent[2][MAXE];      // key, prio, x, y
   __shared__ float entz[2][MAXE];
@@ -179,7 +184,7 @@ fps_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, int spe
   const int cloud = CLUSTER ? (int)(blockIdx.x / C) : (int)blockIdx.x;
   const float *p = xyz + (size_t)cloud * n * 3;
   int32_t *out = idx + (size_t)cloud * m;
-  const int E = C * NW;                            // entries published per step
+  const int E = HIER ? C : C * NW;                 // entries published per step
   const int base = rank * (PPT * NT);
   // Speculative mode: the prefix-check kernels below left out[0] == 0 iff the answer is the
   // identity permutation (the input is already in furthest-point order); then nothing is left
@@ -226,7 +231,7 @@ fps_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, int spe
 
   float ox = __ldg(p), oy = __ldg(p + 1), oz = __ldg(p + 2);
   if (rank == 0 && tid == 0) out[0] = 0;
-  if (SOLO) {
+  if (WSLOT) {
     if (tid < 3 * NW) wslot[tid / NW][tid % NW] = make_int2(0, (int)0x80000000);
     __syncthreads();                               // table and slots written
   }
@@ -245,8 +250,9 @@ fps_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, int spe
       mbar_arrive_expect_tx(bar_local + 8, (uint32_t)E * ENT_BYTES);
     }
     const uint32_t peer = (uint32_t)(lane < C ? lane : 0);
-    ent_remote = map_to_rank(smem_u32(&ent[0][rank * NW + warp]), peer);
-    z_remote = map_to_rank(smem_u32(&entz[0][rank * NW + warp]), peer);
+    const int e_mine = HIER ? rank : rank * NW + warp;
+    ent_remote = map_to_rank(smem_u32(&ent[0][e_mine]), peer);
+    z_remote = map_to_rank(smem_u32(&entz[0][e_mine]), peer);
     bar_remote = map_to_rank(bar_local, peer);
     cluster_sync_all();                            // barriers initialised before any peer sends
   }
@@ -272,7 +278,7 @@ fps_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, int spe
       if (m1 > best) { best = m1; bc = CODE(2 * j + 1); }
     }
     FPS_TICK(0, __float_as_uint(best));
-    if (SOLO) {
+    if (WSLOT) {
       // ---- one CTA: per warp, lane 0 stores the warp's maximum key and the lanes holding it
       // post ~prio with a native 32-bit shared max (no unique owner needed); after the barrier
       // everybody takes the signed 64-bit max {key, ~prio} over the warps and looks the
@@ -305,16 +311,32 @@ fps_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, int spe
       }
       cur = nxt;
       FPS_TICK(3, (unsigned)v);
-      int sel = 0;
-      if (v >= 0) {
-        sel = index_of(~(unsigned)v, bits);
-        const float4 t = tab[sel];
-        ox = t.x; oy = t.y; oz = t.z;
-      }  // else: every point is skipped -> legacy yields index 0 and nothing is ever updated
-      FPS_TICK(4, __float_as_uint(ox));
-      if (tid == 0) out[s + 1] = sel;
-      continue;
+      if (SOLO) {
+        int sel = 0;
+        if (v >= 0) {
+          sel = index_of(~(unsigned)v, bits);
+          const float4 t = tab[sel];
+          ox = t.x; oy = t.y; oz = t.z;
+        }  // else: every point is skipped -> legacy yields index 0 and nothing is ever updated
+        FPS_TICK(4, __float_as_uint(ox));
+        if (tid == 0) out[s + 1] = sel;
+        continue;
+      }
+      // HIER: warp 0 looks the CTA winner's coordinates up and pushes ONE entry into every CTA
+      if (warp == 0) {
+        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+        unsigned cprio = 0xffffffffu;
+        if (v >= 0) {
+          cprio = ~(unsigned)v;
+          t = tab[index_of(cprio, bits) - base];
+        }
+        if (lane < C) {
+          st_async_v4(ent_remote + par * (MAXE * 16), (int)(v >> 32), cprio, t.x, t.y, bar_remote + par * 8);
+          st_async_b32(z_remote + par * (MAXE * 4), t.z, bar_remote + par * 8);
+        }
+      }
     }
+    if (!HIER) {
     // ---- this thread's candidate: coordinates and tie priority
     float cx = 0.f, cy = 0.f, cz = 0.f;
     unsigned cprio;
@@ -350,16 +372,20 @@ fps_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, int spe
         st_async_v4(ent_remote + par * (MAXE * 16), wkey, wprio, sx, sy, bar_remote + par * 8);
         st_async_b32(z_remote + par * (MAXE * 4), sz, bar_remote + par * 8);
       }
+    } else {
+      if (lane == 0) {
+        ent[par][warp] = make_int4(wkey, (int)wprio, __float_as_int(sx), __float_as_int(sy));
+        entz[par][warp] = sz;
+      }
+    }
+    }  // !HIER
+    if (CLUSTER) {
       FPS_TICK(2, s);
       mbar_wait(bar_local + par * 8, (uint32_t)(s >> 1) & 1u);
       // re-arm this buffer for step s+2; peers cannot complete it before every warp of this
       // CTA has published step s+1, which happens after this point in program order
       if (tid == 0 && s + 3 < m) mbar_arrive_expect_tx(bar_local + par * 8, (uint32_t)E * ENT_BYTES);
     } else {
-      if (lane == 0) {
-        ent[par][warp] = make_int4(wkey, (int)wprio, __float_as_int(sx), __float_as_int(sy));
-        entz[par][warp] = sz;
-      }
       FPS_TICK(2, s);
       __syncthreads();
     }
@@ -639,10 +665,10 @@ extern "C" int b200_furthest_point_sampling(const float *xyz, int b, int n, int 
   if (bits == 9) {
     // Per-step cost on B200 (tools/fps_prof.py): ~9 cycles per 128 points of a CTA's share plus
     // an exchange of ~340 cycles alone, ~520 in a cluster of 2-4, ~720 in a cluster of 8 and
-    // >1000 in a cluster of 16 (message fan-in).  So: one CTA up to ~3k points, 4 CTAs up to
-    // ~22k, 8 beyond -- but never more CTAs than let every cloud of the batch be resident.
+    // >1000 in a cluster of 16 (stragglers).  So: one CTA up to ~3k points, 4 CTAs up to
+    // ~12k, 8 beyond -- but never more CTAs than let every cloud of the batch be resident.
     const int sms = b200_sm_count();
-    int want = n <= 3072 ? 1 : n <= 22528 ? 4 : 8;
+    int want = n <= 3072 ? 1 : n <= 12288 ? 4 : 8;
     while (want > 1 && (long long)b * want > sms) want /= 2;
     if (g_force_cluster > 0) want = g_force_cluster;
     NT = 128;

@@ -126,10 +126,130 @@ query_kernel(const float *__restrict__ new_xyz, const float *__restrict__ xyz,
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// Segmented variant for large clouds.  One warp per centre leaves a 1024-centre query with
+// ~7 warps per SM, each walking the whole cloud alone (latency-bound).  Here a CTA handles
+// CPB centres x SEG contiguous point segments (one warp each): every warp collects the
+// first nsample hits of ITS segment into shared memory, then the lists are concatenated in
+// segment order -- the same "first nsample hits in index order" result with SEG x the
+// parallelism.  A warp stops when its own lists are full or when the segments before it
+// have already filled them.
+constexpr int SEG = 4;            // point segments per centre
+constexpr int CPB = QW / SEG;     // centres per CTA
+constexpr int TPS = 512;          // points per segment tile (6 KB each)
+constexpr int MAXNS = 64;         // list length the shared-memory lists are sized for
+
+template <class Pred, int NH, bool BALL>
+__global__ void __launch_bounds__(QT)
+query_seg_kernel(const float *__restrict__ new_xyz, const float *__restrict__ xyz,
+                 const float *__restrict__ rot, int b, int n, int m, float radius, float hmin,
+                 HList hmax, int nsample, int seglen, int32_t *__restrict__ idx) {
+  __shared__ float tile[SEG][TPS * 3];
+  __shared__ int hits[CPB][SEG][NH][MAXNS];
+  __shared__ int cnts[CPB][SEG][NH];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int c = warp / SEG, seg = warp % SEG;
+  const int groups_per_batch = (m + CPB - 1) / CPB;
+  const int bi = blockIdx.x / groups_per_batch;
+  const int j = (blockIdx.x % groups_per_batch) * CPB + c;
+  const bool active = j < m;
+  const float *pts = xyz + (size_t)bi * n * 3;
+  if (tid < CPB * SEG * NH) (&cnts[0][0][0])[tid] = 0;
+
+  Pred pred;
+  if (active)
+    pred.init(new_xyz + ((size_t)bi * m + j) * 3, BALL ? nullptr : rot + ((size_t)bi * m + j) * 9, radius, hmin);
+  int cnt[NH];
+#pragma unroll
+  for (int h = 0; h < NH; ++h) cnt[h] = 0;
+  const int s0 = seg * seglen, s1 = min(n, s0 + seglen);        // this warp's points
+  bool done = !active || s0 >= s1;
+
+  for (int t0 = 0; t0 < seglen; t0 += TPS) {
+    __syncthreads();                                            // previous tile consumed, counts visible
+    // segments before this one may already have filled every list
+    if (!done) {
+      bool need = false;
+#pragma unroll
+      for (int h = 0; h < NH; ++h) {
+        int before = 0;
+        for (int s = 0; s < seg; ++s) before += cnts[c][s][h];
+        if (before < nsample && cnt[h] < nsample) need = true;
+      }
+      if (!need) done = true;
+    }
+#pragma unroll
+    for (int s = 0; s < SEG; ++s) {
+      const int lo = s * seglen + t0, hi = min(n, min((s + 1) * seglen, lo + TPS));
+      const float *src = pts + (size_t)lo * 3;
+      for (int i = tid; i < (hi - lo) * 3; i += QT) tile[s][i] = __ldg(src + i);
+    }
+    __syncthreads();
+    if (!done) {
+      const int base = s0 + t0;
+      const int tn = min(TPS, s1 - base);
+      for (int i0 = 0; i0 < tn; i0 += 32) {
+        const int k = i0 + lane;
+        bool ok = false;
+        float hv = 0.f;
+        if (k < tn) ok = pred.test(tile[seg][3 * k], tile[seg][3 * k + 1], tile[seg][3 * k + 2], hv);
+        bool all_full = true;
+#pragma unroll
+        for (int h = 0; h < NH; ++h) {
+          if (cnt[h] < nsample) {                               // warp-uniform
+            const bool hit = BALL ? ok : (ok && hv < hmax.v[h]);
+            const unsigned bal = __ballot_sync(0xffffffffu, hit);
+            if (bal) {
+              const int pos = cnt[h] + __popc(bal & lanemask_lt());
+              if (hit && pos < nsample) hits[c][seg][h][pos] = base + k;
+              cnt[h] = min(nsample, cnt[h] + __popc(bal));
+            }
+            if (cnt[h] < nsample) all_full = false;
+          }
+        }
+        if (all_full) { done = true; break; }
+      }
+      if (lane < NH) {
+        int v = 0;
+#pragma unroll
+        for (int h = 0; h < NH; ++h) if (lane == h) v = cnt[h];
+        cnts[c][seg][lane] = v;
+      }
+    }
+    if (__syncthreads_and(done)) break;
+  }
+  __syncthreads();
+  // concatenate the segment lists in order; warp (c, seg) writes lists seg, seg+SEG, ...
+  if (active) {
+    const size_t list_stride = (size_t)b * m * nsample;
+    for (int h = seg; h < NH; h += SEG) {
+      int32_t *out = idx + h * list_stride + ((size_t)bi * m + j) * nsample;
+      int total = 0, first = 0;
+      bool any = false;
+      for (int s = 0; s < SEG && total < nsample; ++s) {
+        const int cs = min(cnts[c][s][h], nsample - total);
+        if (cs > 0 && !any) { any = true; first = hits[c][s][h][0]; }
+        for (int i = lane; i < cs; i += 32) out[total + i] = hits[c][s][h][i];
+        total += cs;
+      }
+      for (int i = total + lane; i < nsample; i += 32) out[i] = any ? first : 0;
+    }
+  }
+}
+
 template <class Pred, int NH, bool BALL>
 int launch_query(const float *new_xyz, const float *xyz, const float *rot, int b, int n, int m,
                  float radius, float hmin, const HList &hmax, int nsample, int32_t *idx,
                  cudaStream_t st) {
+  if (!BALL && n >= 4096 && nsample <= MAXNS) {   // (ball queries fill up early; segments would mostly be wasted)
+    const long long grid = (long long)b * ceil_div(m, CPB);
+    if (grid > 0x7fffffffLL) return B200_ECAPACITY;
+    const int seglen = ceil_div(ceil_div(n, SEG), 32) * 32;
+    query_seg_kernel<Pred, NH, BALL><<<(unsigned)grid, QT, 0, st>>>(new_xyz, xyz, rot, b, n, m, radius, hmin,
+                                                                    hmax, nsample, seglen, idx);
+    B200_LAUNCH_CHECK();
+    return 0;
+  }
   const long long grid = (long long)b * ceil_div(m, QW);
   if (grid > 0x7fffffffLL) return B200_ECAPACITY;
   query_kernel<Pred, NH, BALL><<<(unsigned)grid, QT, 0, st>>>(new_xyz, xyz, rot, b, n, m, radius,
