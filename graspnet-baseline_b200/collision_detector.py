@@ -11,7 +11,7 @@ import numpy as np
 import torch
 
 from . import ops as _ext
-from .voxel import voxel_down_sample
+from .voxel import voxel_down_sample_device
 
 
 class ModelFreeCollisionDetector():
@@ -20,9 +20,24 @@ class ModelFreeCollisionDetector():
         self.finger_length = 0.06
         self.voxel_size = voxel_size
         self.device = torch.device(device if device is not None else "cuda")
-        # open3d voxel_down_sample in the reference (:32-35)
-        self.scene_points = voxel_down_sample(np.asarray(scene_points), voxel_size)
-        self._scene_dev = torch.from_numpy(np.ascontiguousarray(self.scene_points, dtype=np.float64)).to(self.device)
+        # open3d voxel_down_sample in the reference (:32-35); here on the device, no host round trip:
+        # detect() reads the row count from device memory
+        self._scene_dev, self._nvox_dev = voxel_down_sample_device(scene_points, voxel_size, self.device)
+        self._scene_host = None
+
+    @property
+    def scene_points(self):
+        """(Nv,3) fp64 numpy, as the reference attribute (copied back on first use)."""
+        if self._scene_host is None:
+            n = self._scene_dev.shape[0] if self._nvox_dev is None else int(self._nvox_dev.item())
+            self._scene_host = self._scene_dev[:n].cpu().numpy()
+        return self._scene_host
+
+    @scene_points.setter
+    def scene_points(self, value):
+        self._scene_host = np.asarray(value, dtype=np.float64)
+        self._scene_dev = torch.from_numpy(np.ascontiguousarray(self._scene_host)).to(self.device)
+        self._nvox_dev = None
 
     def _thresholds(self, grasp_group, approach_dist):
         h = grasp_group.heights
@@ -36,12 +51,15 @@ class ModelFreeCollisionDetector():
     def detect(self, grasp_group, approach_dist=0.03, collision_thresh=0.05, return_empty_grasp=False,
                empty_thresh=0.01, return_ious=False):
         approach_dist = max(approach_dist, self.finger_width)
-        T = np.ascontiguousarray(grasp_group.translations, dtype=np.float64)
-        R = np.ascontiguousarray(grasp_group.rotation_matrices, dtype=np.float64).reshape(-1, 9)
-        thr = np.ascontiguousarray(self._thresholds(grasp_group, approach_dist))
-        dev = self.device
-        counts = _ext.collision_counts(self._scene_dev, torch.from_numpy(T).to(dev), torch.from_numpy(R).to(dev),
-                                       torch.from_numpy(thr).to(dev)).cpu().numpy().astype(np.int64)
+        m = len(grasp_group)
+        # one packed host buffer (T | R | thr) -> one H2D copy; one D2H copy of the integer counts
+        packed = np.empty((m, 22), dtype=np.float64)
+        packed[:, 0:3] = grasp_group.translations
+        packed[:, 3:12] = grasp_group.rotation_matrices.reshape(-1, 9)
+        packed[:, 12:22] = self._thresholds(grasp_group, approach_dist)
+        d = torch.from_numpy(packed).to(self.device, non_blocking=True)
+        T, R, thr = d[:, 0:3].contiguous(), d[:, 3:12].contiguous(), d[:, 12:22].contiguous()
+        counts = _ext.collision_counts(self._scene_dev, T, R, thr, self._nvox_dev).cpu().numpy().astype(np.int64)
         heights = grasp_group.heights[:, np.newaxis]
         widths = grasp_group.widths[:, np.newaxis]
         vox3 = self.voxel_size ** 3

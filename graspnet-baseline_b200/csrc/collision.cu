@@ -24,12 +24,14 @@ constexpr int CTH = 128;    // grasps per CTA (one per thread)
 constexpr int CPT = 1024;   // scene points per CTA slice (24 KB of fp64 xyz)
 
 __global__ void __launch_bounds__(CTH)
-collision_kernel(const double *__restrict__ scene, int n, const double *__restrict__ T,
-                 const double *__restrict__ R, const double *__restrict__ thr, int m,
-                 int32_t *__restrict__ counts) {
+collision_kernel(const double *__restrict__ scene, int n, const int32_t *__restrict__ n_dev,
+                 const double *__restrict__ T, const double *__restrict__ R,
+                 const double *__restrict__ thr, int m, int32_t *__restrict__ counts) {
   __shared__ double pts[CPT * 3];
+  if (n_dev) n = min(n, __ldg(n_dev));               // scene length produced on the device
   const int g = blockIdx.x * CTH + threadIdx.x;
   const int p0 = blockIdx.y * CPT;
+  if (p0 >= n) return;
   const int pn = min(CPT, n - p0);
   for (int i = threadIdx.x; i < pn * 3; i += CTH) pts[i] = __ldg(scene + (size_t)p0 * 3 + i);
   __syncthreads();
@@ -76,8 +78,23 @@ collision_kernel(const double *__restrict__ scene, int n, const double *__restri
 
 }  // namespace
 
+static int collision_launch(const double *scene, int n, const int32_t *n_dev, const double *T,
+                            const double *R, const double *thr, int m, int32_t *counts, void *stream);
+
 extern "C" int b200_collision_counts(const double *scene, int n, const double *T, const double *R,
                                      const double *thr, int m, int32_t *counts, void *stream) {
+  return collision_launch(scene, n, nullptr, T, R, thr, m, counts, stream);
+}
+
+extern "C" int b200_collision_counts_dn(const double *scene, const int32_t *n_dev, int n_max,
+                                        const double *T, const double *R, const double *thr, int m,
+                                        int32_t *counts, void *stream) {
+  if (!n_dev) return B200_EINVAL;
+  return collision_launch(scene, n_max, n_dev, T, R, thr, m, counts, stream);
+}
+
+static int collision_launch(const double *scene, int n, const int32_t *n_dev, const double *T,
+                            const double *R, const double *thr, int m, int32_t *counts, void *stream) {
   if (n < 0 || m < 0) return B200_EINVAL;
   if (m == 0) return 0;
   if (!counts) return B200_EINVAL;
@@ -87,7 +104,7 @@ extern "C" int b200_collision_counts(const double *scene, int n, const double *T
   if (!scene || !T || !R || !thr) return B200_EINVAL;
   if (ceil_div(n, CPT) > 65535) return B200_ECAPACITY;
   dim3 grid((unsigned)ceil_div(m, CTH), (unsigned)ceil_div(n, CPT));
-  collision_kernel<<<grid, CTH, 0, st>>>(scene, n, T, R, thr, m, counts);
+  collision_kernel<<<grid, CTH, 0, st>>>(scene, n, n_dev, T, R, thr, m, counts);
   B200_LAUNCH_CHECK();
   return 0;
 }

@@ -62,5 +62,6 @@ class GraspGroup:
         dev = torch.device(device if device is not None else "cuda")
         g = torch.from_numpy(np.ascontiguousarray(self.grasp_group_array, dtype=np.float32)).to(dev)
         keep, nkeep = _ext.grasp_nms(g, translation_thresh, math.cos(rotation_thresh))
-        rows = keep[: int(nkeep.item())].cpu().numpy()
+        both = torch.cat([nkeep, keep]).cpu().numpy()          # one D2H copy, one synchronisation
+        rows = both[1: 1 + int(both[0])]
         return GraspGroup(self.grasp_group_array[rows])

@@ -195,17 +195,38 @@ def knn(ref, query, idx):
     return 1
 
 
-def collision_counts(scene, T, R, thr):
+def collision_counts(scene, T, R, thr, n_dev=None):
     """scene (N,3) f64, T (M,3), R (M,9), thr (M,10) f64 -> counts (M,6) i32
-    [utils/collision_detector.py:75-100,119]"""
+    [utils/collision_detector.py:75-100,119].  n_dev: optional (1,) i32 device tensor holding the
+    number of valid scene rows (as written by voxel_down_sample), so no host round trip is needed."""
     for t, nm in ((scene, "scene"), (T, "T"), (R, "R"), (thr, "thr")):
         _chk(t, nm, torch.float64)
     n, m = scene.shape[0], T.shape[0]
     counts = torch.empty((m, 6), dtype=torch.int32, device=scene.device)
     with torch.cuda.device(scene.device):
-        _abi.check(_lib.b200_collision_counts(_ptr(scene), n, _ptr(T), _ptr(R), _ptr(thr), m, _ptr(counts),
-                                              _stream()), "collision_counts")
+        if n_dev is None:
+            _abi.check(_lib.b200_collision_counts(_ptr(scene), n, _ptr(T), _ptr(R), _ptr(thr), m, _ptr(counts),
+                                                  _stream()), "collision_counts")
+        else:
+            _chk(n_dev, "n_dev", torch.int32)
+            _abi.check(_lib.b200_collision_counts_dn(_ptr(scene), _ptr(n_dev), n, _ptr(T), _ptr(R), _ptr(thr), m,
+                                                     _ptr(counts), _stream()), "collision_counts_dn")
     return counts
+
+
+def voxel_down_sample(points, voxel_size):
+    """points (N,3) f64 -> (out (N,3) f64 of which the first nvox rows are valid, nvox (1,) i32), both on
+    the device   [utils/collision_detector.py:32-35 -> open3d voxel_down_sample, restated]"""
+    _chk(points, "points", torch.float64)
+    n = points.shape[0]
+    out = torch.empty((max(n, 1), 3), dtype=torch.float64, device=points.device)
+    nvox = torch.empty((1,), dtype=torch.int32, device=points.device)
+    nbytes = _lib.b200_voxel_down_sample_workspace(n)
+    ws = torch.empty((nbytes,), dtype=torch.uint8, device=points.device)
+    with torch.cuda.device(points.device):
+        _abi.check(_lib.b200_voxel_down_sample(_ptr(points), n, float(voxel_size), _ptr(out), _ptr(nvox), _ptr(ws),
+                                               nbytes, _stream()), "voxel_down_sample")
+    return out, nvox
 
 
 def grasp_nms(grasps, translation_thresh, cos_rotation_thresh):

@@ -57,7 +57,7 @@ class GeometryScene:
         nseed = self.sa_cfg[1][0]
         h["rot"] = np.stack([synth.seed_rotations(nseed, seed + s) for s in range(self.B)])
         h["grasps"] = [synth.synthetic_grasps(h["cloud"][s], self.M, seed + s) for s in range(self.B)]
-        h["scene64"] = [voxel_down_sample(h["cloud"][s].astype(np.float64), self.voxel_size) for s in range(self.B)]
+        h["scene64"] = [voxel_down_sample(h["cloud"][s], self.voxel_size, self.dev) for s in range(self.B)]
         return h
 
     def upload(self):

@@ -118,6 +118,19 @@ int b200_knn(const float *ref, const float *query, int b, int dim, int nr, int n
 int b200_collision_counts(const double *scene, int n, const double *T, const double *R,
                           const double *thr, int m, int32_t *counts, void *stream);
 
+/* Same, with the scene length read from DEVICE memory (*n_dev <= n_max) so the call can follow
+ * b200_voxel_down_sample without a host round trip. */
+int b200_collision_counts_dn(const double *scene, const int32_t *n_dev, int n_max, const double *T,
+                             const double *R, const double *thr, int m, int32_t *counts, void *stream);
+
+/* Voxel down-sample behind ModelFreeCollisionDetector.__init__ (utils/collision_detector.py:32-35 calls
+ * open3d's PointCloud.voxel_down_sample; restated, parity unpinned).  points[n,3] f64 -> out[<=n,3] f64
+ * (fp64 mean per occupied voxel, accumulated in point order, rows in ascending voxel-key order),
+ * *nvox (device int) = number of rows.  workspace: b200_voxel_down_sample_workspace(n) bytes. */
+size_t b200_voxel_down_sample_workspace(int n);
+int b200_voxel_down_sample(const double *points, int n, double voxel_size, double *out, int32_t *nvox,
+                           void *workspace, size_t workspace_bytes, void *stream);
+
 /* GraspGroup.nms (graspnetAPI -> grasp_nms.nms_grasp; call sites demo_pointcloud.py:249,
  * grasp_service.py:276).  grasps[M,17] f32; keep[M] i32 receives the surviving
  * row numbers in descending-score order, *nkeep (device int) their count.

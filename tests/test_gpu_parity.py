@@ -210,6 +210,20 @@ def test_collision_counts_bit_exact_at_size(b200, oracle_mod, n, m):
         assert (a == b).all()
 
 
+@pytest.mark.parametrize("n,voxel,kind", [(20000, 0.01, "table"), (200000, 0.005, "table"), (5000, 0.05, "adv"),
+                                          (1, 0.01, "table"), (777, 1e-5, "adv")])
+def test_voxel_down_sample_bit_exact(b200, oracle_mod, n, voxel, kind):
+    f = b200.synth.tabletop_cloud if kind == "table" else b200.synth.adversarial_cloud
+    p = f(n, 21)                                              # float32, as callers pass it
+    got = b200.voxel.voxel_down_sample(p, voxel)
+    want = oracle_mod.voxel_down_sample(p.astype(np.float64), voxel)
+    assert got.dtype == np.float64 and got.shape == want.shape and (got == want).all()
+    det = b200.ModelFreeCollisionDetector(p, voxel_size=voxel)
+    assert (det.scene_points == want).all()
+    again = b200.voxel.voxel_down_sample(got, voxel)         # idempotent up to re-binning: never more rows
+    assert len(again) <= len(got)
+
+
 @pytest.mark.parametrize("m,crowd", [(1024, 60), (4096, 300), (333, 10), (1, 1), (64, 1), (65, 2)])
 def test_nms_keep_set_bit_exact(b200, oracle_mod, m, crowd):
     scene = b200.synth.tabletop_cloud(3000, 2)

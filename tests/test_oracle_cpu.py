@@ -122,15 +122,18 @@ def test_nms_oracle_properties(oracle_mod):
     assert len(oracle_mod.grasp_nms(g, translation_thresh=0.0)) == 400
 
 
-def test_voxel_down_sample_host(oracle_mod):
-    import b200grasp
+def test_voxel_down_sample_oracle_properties(oracle_mod):
     p = np.random.default_rng(0).normal(size=(4000, 3))
-    a = b200grasp.voxel.voxel_down_sample(p, 0.25)
     b = oracle_mod.voxel_down_sample(p, 0.25)
-    assert a.shape == b.shape and (a == b).all()
-    one = b200grasp.voxel.voxel_down_sample(p[:1], 0.01)
+    assert b.dtype == np.float64 and 0 < len(b) < len(p)
+    # every output row is the mean of the points of one voxel: the count-weighted mean is preserved
+    origin = p.min(axis=0) - 0.125
+    key = np.floor((p - origin) / 0.25).astype(np.int64)
+    _, inv, cnt = np.unique(key, axis=0, return_inverse=True, return_counts=True)
+    assert len(cnt) == len(b)
+    assert np.allclose((b * cnt[:, None]).sum(0), p.sum(0), rtol=1e-12)
+    one = oracle_mod.voxel_down_sample(p[:1], 0.01)
     assert (one == p[:1]).all()
-
 
 def test_abi_exports_every_declared_symbol():
     hdr = open(os.path.join(ROOT, "include", "b200grasp.h")).read()
