@@ -312,6 +312,37 @@ def run_ours(args, rank, world, local_rank):
                           "FPS, gather, ball query, grouping, three_nn, three_interpolate, 4x cylinder query of one cfg2 scene",
                   "legacy_geometry_ms_per_scene": round(leg_ms, 4), "ours_geometry_ms_per_scene": round(geo_ms, 4),
                   "speedup": round(leg_ms / geo_ms, 2) if geo_ms > 0 else None}
+    # ---- config 3 shape: 64 scenes per graph launch on this GPU (throughput mode; extra, not the headline)
+    batch64 = None
+    if world == 1 and not args.no_batch64:
+        sc64 = GeometryScene(batch=64, num_point=20000, num_grasp=1024, seed=4321, device=dev)
+        sc64.run_graph()
+        torch.cuda.synchronize()
+        b_steps = 5
+        b_ms = timed(sc64.run_graph, b_steps, 3) / b_steps
+        batch64 = {"workload": "cfg3: 64 scenes of the cfg2 shape in one graph launch on one GPU",
+                   "ms_per_64_scenes": round(b_ms, 4), "scenes_per_s": round(64.0 / (b_ms * 1e-3), 1),
+                   "gpu_launches_per_step": sc64.launches}
+        per64 = {}
+        for _ in range(3):
+            flush.zero_()
+            sc64.timer = []
+            sc64.run()
+            torch.cuda.synchronize()
+            for name, e0, e1 in sc64.timer:
+                per64.setdefault(name, []).append(e0.elapsed_time(e1))
+            sc64.timer = None
+        rows = []
+        for name, v in per64.items():
+            if name in ("collision", "nms"):
+                continue                                    # per-scene launches, same as batch 1
+            ms = float(np.median(v))
+            ab = alg_bytes(name, B=64)
+            rows.append({"kernel": name, "ms": round(ms, 5), "alg_bytes": ab, "gbs": round(ab / (ms * 1e-3) / 1e9, 1)})
+        rows.sort(key=lambda k: -k["ms"])
+        batch64["kernels"] = rows[:12]
+        batch64["peak_gbs"] = peaks()[0]
+        del sc64
     # ---- per-kernel pass (rank 0): CUDA events around every launch, L2 flushed before each pass
     per = {}
     reps = 9
@@ -356,7 +387,7 @@ def run_ours(args, rank, world, local_rank):
             "clocks": clk, "gpu_launches": launches * args.steps,
             "e2e": {"value": round(e2e, 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h_box[0]), "ms_per_step": round(e2e_ms / args.steps, 4)},
-            "roofline": roof, "legacy_cuda": legacy, "kernels": kern}
+            "roofline": roof, "legacy_cuda": legacy, "batch64": batch64, "kernels": kern}
     return line
 
 
@@ -367,6 +398,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-batch64", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

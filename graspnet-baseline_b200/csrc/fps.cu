@@ -560,7 +560,9 @@ fps_prefix_check_kernel(const float *__restrict__ xyz, int n, int m, int bits, i
   __syncthreads();
   const int sub = threadIdx.x & (SPEC_SUB - 1);
   const int k = blockIdx.x * SPEC_PTS + (threadIdx.x >> 3);
-  const int len = (m - 1 + SPEC_SUB - 1) / SPEC_SUB;            // steps per lane
+  // steps per lane, rounded to an odd count: the 8 lanes of a group then read 8 different 16-byte
+  // bank groups (an even stride puts all of them on the same banks: 8-way conflict, measured 12x slower)
+  const int len = ((m - 1 + SPEC_SUB - 1) / SPEC_SUB) | 1;
   const int j0 = 1 + sub * len, j1 = min(m, j0 + len);
   float x = 0.f, y = 0.f, z = 0.f;
   bool live = false;

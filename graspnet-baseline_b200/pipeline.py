@@ -39,6 +39,7 @@ class GeometryScene:
         self._graphs = {}
         self._hold = None
         self._streams = None
+        self._post_streams = None
         g = torch.Generator(device="cpu").manual_seed(seed)
         # stand-ins for MLP outputs (resident, never regenerated)
         self.feat = {}
@@ -132,15 +133,20 @@ class GeometryScene:
         # every temporary stays referenced until the streams have joined: a block freed on the
         # stream that allocated it could otherwise be handed out again while a side stream still reads it
         hold = []
-        after(s_p, main)
-        with torch.cuda.stream(s_p):                  # post-processing: independent of the backbone
-            counts, keeps = [], []
-            for s in range(B if post else 0):
-                T, R, thr = self.coll_in[s]
-                counts.append(ops.collision_counts(self.scene64[s], T, R, thr))
-                keeps.append(ops.grasp_nms(self.grasps[s], 0.03, math.cos(30.0 / 180.0 * math.pi)))
-            if post:
-                out["collision_counts"], out["nms"] = counts, keeps
+        # post-processing: independent of the backbone; per-scene launches (the NMS sweep is a one-CTA
+        # serial chain) are dealt round-robin over a few streams so that scenes of a batch overlap
+        counts, keeps = [None] * B, [None] * B
+        if post:
+            if self._post_streams is None:
+                self._post_streams = [s_p] + [torch.cuda.Stream(device=self.dev) for _ in range(min(B, 8) - 1)]
+            for sp in self._post_streams:
+                after(sp, main)
+            for s in range(B):
+                with torch.cuda.stream(self._post_streams[s % len(self._post_streams)]):
+                    T, R, thr = self.coll_in[s]
+                    counts[s] = ops.collision_counts(self.scene64[s], T, R, thr)
+                    keeps[s] = ops.grasp_nms(self.grasps[s], 0.03, math.cos(30.0 / 180.0 * math.pi))
+            out["collision_counts"], out["nms"] = counts, keeps
         after(s_c, main)
         with torch.cuda.stream(s_c):
             cloud_t = self.cloud.transpose(1, 2).contiguous()
@@ -183,7 +189,7 @@ class GeometryScene:
                 hold += [d2, w]
                 out[name + "_idx"] = idx3
                 out[name + "_interp"] = ops.three_interpolate(self.feat[name + "_known"], idx3, w)
-        after(main, s_q, s_c, s_f, s_p)
+        after(main, s_q, s_c, s_f, *(self._post_streams if post else []))
         self._hold = hold
         return out
 
