@@ -678,14 +678,19 @@ extern "C" int b200_furthest_point_sampling(const float *xyz, int b, int n, int 
     const int cmax = NT == 128 ? max_cluster<128>() : NT == 256 ? max_cluster<256>() : max_cluster<512>();
     C = want > cmax ? cmax : want;
     if (g_force_threads == 0) {
-      // automatic CTA size: the smallest that holds a CTA's share in registers
-      const int share = ceil_div(ceil_div(n, C), 512) * 512;
-      NT = share <= 128 * 48 ? 128 : share <= 256 * 48 ? 256 : 512;
+      // automatic CTA size: the smallest that holds a CTA's share in registers; if the share does not
+      // fit (very large clouds), widen the cluster until some CTA size does
+      for (;; C *= 2) {
+        const int share = ceil_div(ceil_div(n, C), 512) * 512;
+        NT = share <= 128 * 48 ? 128 : share <= 256 * 52 ? 256 : 512;
+        const bool fits = round_ppt(share / NT, NT) != 0 && C * (NT / 32) <= 128;
+        if (fits || C * 2 > cmax) break;
+      }
+    } else {
+      while (C > 1 && C * (NT / 32) > 128) C /= 2;             // at most 4 entries per lane
+      while (C < cmax && C * 2 * (NT / 32) <= 128 &&
+             round_ppt(ceil_div(ceil_div(n, C), 512) * 512 / NT, NT) == 0) C *= 2;
     }
-    while (C > 1 && C * (NT / 32) > 128) C /= 2;               // at most 4 entries per lane
-    // capacity: grow the cluster until a CTA's share fits the largest register tile
-    while (C < cmax && C * 2 * (NT / 32) <= 128 &&
-           round_ppt(ceil_div(ceil_div(n, C), 512) * 512 / NT, NT) == 0) C *= 2;
   }
   const int blocks = ceil_div(ceil_div(n, C), 512);            // 512-blocks per CTA
   const int ppt = round_ppt(blocks * 512 / NT, NT);

@@ -97,6 +97,7 @@ query_kernel(const float *__restrict__ new_xyz, const float *__restrict__ xyz,
         bool ok = false;
         float hv = 0.f;
         if (k < tn) ok = pred.test(tile[3 * k], tile[3 * k + 1], tile[3 * k + 2], hv);
+        if (!__any_sync(0xffffffffu, ok)) continue;           // most 32-point groups hold no candidate at all
         bool all_full = true;
 #pragma unroll
         for (int h = 0; h < NH; ++h) {
@@ -193,6 +194,7 @@ query_seg_kernel(const float *__restrict__ new_xyz, const float *__restrict__ xy
         bool ok = false;
         float hv = 0.f;
         if (k < tn) ok = pred.test(tile[seg][3 * k], tile[seg][3 * k + 1], tile[seg][3 * k + 2], hv);
+        if (!__any_sync(0xffffffffu, ok)) continue;           // most 32-point groups hold no candidate at all
         bool all_full = true;
 #pragma unroll
         for (int h = 0; h < NH; ++h) {
