@@ -178,6 +178,7 @@ def alg_bytes(name, B=1, N=20000, M=1024, nscene=7000):
     if name == "cylinder_multi": return B * (N * 12 + 1024 * 12 + 1024 * 36 + 4 * 1024 * 64 * 4)
     if name.startswith("cylinder_"): return B * (N * 12 + 1024 * 12 + 1024 * 36 + 1024 * 64 * 4)
     if name == "group_xyz_crop": return B * (N * 12 + 4 * 1024 * 64 * 4 + 3 * 4 * 1024 * 64 * 4)
+    if name == "grid_build": return B * (N * 12 + N * 16)      # cloud in, binned {x,y,z,index} out
     if name == "collision": return nscene * 24 + M * (3 + 9 + 10) * 8 + M * 24
     if name == "nms": return M * 68 + M * 4 + 4
     return 0

@@ -36,6 +36,11 @@ SIGNATURES = {
     "b200_grasp_nms": [_vp, _i, _d, _d, _vp, _vp, _vp, _sz, _vp],
     "b200_collision_counts_dn": [_vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp],
     "b200_voxel_down_sample": [_vp, _i, _d, _vp, _vp, _vp, _sz, _vp],
+    "b200_ball_query_grid": [_vp, _vp, _i, _i, _i, _f, _i, _vp, _vp, _sz, _vp],
+    "b200_cylinder_query_multi_grid": [_vp, _vp, _vp, _i, _i, _i, _f, _f, ctypes.POINTER(_f), _i, _i, _vp, _vp, _sz, _vp],
+    "b200_query_grid_build": [_vp, _i, _i, _f, _vp, _sz, _vp],
+    "b200_ball_query_prebuilt": [_vp, _vp, _i, _i, _i, _f, _i, _vp, _vp, _sz, _vp],
+    "b200_cylinder_query_multi_prebuilt": [_vp, _vp, _vp, _i, _i, _i, _f, _f, ctypes.POINTER(_f), _i, _i, _vp, _vp, _sz, _vp],
 }
 for _name, _args in SIGNATURES.items():
     _fn = getattr(lib, _name)
@@ -45,6 +50,8 @@ lib.b200_grasp_nms_workspace.argtypes = [_i]
 lib.b200_grasp_nms_workspace.restype = _sz
 lib.b200_voxel_down_sample_workspace.argtypes = [_i]
 lib.b200_voxel_down_sample_workspace.restype = _sz
+lib.b200_query_grid_workspace.argtypes = [_i, _i]
+lib.b200_query_grid_workspace.restype = _sz
 lib.b200_error_string.argtypes = [_i]
 lib.b200_error_string.restype = ctypes.c_char_p
 lib.b200_version.restype = _i
@@ -53,10 +60,12 @@ lib.b200_fps_set_cluster.argtypes = [_i]
 lib.b200_fps_set_cluster.restype = None
 lib.b200_fps_set_threads.argtypes = [_i]
 lib.b200_fps_set_threads.restype = None
+lib.b200_query_grid_set_threads.argtypes = [_i]
+lib.b200_query_grid_set_threads.restype = None
 lib.b200_fps_set_speculation.argtypes = [_i]
 lib.b200_fps_set_speculation.restype = None
 
-EXPORTS = sorted(list(SIGNATURES) + ["b200_grasp_nms_workspace", "b200_voxel_down_sample_workspace", "b200_error_string", "b200_version", "b200_launch_count"])
+EXPORTS = sorted(list(SIGNATURES) + ["b200_grasp_nms_workspace", "b200_voxel_down_sample_workspace", "b200_query_grid_workspace", "b200_error_string", "b200_version", "b200_launch_count"])
 
 
 def check(code, what):

@@ -71,7 +71,40 @@ def gather_points_grad(grad_out, idx, n):
     return out
 
 
-def ball_query(new_xyz, xyz, radius, nsample):
+# Clouds of at least this many points are queried through the uniform grid (query_grid.cu); smaller ones by
+# the linear scan (query.cu).  Both give the same lists; tests flip this to compare them.
+GRID_QUERY_MIN_N = 4096
+
+
+class QueryGrid:
+    """A cloud binned by query_grid_build: pass it as `grid=` to ball_query / cylinder_query[_multi] on the
+    SAME xyz tensor to skip the binning (any cell edge gives the same lists)."""
+
+    def __init__(self, xyz, ws, nbytes):
+        self.ptr, self.shape, self.ws, self.nbytes = xyz.data_ptr(), tuple(xyz.shape), ws, nbytes
+
+    def check(self, xyz):
+        if xyz.data_ptr() != self.ptr or tuple(xyz.shape) != self.shape:
+            raise ValueError("b200grasp: this QueryGrid was built from another xyz tensor")
+
+
+def _grid_workspace(b, n, device):
+    nbytes = _lib.b200_query_grid_workspace(b, n)
+    return torch.empty((nbytes,), dtype=torch.uint8, device=device), nbytes
+
+
+def query_grid_build(xyz, cell):
+    """xyz (B,N,3) f32 -> QueryGrid with cell edge `cell` (grown by the library if the cloud is too wide)."""
+    _chk(xyz, "xyz", torch.float32)
+    b, n, _ = xyz.shape
+    ws, nbytes = _grid_workspace(b, n, xyz.device)
+    with torch.cuda.device(xyz.device):
+        _abi.check(_lib.b200_query_grid_build(_ptr(xyz), b, n, float(cell), _ptr(ws), nbytes, _stream()),
+                   "query_grid_build")
+    return QueryGrid(xyz, ws, nbytes)
+
+
+def ball_query(new_xyz, xyz, radius, nsample, grid=None):
     """new_xyz (B,M,3), xyz (B,N,3) -> (B,M,nsample) i32   [ball_query.cpp:13-37]"""
     _chk(new_xyz, "new_xyz", torch.float32)
     _chk(xyz, "xyz", torch.float32)
@@ -79,18 +112,30 @@ def ball_query(new_xyz, xyz, radius, nsample):
     n = xyz.shape[1]
     out = torch.empty((b, m, nsample), dtype=torch.int32, device=xyz.device)
     with torch.cuda.device(xyz.device):
-        _abi.check(_lib.b200_ball_query(_ptr(new_xyz), _ptr(xyz), b, n, m, float(radius), int(nsample),
-                                        _ptr(out), _stream()), "ball_query")
+        if grid is not None:
+            grid.check(xyz)
+            _abi.check(_lib.b200_ball_query_prebuilt(_ptr(new_xyz), _ptr(xyz), b, n, m, float(radius), int(nsample),
+                                                     _ptr(out), _ptr(grid.ws), grid.nbytes, _stream()),
+                       "ball_query_prebuilt")
+        elif n >= GRID_QUERY_MIN_N:
+            ws, nbytes = _grid_workspace(b, n, xyz.device)
+            _abi.check(_lib.b200_ball_query_grid(_ptr(new_xyz), _ptr(xyz), b, n, m, float(radius), int(nsample),
+                                                 _ptr(out), _ptr(ws), nbytes, _stream()), "ball_query_grid")
+        else:
+            _abi.check(_lib.b200_ball_query(_ptr(new_xyz), _ptr(xyz), b, n, m, float(radius), int(nsample),
+                                            _ptr(out), _stream()), "ball_query")
     return out
 
 
-def cylinder_query(new_xyz, xyz, rot, radius, hmin, hmax, nsample):
+def cylinder_query(new_xyz, xyz, rot, radius, hmin, hmax, nsample, grid=None):
     """new_xyz (B,M,3), xyz (B,N,3), rot (B,M,9) -> (B,M,nsample) i32   [cylinder_query.cpp:10-37]"""
     _chk(new_xyz, "new_xyz", torch.float32)
     _chk(xyz, "xyz", torch.float32)
     _chk(rot, "rot", torch.float32)
     b, m, _ = new_xyz.shape
     n = xyz.shape[1]
+    if grid is not None or n >= GRID_QUERY_MIN_N:
+        return cylinder_query_multi(new_xyz, xyz, rot, radius, hmin, [hmax], nsample, grid=grid)[0]
     out = torch.empty((b, m, nsample), dtype=torch.int32, device=xyz.device)
     with torch.cuda.device(xyz.device):
         _abi.check(_lib.b200_cylinder_query(_ptr(new_xyz), _ptr(xyz), _ptr(rot), b, n, m, float(radius),
@@ -99,7 +144,7 @@ def cylinder_query(new_xyz, xyz, rot, radius, hmin, hmax, nsample):
     return out
 
 
-def cylinder_query_multi(new_xyz, xyz, rot, radius, hmin, hmax_list, nsample):
+def cylinder_query_multi(new_xyz, xyz, rot, radius, hmin, hmax_list, nsample, grid=None):
     """One scan for all hmax of CloudCrop (models/modules.py:127-130) -> (H,B,M,nsample) i32."""
     _chk(new_xyz, "new_xyz", torch.float32)
     _chk(xyz, "xyz", torch.float32)
@@ -110,9 +155,22 @@ def cylinder_query_multi(new_xyz, xyz, rot, radius, hmin, hmax_list, nsample):
     hm = (ctypes.c_float * max(nh, 1))(*[float(h) for h in hmax_list])
     out = torch.empty((nh, b, m, nsample), dtype=torch.int32, device=xyz.device)
     with torch.cuda.device(xyz.device):
-        _abi.check(_lib.b200_cylinder_query_multi(_ptr(new_xyz), _ptr(xyz), _ptr(rot), b, n, m, float(radius),
-                                                  float(hmin), hm, nh, int(nsample), _ptr(out), _stream()),
-                   "cylinder_query_multi")
+        if grid is not None:
+            grid.check(xyz)
+            _abi.check(_lib.b200_cylinder_query_multi_prebuilt(_ptr(new_xyz), _ptr(xyz), _ptr(rot), b, n, m,
+                                                               float(radius), float(hmin), hm, nh, int(nsample),
+                                                               _ptr(out), _ptr(grid.ws), grid.nbytes, _stream()),
+                       "cylinder_query_multi_prebuilt")
+        elif n >= GRID_QUERY_MIN_N:
+            ws, nbytes = _grid_workspace(b, n, xyz.device)
+            _abi.check(_lib.b200_cylinder_query_multi_grid(_ptr(new_xyz), _ptr(xyz), _ptr(rot), b, n, m,
+                                                           float(radius), float(hmin), hm, nh, int(nsample),
+                                                           _ptr(out), _ptr(ws), nbytes, _stream()),
+                       "cylinder_query_multi_grid")
+        else:
+            _abi.check(_lib.b200_cylinder_query_multi(_ptr(new_xyz), _ptr(xyz), _ptr(rot), b, n, m, float(radius),
+                                                      float(hmin), hm, nh, int(nsample), _ptr(out), _stream()),
+                       "cylinder_query_multi")
     return out
 
 

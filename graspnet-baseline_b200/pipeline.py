@@ -20,6 +20,9 @@ from . import ops, synth
 # (npoint, radius, nsample, C_in features grouped at this level)  -- models/backbone.py:30-64
 SA_CFG = [(2048, 0.04, 64, 0), (1024, 0.1, 32, 128), (512, 0.2, 16, 256), (256, 0.3, 16, 256)]
 CYL = dict(radius=0.05, hmin=-0.02, hmax_list=[0.01, 0.02, 0.03, 0.04], nsample=64)   # models/graspnet.py:39,44
+# cell edge of the one uniform grid that serves SA1's ball query (bounding radius 0.04) and CloudCrop's cylinder
+# query (0.064); any value gives the same lists, 0.026 was the fastest of a sweep (profiles/r01_query_grid.txt)
+GRID_CELL = 0.026
 
 
 class GeometryScene:
@@ -81,13 +84,13 @@ class GeometryScene:
         return f(gg.translations), f(gg.rotation_matrices.reshape(-1, 9)), f(thr)
 
     # ---- optional per-op CUDA-event timing (bench.py's roofline pass)
-    def _op(self, name, fn, *args):
+    def _op(self, name, fn, *args, **kw):
         if self.timer is None:
-            return fn(*args)
+            return fn(*args, **kw)
         st = torch.cuda.current_stream()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(st)
-        r = fn(*args)
+        r = fn(*args, **kw)
         e1.record(st)
         self.timer.append((name, e0, e1))
         return r
@@ -150,6 +153,10 @@ class GeometryScene:
         after(s_c, main)
         with torch.cuda.stream(s_c):
             cloud_t = self.cloud.transpose(1, 2).contiguous()
+            # one binning of the full cloud serves SA1's ball query and CloudCrop's cylinder query; it runs
+            # while the main stream is busy with SA1's FPS
+            grid = ops.query_grid_build(self.cloud, GRID_CELL) if self.cloud.shape[1] >= ops.GRID_QUERY_MIN_N else None
+            hold.append(grid)
         xyz, xyz_t = self.cloud, None
         for lvl, (npoint, radius, nsample, cin) in enumerate(self.sa_cfg):
             name = "sa%d" % (lvl + 1)
@@ -161,9 +168,9 @@ class GeometryScene:
             new_xyz = new_xyz_t.transpose(1, 2).contiguous()
             hold += [xyz_t, new_xyz_t]
             out[name + "_inds"], out[name + "_xyz"] = inds, new_xyz
-            after(s_q, main)
+            after(s_q, main, *([s_c] if lvl == 0 else []))
             with torch.cuda.stream(s_q):              # neighbourhood queries + grouping of this level
-                idx = ops.ball_query(new_xyz, xyz, radius, nsample)
+                idx = ops.ball_query(new_xyz, xyz, radius, nsample, grid=grid if lvl == 0 else None)
                 out[name + "_idx"] = idx
                 out[name + "_grouped_xyz"] = ops.group_points(xyz_t, idx)
                 if cin:
@@ -173,7 +180,7 @@ class GeometryScene:
                 with torch.cuda.stream(s_c):
                     rot9 = self.rot.view(B, -1, 9)
                     cidx = ops.cylinder_query_multi(new_xyz, self.cloud, rot9, CYL["radius"], CYL["hmin"],
-                                                    CYL["hmax_list"], CYL["nsample"])
+                                                    CYL["hmax_list"], CYL["nsample"], grid=grid)
                     out["crop_idx"] = cidx
                     cat = cidx.permute(1, 0, 2, 3).reshape(B, cidx.shape[0] * cidx.shape[2], cidx.shape[3])
                     if B > 1:
@@ -211,11 +218,16 @@ class GeometryScene:
         out = {}
         L = 0
         xyz = self.cloud
+        grid = None
+        if self.cloud.shape[1] >= ops.GRID_QUERY_MIN_N:
+            grid = self._op('grid_build', ops.query_grid_build, self.cloud, GRID_CELL)
+            L += 4
         for lvl, (npoint, radius, nsample, cin) in enumerate(self.sa_cfg):
             xyz_t = xyz.transpose(1, 2).contiguous(); self.glue += 1
             inds = self._op('fps_sa%d' % (lvl + 1), ops.furthest_point_sampling, xyz, npoint)
             new_xyz = self._op('gather_sa%d' % (lvl + 1), ops.gather_points, xyz_t, inds).transpose(1, 2).contiguous(); self.glue += 1
-            idx = self._op('ball_sa%d' % (lvl + 1), ops.ball_query, new_xyz, xyz, radius, nsample)
+            idx = self._op('ball_sa%d' % (lvl + 1), ops.ball_query, new_xyz, xyz, radius, nsample,
+                           grid=grid if lvl == 0 else None)
             out["sa%d_grouped_xyz" % (lvl + 1)] = self._op('group_xyz_sa%d' % (lvl + 1), ops.group_points, xyz_t, idx)
             L += 4
             if cin:
@@ -235,11 +247,11 @@ class GeometryScene:
         cloud_t = self.cloud.transpose(1, 2).contiguous(); self.glue += 1
         if self.fused_cylinder:
             cidx = self._op('cylinder_multi', ops.cylinder_query_multi, seed_xyz, self.cloud, rot9, CYL["radius"],
-                            CYL["hmin"], CYL["hmax_list"], CYL["nsample"])
+                            CYL["hmin"], CYL["hmax_list"], CYL["nsample"], grid=grid)
             L += 1
         else:
             cidx = torch.stack([self._op('cylinder_%g' % h, ops.cylinder_query, seed_xyz, self.cloud, rot9, CYL["radius"],
-                                         CYL["hmin"], h, CYL["nsample"]) for h in CYL["hmax_list"]])
+                                         CYL["hmin"], h, CYL["nsample"], grid=grid) for h in CYL["hmax_list"]])
             L += len(CYL["hmax_list"]); self.glue += 1
         out["crop_idx"] = cidx
         nh = cidx.shape[0]

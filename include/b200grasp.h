@@ -77,6 +77,32 @@ int b200_cylinder_query_multi(const float *new_xyz, const float *xyz, const floa
                               int n, int m, float radius, float hmin, const float *hmax, int nh,
                               int nsample, int32_t *idx, void *stream);
 
+/* Grid-accelerated forms of b200_ball_query / b200_cylinder_query_multi: identical results (the first
+ * nsample hits IN INDEX ORDER, padded with the first hit, zeros if none), but the cloud is first binned
+ * into a uniform grid held in `workspace` (b200_query_grid_workspace(b, n) bytes of device memory, no
+ * alignment beyond cudaMalloc's) and each centre only visits the cells its bounding sphere touches.
+ * Inputs the grid cannot prune (non-finite radius, clouds of >= 2^24 points) and centres whose `rot` is
+ * not orthonormal are answered by the linear scan, so the result never depends on which form ran.
+ *   *_grid      : bin (cell edge = half the query's bounding radius), then query.
+ *   *_prebuilt  : query a grid that b200_query_grid_build made of the SAME xyz (b, n) earlier on the same
+ *                 stream order; any cell edge gives the same lists, only the speed differs.  This is how one
+ *                 binning serves SA1's ball query and CloudCrop's cylinder query (both read the full cloud,
+ *                 models/backbone.py:93, models/modules.py:127-130). */
+size_t b200_query_grid_workspace(int b, int n);
+int b200_query_grid_build(const float *xyz, int b, int n, float cell, void *workspace, size_t workspace_bytes,
+                          void *stream);
+int b200_ball_query_grid(const float *new_xyz, const float *xyz, int b, int n, int m, float radius,
+                         int nsample, int32_t *idx, void *workspace, size_t workspace_bytes, void *stream);
+int b200_ball_query_prebuilt(const float *new_xyz, const float *xyz, int b, int n, int m, float radius,
+                             int nsample, int32_t *idx, const void *grid, size_t grid_bytes, void *stream);
+int b200_cylinder_query_multi_grid(const float *new_xyz, const float *xyz, const float *rot, int b, int n,
+                                   int m, float radius, float hmin, const float *hmax, int nh, int nsample,
+                                   int32_t *idx, void *workspace, size_t workspace_bytes, void *stream);
+int b200_cylinder_query_multi_prebuilt(const float *new_xyz, const float *xyz, const float *rot, int b, int n,
+                                       int m, float radius, float hmin, const float *hmax, int nh,
+                                       int nsample, int32_t *idx, const void *grid, size_t grid_bytes,
+                                       void *stream);
+
 /* Replaces group_points(points[B,C,N], idx[B,M,ns]) -> [B,C,M,ns]
  * (group_points.cpp:17-40, group_points.h:9; group_points_gpu.cu:13-33). */
 int b200_group_points(const float *points, const int32_t *idx, int b, int c, int n, int m, int ns,
