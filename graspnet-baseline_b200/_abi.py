@@ -62,6 +62,8 @@ lib.b200_fps_set_threads.argtypes = [_i]
 lib.b200_fps_set_threads.restype = None
 lib.b200_query_grid_set_threads.argtypes = [_i]
 lib.b200_query_grid_set_threads.restype = None
+lib.b200_fps_set_multi.argtypes = [_i]
+lib.b200_fps_set_multi.restype = None
 lib.b200_fps_set_speculation.argtypes = [_i]
 lib.b200_fps_set_speculation.restype = None
 

@@ -56,7 +56,7 @@ def build(force=False, verbose=False):
 def build_fps_profile():
     """Instrumented FPS-only library (clock64 stage counters) for tools/fps_prof.py; not shipped."""
     out = os.path.join(HERE, "lib", "libb200fps_prof.so")
-    cmd = [NVCC, "-shared", "-o", out, os.path.join(CSRC, "fps.cu"), os.path.join(CSRC, "common.cu"),
+    cmd = [NVCC, "-shared", "-o", out, os.path.join(CSRC, "fps.cu"), os.path.join(CSRC, "fps_multi.cu"), os.path.join(CSRC, "common.cu"),
            "-DFPS_PROFILE"] + FLAGS
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode:

@@ -27,100 +27,9 @@
 // itself).  Distances use the legacy FMA association; the skip test `(double)mag <= 1e-3`
 // is done in fp64.
 #include "common.cuh"
+#include "fps_common.cuh"
 
 namespace {
-
-constexpr int MAXC = 16;       // largest cluster supported (non-portable size, opt-in)
-constexpr int MAXE = 256;      // published entries per step: C x warps-per-CTA
-constexpr int ENT_BYTES = 20;  // key, prio, x, y (16 B) + z (4 B)
-
-__device__ __forceinline__ unsigned prio_of(int k, int bits) {
-  const unsigned r = bits ? (__brev((unsigned)k) >> (32 - bits)) : 0u;  // bitrev of the low `bits` bits
-  return (r << 22) | ((unsigned)k >> bits);
-}
-__device__ __forceinline__ int index_of(unsigned prio, int bits) {
-  const unsigned r = prio >> 22;
-  const unsigned lo = bits ? (__brev(r) >> (32 - bits)) : 0u;
-  return (int)(((prio & 0x3fffffu) << bits) | lo);
-}
-
-// ---- cluster / mbarrier / st.async plumbing (PTX; shared::cluster addresses are 32-bit)
-__device__ __forceinline__ uint32_t smem_u32(const void *p) {
-  return (uint32_t)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ uint32_t map_to_rank(uint32_t addr, uint32_t rank) {
-  uint32_t r;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
-  return r;
-}
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-  uint32_t r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  do {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
-  } while (!ok);
-}
-__device__ __forceinline__ void st_async_v4(uint32_t addr, int a, unsigned b, float c, float d, uint32_t bar) {
-  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];"
-               ::"r"(addr), "r"(a), "r"(b), "r"(__float_as_uint(c)), "r"(__float_as_uint(d)), "r"(bar) : "memory");
-}
-__device__ __forceinline__ void st_async_b32(uint32_t addr, float v, uint32_t bar) {
-  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];"
-               ::"r"(addr), "r"(__float_as_uint(v)), "r"(bar) : "memory");
-}
-
-// order in which a thread visits its 512/NT residues (mod 512): ascending bit-reversed
-// priority, i.e. residue tid + NT * brev(r) with brev over log2(R) bits
-__host__ __device__ constexpr int brev_small(int r, int R) {
-  int out = 0;
-  for (int b = 1, o = R >> 1; b < R; b <<= 1, o >>= 1)
-    if (r & b) out |= o;
-  return out;
-}
-
-// ---- packed fp32x2 arithmetic (FADD2 / FMUL2 / FFMA2 on sm_100): two points per instruction,
-// each half rounded exactly like the scalar op, so the legacy association is preserved
-typedef unsigned long long f32x2;
-__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
-  f32x2 r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-  return r;
-}
-__device__ __forceinline__ void unpack2(f32x2 v, float &lo, float &hi) {
-  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
-}
-__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) {
-  f32x2 r;
-  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-  return r;
-}
-__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
-  f32x2 r;
-  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-  return r;
-}
-__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
-  f32x2 r;
-  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
-  return r;
-}
 
 #ifdef FPS_PROFILE
 // stage cycle counters of (cloud 0, rank 0, thread 0): compute, warp-reduce, publish, wait, select
@@ -614,7 +523,7 @@ int round_ppt(int want, int nt) {
   return 0;
 }
 
-int g_force_cluster = 0, g_force_threads = 0, g_spec_enabled = 1;
+int g_force_cluster = 0, g_force_threads = 0, g_spec_enabled = 1, g_multi_enabled = 1;
 
 // Largest cluster size the device will co-schedule for this kernel family (16 needs the
 // non-portable opt-in and a GPC with 16 free SMs; fall back to the portable 8).
@@ -648,6 +557,7 @@ int max_cluster() {
 extern "C" void b200_fps_set_cluster(int c) { g_force_cluster = c; }
 extern "C" void b200_fps_set_threads(int t) { g_force_threads = t; }
 extern "C" void b200_fps_set_speculation(int on) { g_spec_enabled = on; }
+extern "C" void b200_fps_set_multi(int on) { g_multi_enabled = on; }
 #ifdef FPS_PROFILE
 extern "C" int b200_fps_read_profile(unsigned long long *out5) {
   return (int)cudaMemcpyFromSymbol(out5, g_fps_prof, 6 * sizeof(unsigned long long));
@@ -671,6 +581,9 @@ extern "C" int b200_furthest_point_sampling(const float *xyz, int b, int n, int 
     // ~12k, 8 beyond -- but never more CTAs than let every cloud of the batch be resident.
     const int sms = b200_sm_count();
     int want = n <= 3072 ? 1 : n <= 12288 ? 4 : 8;
+    // fps_multi.cu pays the exchange once per ~6 samples, which moves the optimum to wider clusters
+    // (tools/fps_multi_sweep.py: 8 CTAs from ~3k points, 16 beyond ~16k)
+    if (g_multi_enabled) want = n <= 3072 ? 1 : (n <= 16384 || (long long)b * 16 > sms / 2) ? 8 : 16;
     while (want > 1 && (long long)b * want > sms) want /= 2;
     if (g_force_cluster > 0) want = g_force_cluster;
     NT = 128;
@@ -702,6 +615,10 @@ extern "C" int b200_furthest_point_sampling(const float *xyz, int b, int n, int 
     B200_LAUNCH_CHECK();
     fps_prefix_check_kernel<<<dim3((unsigned)ceil_div(n, SPEC_PTS), (unsigned)b), SPEC_NT, 0, st>>>(xyz, n, m, bits, idx);
     B200_LAUNCH_CHECK();
+  }
+  if (g_multi_enabled && C >= 2) {                              // several samples per exchange where covered
+    const int rc = b200_fps_multi_launch(xyz, b, n, m, C, NT, ppt, bits, spec, idx, st);
+    if (rc != B200_ECAPACITY) return rc;
   }
 #define FPS_CASE(P, T) if (NT == T && ppt == P) return launch_et<P / 2, T>(xyz, b, n, m, C, bits, spec, idx, st);
   FPS_CASE(2, 512) FPS_CASE(4, 512) FPS_CASE(6, 512) FPS_CASE(8, 512) FPS_CASE(10, 512) FPS_CASE(12, 512)

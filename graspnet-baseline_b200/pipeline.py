@@ -23,6 +23,7 @@ CYL = dict(radius=0.05, hmin=-0.02, hmax_list=[0.01, 0.02, 0.03, 0.04], nsample=
 # cell edge of the one uniform grid that serves SA1's ball query (bounding radius 0.04) and CloudCrop's cylinder
 # query (0.064); any value gives the same lists, 0.026 was the fastest of a sweep (profiles/r01_query_grid.txt)
 GRID_CELL = 0.026
+POST_STREAMS = 16         # streams the per-scene collision + NMS launches of a batch are spread over
 
 
 class GeometryScene:
@@ -141,7 +142,7 @@ class GeometryScene:
         counts, keeps = [None] * B, [None] * B
         if post:
             if self._post_streams is None:
-                self._post_streams = [s_p] + [torch.cuda.Stream(device=self.dev) for _ in range(min(B, 8) - 1)]
+                self._post_streams = [s_p] + [torch.cuda.Stream(device=self.dev) for _ in range(min(B, POST_STREAMS) - 1)]
             for sp in self._post_streams:
                 after(sp, main)
             for s in range(B):

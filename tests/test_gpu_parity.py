@@ -44,6 +44,45 @@ def test_fps_every_cluster_size_agrees(b200, oracle_mod, c):
     assert (got == want).all()
 
 
+@pytest.mark.parametrize("kind,b,n,m,c,nt", [
+    ("table", 1, 20000, 2048, 0, 0), ("table", 1, 20000, 2048, 8, 128), ("adv", 2, 20000, 1500, 16, 128),
+    ("adv", 1, 5000, 5000, 8, 128), ("table", 2, 3500, 3000, 4, 128), ("adv", 1, 3100, 3200, 2, 128),
+    ("table", 1, 49000, 700, 8, 256), ("adv", 1, 99000, 300, 16, 256), ("table", 3, 8192, 1000, 16, 128)])
+def test_fps_several_samples_per_exchange_equals_chain_and_oracle(b200, oracle_mod, kind, b, n, m, c, nt):
+    """fps_multi.cu accepts a run of samples per cluster exchange; fps.cu's chain kernel takes one per step.
+    Both must give the oracle's indices -- on tie-heavy clouds (adv), with more samples than points, and for one,
+    two and four candidates per lane (cluster size x CTA width)."""
+    lib = b200._abi.lib
+    x = clouds(b200, b, n, kind, 13 * n + m)
+    want = oracle_mod.furthest_point_sampling(x, m)
+    lib.b200_fps_set_cluster(c)
+    lib.b200_fps_set_threads(nt)
+    try:
+        for multi in (1, 0):
+            lib.b200_fps_set_multi(multi)
+            got = b200.ops.furthest_point_sampling(dev(x), m).cpu().numpy()
+            assert (got == want).all(), "multi=%d" % multi
+    finally:
+        lib.b200_fps_set_cluster(0)
+        lib.b200_fps_set_threads(0)
+        lib.b200_fps_set_multi(1)
+
+
+def test_fps_several_samples_per_exchange_degenerate_clouds(b200, oracle_mod):
+    """Every point skipped (|p|^2 <= 1e-3), all points identical, and a few live points among skipped ones:
+    the acceptance chain has no / only zero-valued candidates."""
+    rng = np.random.default_rng(2)
+    n = 6000
+    skipped = np.full((1, n, 3), 0.01, np.float32)
+    same = np.full((1, n, 3), 0.37, np.float32)
+    few = skipped.copy()
+    few[0, rng.choice(n, 40, replace=False)] = rng.uniform(0.2, 0.4, (40, 3)).astype(np.float32)
+    for x in (skipped, same, few):
+        want = oracle_mod.furthest_point_sampling(x, 300)
+        got = b200.ops.furthest_point_sampling(dev(x), 300).cpu().numpy()
+        assert (got == want).all()
+
+
 def test_fps_all_skipped_and_more_samples_than_points(b200, oracle_mod):
     x = np.full((1, 64, 3), 0.01, np.float32)
     assert (b200.ops.furthest_point_sampling(dev(x), 8).cpu().numpy() == 0).all()
