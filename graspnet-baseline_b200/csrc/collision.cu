@@ -21,7 +21,8 @@
 namespace {
 
 constexpr int CTH = 128;    // grasps per CTA (one per thread)
-constexpr int CPT = 1024;   // scene points per CTA slice (24 KB of fp64 xyz)
+constexpr int CPT = 256;    // scene points per CTA slice (6 KB of fp64 xyz): enough CTAs to fill every SM several times
+constexpr int CU = 4;       // points per inner step: CU independent fp64 chains per thread
 
 __global__ void __launch_bounds__(CTH)
 collision_kernel(const double *__restrict__ scene, int n, const int32_t *__restrict__ n_dev,
@@ -33,7 +34,9 @@ collision_kernel(const double *__restrict__ scene, int n, const int32_t *__restr
   const int p0 = blockIdx.y * CPT;
   if (p0 >= n) return;
   const int pn = min(CPT, n - p0);
-  for (int i = threadIdx.x; i < pn * 3; i += CTH) pts[i] = __ldg(scene + (size_t)p0 * 3 + i);
+  // the tail of a short slice is NaN: every comparison below is false for it
+  for (int i = threadIdx.x; i < CPT * 3; i += CTH)
+    pts[i] = i < pn * 3 ? __ldg(scene + (size_t)p0 * 3 + i) : __longlong_as_double(0x7ff8000000000000LL);
   __syncthreads();
   if (g >= m) return;
   const double *t = T + (size_t)g * 3, *r = R + (size_t)g * 9, *h = thr + (size_t)g * 10;
@@ -43,29 +46,39 @@ collision_kernel(const double *__restrict__ scene, int n, const int32_t *__restr
   const double h0 = h[0], h1 = h[1], h2 = h[2], h3 = h[3], h4 = h[4], h5 = h[5], h6 = h[6],
                h7 = h[7], h8 = h[8], h9 = h[9];
   int cg_ = 0, cl = 0, cr = 0, cb = 0, cs = 0, ci = 0;
-#pragma unroll 2
-  for (int k = 0; k < pn; ++k) {
-    const double x = __dsub_rn(pts[3 * k], t0), y = __dsub_rn(pts[3 * k + 1], t1),
-                 z = __dsub_rn(pts[3 * k + 2], t2);
-    const double tz = __fma_rn(z, r8, __fma_rn(y, r5, __dmul_rn(x, r2)));
-    const bool m1 = (tz > h0) & (tz < h1);
-    if (!__any_sync(__activemask(), m1)) continue;     // every mask below needs the height slab
-    const double tx = __fma_rn(z, r6, __fma_rn(y, r3, __dmul_rn(x, r0)));
-    const double ty = __fma_rn(z, r7, __fma_rn(y, r4, __dmul_rn(x, r1)));
-    const bool m2 = (tx > h2) & (tx < h3);
-    const bool m3 = ty > h4;
-    const bool m4 = ty < h5;
-    const bool m5 = ty < h6;
-    const bool m6 = ty > h7;
-    const bool m7 = (tx <= h2) & (tx > h8);
-    const bool m8 = (tx <= h8) & (tx > h9);
-    const bool left = m1 & m2 & m3 & m4;
-    const bool right = m1 & m2 & m5 & m6;
-    const bool bottom = m1 & m3 & m5 & m7;
-    const bool shifting = m1 & m3 & m5 & m8;
-    cg_ += (left | right | bottom | shifting);
-    cl += left; cr += right; cb += bottom; cs += shifting;
-    ci += (m1 & m2 & (!m4) & (!m6));
+  const int steps = (pn + CU - 1) / CU;
+  for (int k4 = 0; k4 < steps; ++k4) {
+    double x[CU], y[CU], z[CU];
+    bool m1[CU], any = false;
+#pragma unroll
+    for (int u = 0; u < CU; ++u) {
+      const int k = k4 * CU + u;
+      x[u] = __dsub_rn(pts[3 * k], t0); y[u] = __dsub_rn(pts[3 * k + 1], t1); z[u] = __dsub_rn(pts[3 * k + 2], t2);
+      const double tz = __fma_rn(z[u], r8, __fma_rn(y[u], r5, __dmul_rn(x[u], r2)));
+      m1[u] = (tz > h0) & (tz < h1);
+      any = any | m1[u];
+    }
+    if (!__any_sync(__activemask(), any)) continue;    // every mask below needs the height slab
+#pragma unroll
+    for (int u = 0; u < CU; ++u) {
+      if (!m1[u]) continue;
+      const double tx = __fma_rn(z[u], r6, __fma_rn(y[u], r3, __dmul_rn(x[u], r0)));
+      const double ty = __fma_rn(z[u], r7, __fma_rn(y[u], r4, __dmul_rn(x[u], r1)));
+      const bool m2 = (tx > h2) & (tx < h3);
+      const bool m3 = ty > h4;
+      const bool m4 = ty < h5;
+      const bool m5 = ty < h6;
+      const bool m6 = ty > h7;
+      const bool m7 = (tx <= h2) & (tx > h8);
+      const bool m8 = (tx <= h8) & (tx > h9);
+      const bool left = m2 & m3 & m4;
+      const bool right = m2 & m5 & m6;
+      const bool bottom = m3 & m5 & m7;
+      const bool shifting = m3 & m5 & m8;
+      cg_ += (left | right | bottom | shifting);
+      cl += left; cr += right; cb += bottom; cs += shifting;
+      ci += (m2 & (!m4) & (!m6));
+    }
   }
   int32_t *o = counts + (size_t)g * 6;
   if (cg_) atomicAdd(o + 0, cg_);

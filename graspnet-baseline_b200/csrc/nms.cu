@@ -12,9 +12,10 @@
 //   2. mask kernel   : 64x64 tiles of the upper triangle; thread = row, 64-bit word
 //                      of "row suppresses column" bits (the torchvision-NMS layout)
 //   3. sweep kernel  : one CTA; per 64-row block the diagonal word chain is resolved
-//                      serially from shared memory by one thread, then all threads OR
-//                      the kept rows into the remaining removed-words in parallel;
-//                      finally a popc prefix compacts the survivors.
+//                      serially from shared memory by one thread, then the kept rows are
+//                      OR-ed into the remaining removed-words (warp = column word, lane = row,
+//                      one load per lane + a warp OR reduction); finally a popc prefix
+//                      compacts the survivors.
 #include "common.cuh"
 
 namespace {
@@ -85,47 +86,58 @@ nms_mask_kernel(const float *__restrict__ grasps, const int32_t *__restrict__ or
 }
 
 constexpr int ST = 256;
+constexpr int MAXW = 512;                    // 32768 grasps / 64
 
+// One CTA.  Per 64-row block: (a) the diagonal word chain is resolved serially by one thread from shared memory
+// (the 64 words were prefetched during the previous block); (b) every kept row's remaining words are OR-ed into
+// the removed set: a warp takes a column word, lane = row, ONE independent global load per lane and a warp OR
+// reduction -- a single memory latency per block instead of one per kept row.
 __global__ void __launch_bounds__(ST)
 nms_sweep_kernel(const unsigned long long *__restrict__ mask, const int32_t *__restrict__ order, int m,
-                 int W, unsigned long long *__restrict__ removed /* W words, global scratch */,
-                 int32_t *__restrict__ keep, int32_t *__restrict__ nkeep) {
+                 int W, int32_t *__restrict__ keep, int32_t *__restrict__ nkeep) {
+  __shared__ unsigned long long removed[MAXW];
   __shared__ unsigned long long diag[64];
   __shared__ unsigned long long s_keep;
   __shared__ int s_prefix[ST];
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   for (int w = tid; w < W; w += ST) removed[w] = 0ull;
-  __syncthreads();
+  unsigned long long dnext = 0ull;             // diagonal word of row (wb*64 + tid), fetched one block ahead
+  if (tid < 64 && tid < m) dnext = mask[(size_t)tid * W];
   for (int wb = 0; wb < W; ++wb) {
     if (tid < 64) {
-      const int a = wb * 64 + tid;
-      diag[tid] = a < m ? mask[(size_t)a * W + wb] : 0ull;
+      diag[tid] = dnext;
+      const int a = (wb + 1) * 64 + tid;
+      dnext = (wb + 1 < W && a < m) ? mask[(size_t)a * W + wb + 1] : 0ull;
     }
     __syncthreads();
     if (tid == 0) {
-      unsigned long long rem = removed[wb], kb = 0ull;
       const int rn = min(64, m - wb * 64);
-      for (int bit = 0; bit < rn; ++bit) {
-        if (!((rem >> bit) & 1ull)) { kb |= 1ull << bit; rem |= diag[bit]; }
+      unsigned long long rem = removed[wb] | (rn < 64 ? ~0ull << rn : 0ull), kb = 0ull;
+#pragma unroll 16
+      for (int bit = 0; bit < 64; ++bit) {
+        const unsigned long long d = diag[bit];
+        const unsigned long long alive = ((rem >> bit) & 1ull) ^ 1ull;
+        kb |= alive << bit;
+        rem |= d & (0ull - alive);
       }
       s_keep = kb;
       removed[wb] = ~kb;                     // final: bit set = not kept (padding bits too)
     }
     __syncthreads();
     const unsigned long long kb = s_keep;
-    for (int w = wb + 1 + tid; w < W; w += ST) {
-      unsigned long long acc = 0ull, bitsleft = kb;
-      while (bitsleft) {
-        const int bit = __ffsll((long long)bitsleft) - 1;
-        bitsleft &= bitsleft - 1;
-        acc |= mask[(size_t)(wb * 64 + bit) * W + w];
-      }
-      removed[w] |= acc;
+    const unsigned kbl = (unsigned)kb, kbh = (unsigned)(kb >> 32);
+    const bool k0 = (kbl >> lane) & 1u, k1 = (kbh >> lane) & 1u;
+    const unsigned long long *r0 = mask + (size_t)(wb * 64 + lane) * W, *r1 = r0 + (size_t)32 * W;
+    for (int w = wb + 1 + warp; w < W; w += ST / 32) {
+      const unsigned long long v0 = k0 ? r0[w] : 0ull, v1 = k1 ? r1[w] : 0ull;
+      const unsigned long long v = v0 | v1;
+      const unsigned lo = __reduce_or_sync(0xffffffffu, (unsigned)v);
+      const unsigned hi = __reduce_or_sync(0xffffffffu, (unsigned)(v >> 32));
+      if (lane == 0) removed[w] |= ((unsigned long long)hi << 32) | lo;
     }
     __syncthreads();
   }
-  // compaction: survivors in sorted order
-  // each thread owns a contiguous range of words
+  // compaction: survivors in sorted order; each thread owns a contiguous range of words
   const int per = (W + ST - 1) / ST;
   const int w0 = min(W, tid * per), w1 = min(W, w0 + per);
   int cnt = 0;
@@ -183,7 +195,7 @@ extern "C" int b200_grasp_nms(const float *grasps, int m, double translation_thr
   nms_mask_kernel<<<dim3((unsigned)W, (unsigned)W), 64, 0, st>>>(grasps, order, m, W, translation_thresh,
                                                                 cos_rotation_thresh, mask);
   B200_LAUNCH_CHECK();
-  nms_sweep_kernel<<<1, ST, 0, st>>>(mask, order, m, W, removed, keep, nkeep);
+  nms_sweep_kernel<<<1, ST, 0, st>>>(mask, order, m, W, keep, nkeep);
   B200_LAUNCH_CHECK();
   return 0;
 }
