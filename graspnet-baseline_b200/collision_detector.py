@@ -58,8 +58,7 @@ class ModelFreeCollisionDetector():
         packed[:, 3:12] = grasp_group.rotation_matrices.reshape(-1, 9)
         packed[:, 12:22] = self._thresholds(grasp_group, approach_dist)
         d = torch.from_numpy(packed).to(self.device, non_blocking=True)
-        T, R, thr = d[:, 0:3].contiguous(), d[:, 3:12].contiguous(), d[:, 12:22].contiguous()
-        counts = _ext.collision_counts(self._scene_dev, T, R, thr, self._nvox_dev).cpu().numpy().astype(np.int64)
+        counts = _ext.collision_counts_packed(self._scene_dev, d, self._nvox_dev).cpu().numpy().astype(np.int64)
         heights = grasp_group.heights[:, np.newaxis]
         widths = grasp_group.widths[:, np.newaxis]
         vox3 = self.voxel_size ** 3

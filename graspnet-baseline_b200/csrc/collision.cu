@@ -27,7 +27,8 @@ constexpr int CU = 4;       // points per inner step: CU independent fp64 chains
 __global__ void __launch_bounds__(CTH)
 collision_kernel(const double *__restrict__ scene, int n, const int32_t *__restrict__ n_dev,
                  const double *__restrict__ T, const double *__restrict__ R,
-                 const double *__restrict__ thr, int m, int32_t *__restrict__ counts) {
+                 const double *__restrict__ thr, int st, int sr, int sh, int m,
+                 int32_t *__restrict__ counts) {
   __shared__ double pts[CPT * 3];
   if (n_dev) n = min(n, __ldg(n_dev));               // scene length produced on the device
   const int g = blockIdx.x * CTH + threadIdx.x;
@@ -39,7 +40,7 @@ collision_kernel(const double *__restrict__ scene, int n, const int32_t *__restr
     pts[i] = i < pn * 3 ? __ldg(scene + (size_t)p0 * 3 + i) : __longlong_as_double(0x7ff8000000000000LL);
   __syncthreads();
   if (g >= m) return;
-  const double *t = T + (size_t)g * 3, *r = R + (size_t)g * 9, *h = thr + (size_t)g * 10;
+  const double *t = T + (size_t)g * st, *r = R + (size_t)g * sr, *h = thr + (size_t)g * sh;   // row strides
   const double t0 = t[0], t1 = t[1], t2 = t[2];
   const double r0 = r[0], r1 = r[1], r2 = r[2], r3 = r[3], r4 = r[4], r5 = r[5], r6 = r[6],
                r7 = r[7], r8 = r[8];
@@ -92,32 +93,40 @@ collision_kernel(const double *__restrict__ scene, int n, const int32_t *__restr
 }  // namespace
 
 static int collision_launch(const double *scene, int n, const int32_t *n_dev, const double *T,
-                            const double *R, const double *thr, int m, int32_t *counts, void *stream);
+                            const double *R, const double *thr, int st, int sr, int sh, int m, int32_t *counts,
+                            void *stream);
 
 extern "C" int b200_collision_counts(const double *scene, int n, const double *T, const double *R,
                                      const double *thr, int m, int32_t *counts, void *stream) {
-  return collision_launch(scene, n, nullptr, T, R, thr, m, counts, stream);
+  return collision_launch(scene, n, nullptr, T, R, thr, 3, 9, 10, m, counts, stream);
 }
 
 extern "C" int b200_collision_counts_dn(const double *scene, const int32_t *n_dev, int n_max,
                                         const double *T, const double *R, const double *thr, int m,
                                         int32_t *counts, void *stream) {
   if (!n_dev) return B200_EINVAL;
-  return collision_launch(scene, n_max, n_dev, T, R, thr, m, counts, stream);
+  return collision_launch(scene, n_max, n_dev, T, R, thr, 3, 9, 10, m, counts, stream);
+}
+
+extern "C" int b200_collision_counts_packed(const double *scene, const int32_t *n_dev, int n_max,
+                                            const double *packed, int m, int32_t *counts, void *stream) {
+  if (!packed && m > 0) return B200_EINVAL;
+  return collision_launch(scene, n_max, n_dev, packed, packed + 3, packed + 12, 22, 22, 22, m, counts, stream);
 }
 
 static int collision_launch(const double *scene, int n, const int32_t *n_dev, const double *T,
-                            const double *R, const double *thr, int m, int32_t *counts, void *stream) {
+                            const double *R, const double *thr, int st, int sr, int sh, int m, int32_t *counts,
+                            void *stream) {
   if (n < 0 || m < 0) return B200_EINVAL;
   if (m == 0) return 0;
   if (!counts) return B200_EINVAL;
-  cudaStream_t st = (cudaStream_t)stream;
-  B200_CUDA(cudaMemsetAsync(counts, 0, sizeof(int32_t) * 6 * (size_t)m, st));
+  cudaStream_t cs = (cudaStream_t)stream;
+  B200_CUDA(cudaMemsetAsync(counts, 0, sizeof(int32_t) * 6 * (size_t)m, cs));
   if (n == 0) return 0;
   if (!scene || !T || !R || !thr) return B200_EINVAL;
   if (ceil_div(n, CPT) > 65535) return B200_ECAPACITY;
   dim3 grid((unsigned)ceil_div(m, CTH), (unsigned)ceil_div(n, CPT));
-  collision_kernel<<<grid, CTH, 0, st>>>(scene, n, n_dev, T, R, thr, m, counts);
+  collision_kernel<<<grid, CTH, 0, cs>>>(scene, n, n_dev, T, R, thr, st, sr, sh, m, counts);
   B200_LAUNCH_CHECK();
   return 0;
 }

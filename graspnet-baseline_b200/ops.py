@@ -272,6 +272,23 @@ def collision_counts(scene, T, R, thr, n_dev=None):
     return counts
 
 
+def collision_counts_packed(scene, packed, n_dev=None):
+    """scene (N,3) f64, packed (M,22) f64 = T | R | thr per grasp -> counts (M,6) i32 (see collision_counts)."""
+    _chk(scene, "scene", torch.float64)
+    _chk(packed, "packed", torch.float64)
+    if packed.dim() != 2 or packed.shape[1] != 22:
+        raise ValueError("b200grasp: packed must be (M,22)")
+    n, m = scene.shape[0], packed.shape[0]
+    counts = torch.empty((m, 6), dtype=torch.int32, device=scene.device)
+    if n_dev is not None:
+        _chk(n_dev, "n_dev", torch.int32)
+    with torch.cuda.device(scene.device):
+        _abi.check(_lib.b200_collision_counts_packed(_ptr(scene), _ptr(n_dev) if n_dev is not None else None, n,
+                                                     _ptr(packed), m, _ptr(counts), _stream()),
+                   "collision_counts_packed")
+    return counts
+
+
 def voxel_down_sample(points, voxel_size):
     """points (N,3) f64 -> (out (N,3) f64 of which the first nvox rows are valid, nvox (1,) i32), both on
     the device   [utils/collision_detector.py:32-35 -> open3d voxel_down_sample, restated]"""

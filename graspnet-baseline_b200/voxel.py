@@ -16,7 +16,12 @@ def voxel_down_sample_device(points, voxel_size, device="cuda"):
     if isinstance(points, torch.Tensor):
         p = points.to(device=device, dtype=torch.float64).reshape(-1, 3).contiguous()
     else:
-        p = torch.from_numpy(np.ascontiguousarray(np.asarray(points, dtype=np.float64).reshape(-1, 3))).to(device)
+        a = np.asarray(points)
+        if a.dtype == np.float32:
+            # half the bytes over PCIe; float -> double on the device is exact
+            p = torch.from_numpy(np.ascontiguousarray(a.reshape(-1, 3))).to(device).double()
+        else:
+            p = torch.from_numpy(np.ascontiguousarray(np.asarray(a, dtype=np.float64).reshape(-1, 3))).to(device)
     return _ext.voxel_down_sample(p, voxel_size)
 
 

@@ -149,6 +149,11 @@ int b200_collision_counts(const double *scene, int n, const double *T, const dou
 int b200_collision_counts_dn(const double *scene, const int32_t *n_dev, int n_max, const double *T,
                              const double *R, const double *thr, int m, int32_t *counts, void *stream);
 
+/* Same, with the per-grasp inputs in ONE row-major [M,22] fp64 buffer: T (3) | R (9) | thr (10) -- the layout
+ * ModelFreeCollisionDetector.detect uploads with a single copy.  n_dev may be NULL (then n_max is the length). */
+int b200_collision_counts_packed(const double *scene, const int32_t *n_dev, int n_max, const double *packed,
+                                 int m, int32_t *counts, void *stream);
+
 /* Voxel down-sample behind ModelFreeCollisionDetector.__init__ (utils/collision_detector.py:32-35 calls
  * open3d's PointCloud.voxel_down_sample; restated, parity unpinned).  points[n,3] f64 -> out[<=n,3] f64
  * (fp64 mean per occupied voxel, accumulated in point order, rows in ascending voxel-key order),
