@@ -1,0 +1,138 @@
+// decode.cu -- head outputs -> grasp rows (sm_100a).
+//
+// Replaces pred_decode (reference models/graspnet.py:77-134) and the rotation construction it calls
+// (utils/loss_utils.py:68-96, batch_viewpoint_params_to_matrix): per seed point the best in-plane angle class per
+// depth (argmax over A), the best depth (argmax over D of the gathered scores), width = clamp(1.2 w, 0, 0.1),
+// score = score * tolerance / 0.05, rotation from the (negated) approach view and the angle, and the rows of the
+// seeds whose objectness argmax is 1 compacted IN SEED ORDER into the (M,17) layout the collision detector and
+// NMS read: [score, width, 0.02, depth, R(9 row-major), centre(3), -1].  The reference does this with ~40 small
+// torch launches and a boolean-mask compaction per scene; here it is one launch for the whole batch, one CTA per
+// scene (1024 seeds = one pass), and the row count stays on the device.
+//
+// Exactness: classes, depth, width, score and centre are selections of inputs or single-rounded fp32 expressions
+// in the reference's order (bit-exact against the reference, tests/golden/decode_*.npz); the rotation goes through
+// norms, sin/cos and a 3x3 product and is compared to 1e-6.  torch.argmax returns the FIRST maximum; the strict `>`
+// scans below do the same.  The reference calls torch.cross without `dim`: with exactly three surviving seeds the
+// cross product runs down the rows (first dimension of size 3) -- reproduced by the fix-up at the end.
+#include "common.cuh"
+
+namespace {
+
+constexpr int DT = 1024;
+constexpr int MAXD = 8;
+
+struct Frame { float ax[3], ay[3], s, c; };
+
+__global__ void __launch_bounds__(DT)
+pred_decode_kernel(const float *__restrict__ objectness, const float *__restrict__ score,
+                   const float *__restrict__ angle_cls, const float *__restrict__ width,
+                   const float *__restrict__ tol, const float *__restrict__ xyz, const float *__restrict__ view,
+                   int ns, int na, int nd, float *__restrict__ rows, int32_t *__restrict__ nrows) {
+  __shared__ int warp_sum[DT / 32];
+  __shared__ int s_base;
+  __shared__ Frame first3[3];
+  const int scene = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const size_t head = (size_t)scene * na * ns * nd;
+  const float *obj = objectness + (size_t)scene * 2 * ns;
+  const float *sc = score + head, *cl = angle_cls + head, *wd = width + head, *tl = tol + head;
+  const float *ctr = xyz + (size_t)scene * ns * 3, *vw = view + (size_t)scene * ns * 3;
+  float *out = rows + (size_t)scene * ns * 17;
+  if (tid == 0) s_base = 0;
+  __syncthreads();
+  for (int i0 = 0; i0 < ns; i0 += DT) {
+    const int i = i0 + tid;
+    bool keep = false;
+    float g_score = 0.f, g_width = 0.f, g_depth = 0.f, g_angle = 0.f;
+    if (i < ns) {
+      keep = __ldg(obj + ns + i) > __ldg(obj + i);                 // argmax over 2 == 1 (first maximum wins a tie)
+      float best = 0.f;
+      for (int d = 0; d < nd; ++d) {
+        // angle class of this depth: first maximum over the A class scores
+        int a_best = 0;
+        float c_best = __ldg(cl + ((size_t)0 * ns + i) * nd + d);
+        for (int a = 1; a < na; ++a) {
+          const float c = __ldg(cl + ((size_t)a * ns + i) * nd + d);
+          if (c > c_best) { c_best = c; a_best = a; }
+        }
+        const size_t at = ((size_t)a_best * ns + i) * nd + d;
+        const float s = __ldg(sc + at);
+        if (d == 0 || s > best) {                                   // depth class: first maximum of the gathered scores
+          best = s;
+          const float w = __fmul_rn(1.2f, __ldg(wd + at));
+          g_width = fminf(fmaxf(w, 0.f), 0.1f);
+          g_score = __fdiv_rn(__fmul_rn(s, __ldg(tl + at)), 0.05f);
+          g_depth = __fmul_rn((float)(d + 1), 0.01f);
+          g_angle = __fmul_rn(__fdiv_rn((float)a_best, 12.f), 3.14159265358979323846f);
+        }
+      }
+    }
+    // order-preserving compaction: block exclusive scan of the keep flags
+    const unsigned bal = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) warp_sum[warp] = __popc(bal);
+    __syncthreads();
+    int before = s_base;
+    for (int w = 0; w < warp; ++w) before += warp_sum[w];
+    const int pos = before + __popc(bal & lanemask_lt());
+    if (keep) {
+      const float tx = -__ldg(vw + 3 * (size_t)i), ty = -__ldg(vw + 3 * (size_t)i + 1), tz = -__ldg(vw + 3 * (size_t)i + 2);
+      float yx = -ty, yy = tx;                                      // axis_y = (-x1, x0, 0)
+      if (sqrtf(yx * yx + yy * yy) == 0.f) yy = 1.f;
+      const float nx = sqrtf(tx * tx + ty * ty + tz * tz), ny = sqrtf(yx * yx + yy * yy);
+      const float ax0 = tx / nx, ax1 = ty / nx, ax2 = tz / nx;
+      const float ay0 = yx / ny, ay1 = yy / ny, ay2 = 0.f / ny;
+      const float az0 = ax1 * ay2 - ax2 * ay1, az1 = ax2 * ay0 - ax0 * ay2, az2 = ax0 * ay1 - ax1 * ay0;
+      const float s = sinf(g_angle), c = cosf(g_angle);
+      float *r = out + (size_t)pos * 17;
+      r[0] = g_score; r[1] = g_width; r[2] = 0.02f; r[3] = g_depth;
+      r[4] = ax0; r[5] = ay0 * c + az0 * s; r[6] = az0 * c - ay0 * s;
+      r[7] = ax1; r[8] = ay1 * c + az1 * s; r[9] = az1 * c - ay1 * s;
+      r[10] = ax2; r[11] = ay2 * c + az2 * s; r[12] = az2 * c - ay2 * s;
+      r[13] = __ldg(ctr + 3 * (size_t)i); r[14] = __ldg(ctr + 3 * (size_t)i + 1); r[15] = __ldg(ctr + 3 * (size_t)i + 2);
+      r[16] = -1.f;
+      if (pos < 3) {
+        Frame &f = first3[pos];
+        f.ax[0] = ax0; f.ax[1] = ax1; f.ax[2] = ax2;
+        f.ay[0] = ay0; f.ay[1] = ay1; f.ay[2] = ay2;
+        f.s = s; f.c = c;
+      }
+    }
+    __syncthreads();
+    if (tid == DT - 1) s_base = pos + (keep ? 1 : 0);
+    __syncthreads();
+  }
+  if (tid == 0) {
+    const int total = s_base;
+    nrows[scene] = total;
+    if (total == 3) {
+      // torch.cross(axis_x, axis_y) without `dim` on (3,3) inputs: the cross product of the COLUMNS
+      for (int j = 0; j < 3; ++j) {
+        const float a0 = first3[0].ax[j], a1 = first3[1].ax[j], a2 = first3[2].ax[j];
+        const float b0 = first3[0].ay[j], b1 = first3[1].ay[j], b2 = first3[2].ay[j];
+        const float z[3] = {a1 * b2 - a2 * b1, a2 * b0 - a0 * b2, a0 * b1 - a1 * b0};
+        for (int i = 0; i < 3; ++i) {
+          float *r = out + (size_t)i * 17 + 4 + 3 * j;
+          r[1] = first3[i].ay[j] * first3[i].c + z[i] * first3[i].s;
+          r[2] = z[i] * first3[i].c - first3[i].ay[j] * first3[i].s;
+        }
+      }
+    }
+  }
+}
+
+}  // namespace
+
+extern "C" int b200_pred_decode(const float *objectness, const float *score, const float *angle_cls,
+                                const float *width, const float *tolerance, const float *xyz, const float *view_xyz,
+                                int b, int ns, int num_angle, int num_depth, float *rows, int32_t *nrows,
+                                void *stream) {
+  if (b < 0 || ns < 0 || num_angle < 1 || num_depth < 1) return B200_EINVAL;
+  if (num_depth > MAXD) return B200_ECAPACITY;
+  if (b == 0) return 0;
+  if (!nrows) return B200_EINVAL;
+  if (ns > 0 && (!objectness || !score || !angle_cls || !width || !tolerance || !xyz || !view_xyz || !rows))
+    return B200_EINVAL;
+  pred_decode_kernel<<<b, DT, 0, (cudaStream_t)stream>>>(objectness, score, angle_cls, width, tolerance, xyz, view_xyz,
+                                                        ns, num_angle, num_depth, rows, nrows);
+  B200_LAUNCH_CHECK();
+  return 0;
+}

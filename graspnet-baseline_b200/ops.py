@@ -289,6 +289,25 @@ def collision_counts_packed(scene, packed, n_dev=None):
     return counts
 
 
+def pred_decode(objectness, score, angle_cls, width, tolerance, xyz, view_xyz):
+    """Head outputs of a batch -> (rows (B,Ns,17) f32, nrows (B,) i32), both on the device
+    [models/graspnet.py:77-134].  objectness (B,2,Ns); score/angle_cls/width/tolerance (B,A,Ns,D); xyz, view (B,Ns,3)."""
+    for t, nm in ((objectness, "objectness"), (score, "score"), (angle_cls, "angle_cls"), (width, "width"),
+                  (tolerance, "tolerance"), (xyz, "xyz"), (view_xyz, "view_xyz")):
+        _chk(t, nm, torch.float32)
+    b, na, ns, nd = score.shape
+    if tuple(objectness.shape) != (b, 2, ns) or tuple(xyz.shape) != (b, ns, 3) or tuple(view_xyz.shape) != (b, ns, 3) \
+            or any(tuple(t.shape) != (b, na, ns, nd) for t in (angle_cls, width, tolerance)):
+        raise ValueError("b200grasp: pred_decode shapes do not agree")
+    rows = torch.empty((b, ns, 17), dtype=torch.float32, device=score.device)
+    nrows = torch.empty((b,), dtype=torch.int32, device=score.device)
+    with torch.cuda.device(score.device):
+        _abi.check(_lib.b200_pred_decode(_ptr(objectness), _ptr(score), _ptr(angle_cls), _ptr(width), _ptr(tolerance),
+                                         _ptr(xyz), _ptr(view_xyz), b, ns, na, nd, _ptr(rows), _ptr(nrows), _stream()),
+                   "pred_decode")
+    return rows, nrows
+
+
 def voxel_down_sample(points, voxel_size):
     """points (N,3) f64 -> (out (N,3) f64 of which the first nvox rows are valid, nvox (1,) i32), both on
     the device   [utils/collision_detector.py:32-35 -> open3d voxel_down_sample, restated]"""

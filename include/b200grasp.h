@@ -77,6 +77,17 @@ int b200_cylinder_query_multi(const float *new_xyz, const float *xyz, const floa
                               int n, int m, float radius, float hmin, const float *hmax, int nh,
                               int nsample, int32_t *idx, void *stream);
 
+/* Replaces pred_decode(end_points) (models/graspnet.py:77-134, with batch_viewpoint_params_to_matrix,
+ * utils/loss_utils.py:68-96) for a batch of b scenes in one launch:
+ *   objectness [b,2,ns]; score / angle_cls / width / tolerance [b,A,ns,D] (A = num_angle, D = num_depth <= 8);
+ *   xyz (fp2_xyz) and view_xyz (grasp_top_view_xyz) [b,ns,3]; all fp32.
+ *   rows [b,ns,17] OUT: the rows of the seeds whose objectness argmax is 1, in seed order, as
+ *   [score, width, 0.02, depth, R(9 row-major), centre(3), -1]; nrows [b] i32 OUT: how many per scene
+ *   (rows beyond it are not written).  No host synchronisation. */
+int b200_pred_decode(const float *objectness, const float *score, const float *angle_cls, const float *width,
+                     const float *tolerance, const float *xyz, const float *view_xyz, int b, int ns,
+                     int num_angle, int num_depth, float *rows, int32_t *nrows, void *stream);
+
 /* Grid-accelerated forms of b200_ball_query / b200_cylinder_query_multi: identical results (the first
  * nsample hits IN INDEX ORDER, padded with the first hit, zeros if none), but the cloud is first binned
  * into a uniform grid held in `workspace` (b200_query_grid_workspace(b, n) bytes of device memory, no

@@ -121,3 +121,62 @@ def grasp_nms(grasps, translation_thresh=0.03, rotation_thresh=30.0 / 180.0 * ma
     keep = np.zeros(max(m, 1), np.int32)
     nk = lib().oracle_grasp_nms(_p(g), m, float(translation_thresh), math.cos(rotation_thresh), _p(keep))
     return keep[:nk].copy()
+
+
+GRASP_MAX_WIDTH = 0.1        # utils/loss_utils.py:8
+GRASP_MAX_TOLERANCE = 0.05   # utils/loss_utils.py:9
+
+
+def viewpoint_params_to_matrix(towards, angle):
+    """utils/loss_utils.py:68-96 (batch_viewpoint_params_to_matrix) in fp32 numpy: x axis = normalised approach
+    vector, y axis = (-x1, x0, 0) normalised ((0,1,0) when that is zero), z = x cross y, then an in-plane rotation
+    by `angle`.  The reference calls torch.cross WITHOUT `dim`, which picks the FIRST dimension of size 3: with
+    exactly three grasps the cross product runs down the rows instead of along each row (loss_utils.py:89) --
+    restated as is."""
+    f = np.float32
+    ax = np.asarray(towards, f).reshape(-1, 3)
+    n = ax.shape[0]
+    ay = np.stack([-ax[:, 1], ax[:, 0], np.zeros(n, f)], axis=-1)
+    ny = np.sqrt((ay * ay).sum(-1, dtype=f), dtype=f)
+    ay[ny == 0, 1] = 1
+    ax = ax / np.sqrt((ax * ax).sum(-1, dtype=f), dtype=f)[:, None]
+    ay = ay / np.sqrt((ay * ay).sum(-1, dtype=f), dtype=f)[:, None]
+    az = np.cross(ax, ay, axis=0 if n == 3 else -1).astype(f)
+    s, c = np.sin(np.asarray(angle, f), dtype=f), np.cos(np.asarray(angle, f), dtype=f)
+    R = np.empty((n, 3, 3), f)
+    R[:, :, 0] = ax
+    R[:, :, 1] = ay * c[:, None] + az * s[:, None]
+    R[:, :, 2] = az * c[:, None] - ay * s[:, None]
+    return R
+
+
+def pred_decode(objectness_score, grasp_score_pred, grasp_angle_cls_pred, grasp_width_pred, grasp_tolerance_pred,
+                fp2_xyz, grasp_top_view_xyz):
+    """models/graspnet.py:77-134 for ONE scene: head outputs -> (M,17) fp32 grasp rows
+    [score, width, 0.02, depth, R(9), centre(3), -1], seeds whose objectness argmax is 1, in seed order.
+    Shapes: objectness (2,Ns); score / angle-class score / width / tolerance (A,Ns,D); fp2_xyz, top view (Ns,3).
+    Everything but the rotation is a selection of inputs or a single-rounded fp32 expression (exact); the rotation
+    goes through norms, sin/cos and a 3x3 product (compared to 1e-6)."""
+    f = np.float32
+    score = np.asarray(grasp_score_pred, f)
+    cls = np.asarray(grasp_angle_cls_pred, f)
+    width = np.clip(f(1.2) * np.asarray(grasp_width_pred, f), f(0), f(GRASP_MAX_WIDTH))      # :84-85
+    tol = np.asarray(grasp_tolerance_pred, f)
+    a_cls = np.argmax(cls, axis=0)                                                           # (Ns,D) first maximum
+    angle = (a_cls.astype(f) / f(12)) * f(np.pi)                                             # :92
+    pick = lambda t: np.take_along_axis(t, a_cls[None], axis=0)[0]
+    score, width, tol = pick(score), pick(width), pick(tol)                                  # (Ns,D)
+    d_cls = np.argmax(score, axis=1)[:, None]                                                # :101
+    depth = (d_cls.astype(f) + f(1)) * f(0.01)
+    take = lambda t: np.take_along_axis(t, d_cls, axis=1)
+    score, angle, width, tol = take(score), take(angle), take(width), take(tol)              # (Ns,1)
+    obj = np.asarray(objectness_score, f)
+    mask = np.argmax(obj, axis=0) == 1                                                       # :110-111
+    score, width, depth, angle, tol = score[mask], width[mask], depth[mask], angle[mask], tol[mask]
+    centre = np.asarray(fp2_xyz, f)[mask]
+    towards = -np.asarray(grasp_top_view_xyz, f)[mask]
+    score = (score * tol) / f(GRASP_MAX_TOLERANCE)                                           # :119
+    R = viewpoint_params_to_matrix(towards, angle.reshape(-1)).reshape(-1, 9)
+    m = score.shape[0]
+    return np.concatenate([score, width, np.full((m, 1), 0.02, f), depth, R, centre, np.full((m, 1), -1, f)],
+                          axis=1).astype(f)

@@ -12,6 +12,10 @@ neither exists on the GPU box, which only reads the committed .npz files.
   knn_*.npz       : the reference's own CPU knn (knn/src/cpu/knn_cpu.cpp through
                     knn/src/knn.h:53-63, compiled unmodified into oracle/_ref) on seeded
                     inputs; stores inputs and the 1-based int64 indices.
+  decode_*.npz    : models/graspnet.py::pred_decode (lines 77-134; the function body is taken from the
+                    reference file with `ast` at generation time and executed with the reference's own
+                    utils/loss_utils.py::batch_viewpoint_params_to_matrix) on seeded synthetic head
+                    outputs; stores the inputs and the (M,17) rows it returns.
 No pointnet2 fixture can be produced here: every pointnet2 op of the reference is
 CUDA-only and this container has no GPU -- those are pinned on the GPU box against
 oracle/_ref directly (tests/test_gpu_vs_legacy.py).
@@ -139,6 +143,60 @@ def make_knn():
         print("knn", name, tuple(ref.shape), tuple(query.shape), k)
 
 
+def _reference_pred_decode():
+    """pred_decode exactly as written in the reference, without importing models/graspnet.py (that module
+    imports the CUDA-only pointnet2 extension at the top)."""
+    import ast
+    import torch
+    sys.path.insert(0, os.path.join(REF, "utils"))
+    import loss_utils
+    src = open(os.path.join(REF, "models", "graspnet.py")).read()
+    fn = next(n for n in ast.parse(src).body if isinstance(n, ast.FunctionDef) and n.name == "pred_decode")
+    glob = {"torch": torch, "np": np, "GRASP_MAX_WIDTH": loss_utils.GRASP_MAX_WIDTH,
+            "GRASP_MAX_TOLERANCE": loss_utils.GRASP_MAX_TOLERANCE,
+            "batch_viewpoint_params_to_matrix": loss_utils.batch_viewpoint_params_to_matrix}
+    exec(compile(ast.Module(body=[fn], type_ignores=[]), "graspnet.py:pred_decode", "exec"), glob)
+    return glob["pred_decode"]
+
+
+def synth_heads(seed, b, ns, a=12, d=4, ties=False):
+    """head outputs with the shapes models/modules.py produces (OperationNet / ToleranceNet / ApproachNet)."""
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    ep = {"point_clouds": torch.zeros(b, 1, 3),
+          "objectness_score": torch.randn(b, 2, ns, generator=g),
+          "grasp_score_pred": torch.rand(b, a, ns, d, generator=g) * 1.2 - 0.1,
+          "grasp_angle_cls_pred": torch.randn(b, a, ns, d, generator=g),
+          "grasp_width_pred": torch.rand(b, a, ns, d, generator=g) * 0.12 - 0.01,
+          "grasp_tolerance_pred": torch.rand(b, a, ns, d, generator=g) * 0.06,
+          "fp2_xyz": torch.rand(b, ns, 3, generator=g) * 0.6 - 0.3,
+          "grasp_top_view_xyz": torch.nn.functional.normalize(torch.randn(b, ns, 3, generator=g), dim=-1)}
+    if ties:   # equal class scores / equal depth scores / objectness ties / views along +-z (axis_y degenerate)
+        ep["grasp_angle_cls_pred"] = torch.round(ep["grasp_angle_cls_pred"])
+        ep["grasp_score_pred"] = torch.round(ep["grasp_score_pred"] * 4) / 4
+        ep["objectness_score"] = torch.round(ep["objectness_score"])
+        ep["grasp_top_view_xyz"][:, ::5] = torch.tensor([0.0, 0.0, 1.0])
+        ep["grasp_top_view_xyz"][:, 1::7] = torch.tensor([0.0, 0.0, -1.0])
+    return ep
+
+
+def make_decode():
+    pred_decode = _reference_pred_decode()
+    for name, seed, b, ns, ties in (("a", 0, 1, 1024, False), ("b", 1, 2, 257, True), ("c", 2, 1, 5, True)):
+        ep = synth_heads(seed, b, ns, ties=ties)
+        out = pred_decode(ep)
+        save = {k: v.numpy() for k, v in ep.items() if k != "point_clouds"}
+        for i, o in enumerate(out):
+            save["rows_%d" % i] = o.numpy()
+        np.savez_compressed(os.path.join(HERE, f"decode_{name}.npz"), **save)
+        print("decode", name, b, ns, [tuple(o.shape) for o in out])
+
+
 if __name__ == "__main__":
-    make_collision()
-    make_knn()
+    which = sys.argv[1:] or ["collision", "knn", "decode"]
+    if "collision" in which:
+        make_collision()
+    if "knn" in which:
+        make_knn()
+    if "decode" in which:
+        make_decode()

@@ -11,8 +11,8 @@ lib.b200_furthest_point_sampling.argtypes = [vp, ci, ci, ci, vp, vp]
 lib.b200_fps_set_cluster.argtypes = [ci]
 lib.b200_fps_set_threads.argtypes = [ci]
 names = ["compute", "warp-reduce", "publish", "wait+load", "chain", "tail"]
-for kind, n, m, c, nt in (("table", 20000, 2048, 8, 128), ("table", 20000, 2048, 16, 128), ("table", 20000, 2048, 8, 256),
-                          ("table", 20000, 2048, 4, 256), ("adv", 20000, 2048, 8, 128)):
+for kind, n, m, c, nt in (("table", 20000, 2048, 8, 128), ("table", 20000, 2048, 16, 128), ("adv", 20000, 2048, 8, 128),
+                          ("table", 12000, 1024, 8, 128), ("table", 49000, 1024, 16, 128)):
     f = b200grasp.synth.tabletop_cloud if kind == "table" else b200grasp.synth.adversarial_cloud
     x = torch.from_numpy(f(n, 3)[None]).cuda()
     out = torch.empty(1, m, dtype=torch.int32, device="cuda")
