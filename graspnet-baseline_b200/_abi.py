@@ -37,6 +37,10 @@ SIGNATURES = {
     "b200_collision_counts_dn": [_vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp],
     "b200_voxel_down_sample": [_vp, _i, _d, _vp, _vp, _vp, _sz, _vp],
     "b200_collision_counts_packed": [_vp, _vp, _i, _vp, _i, _vp, _vp],
+    "b200_collision_mask_device": [_vp, _vp, _i, _vp, _vp, _i, _d, _d, _d, _vp, _vp, _sz, _vp],
+    "b200_compact_rows": [_vp, _i, _vp, _vp, _i, _vp, _vp, _vp],
+    "b200_grasp_nms_device": [_vp, _vp, _i, _d, _d, _vp, _vp, _vp, _sz, _vp],
+    "b200_gather_rows": [_vp, _i, _vp, _vp, _i, _vp, _vp],
     "b200_pred_decode": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp],
     "b200_ball_query_grid": [_vp, _vp, _i, _i, _i, _f, _i, _vp, _vp, _sz, _vp],
     "b200_cylinder_query_multi_grid": [_vp, _vp, _vp, _i, _i, _i, _f, _f, ctypes.POINTER(_f), _i, _i, _vp, _vp, _sz, _vp],
@@ -52,6 +56,8 @@ lib.b200_grasp_nms_workspace.argtypes = [_i]
 lib.b200_grasp_nms_workspace.restype = _sz
 lib.b200_voxel_down_sample_workspace.argtypes = [_i]
 lib.b200_voxel_down_sample_workspace.restype = _sz
+lib.b200_collision_mask_workspace.argtypes = [_i]
+lib.b200_collision_mask_workspace.restype = _sz
 lib.b200_query_grid_workspace.argtypes = [_i, _i]
 lib.b200_query_grid_workspace.restype = _sz
 lib.b200_error_string.argtypes = [_i]
@@ -69,7 +75,7 @@ lib.b200_fps_set_multi.restype = None
 lib.b200_fps_set_speculation.argtypes = [_i]
 lib.b200_fps_set_speculation.restype = None
 
-EXPORTS = sorted(list(SIGNATURES) + ["b200_grasp_nms_workspace", "b200_voxel_down_sample_workspace", "b200_query_grid_workspace", "b200_error_string", "b200_version", "b200_launch_count"])
+EXPORTS = sorted(list(SIGNATURES) + ["b200_grasp_nms_workspace", "b200_voxel_down_sample_workspace", "b200_query_grid_workspace", "b200_collision_mask_workspace", "b200_error_string", "b200_version", "b200_launch_count"])
 
 
 def check(code, what):

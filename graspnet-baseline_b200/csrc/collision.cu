@@ -16,6 +16,8 @@
 // Rounding: numpy evaluates (p - T) . R for an (N,3)x(3,3) fp64 product with the
 // BLAS micro-kernel's FMA chain  t_c = fma(z, R[2][c], fma(y, R[1][c], x * R[0][c]))
 // (pinned against the reference itself in tests/golden/collision_*.npz).
+#include <cmath>
+
 #include "common.cuh"
 
 namespace {
@@ -28,9 +30,10 @@ __global__ void __launch_bounds__(CTH)
 collision_kernel(const double *__restrict__ scene, int n, const int32_t *__restrict__ n_dev,
                  const double *__restrict__ T, const double *__restrict__ R,
                  const double *__restrict__ thr, int st, int sr, int sh, int m,
-                 int32_t *__restrict__ counts) {
+                 const int32_t *__restrict__ m_dev, int32_t *__restrict__ counts) {
   __shared__ double pts[CPT * 3];
   if (n_dev) n = min(n, __ldg(n_dev));               // scene length produced on the device
+  if (m_dev) m = min(m, __ldg(m_dev));               // grasp count produced on the device (decode / compaction)
   const int g = blockIdx.x * CTH + threadIdx.x;
   const int p0 = blockIdx.y * CPT;
   if (p0 >= n) return;
@@ -93,30 +96,30 @@ collision_kernel(const double *__restrict__ scene, int n, const int32_t *__restr
 }  // namespace
 
 static int collision_launch(const double *scene, int n, const int32_t *n_dev, const double *T,
-                            const double *R, const double *thr, int st, int sr, int sh, int m, int32_t *counts,
-                            void *stream);
+                            const double *R, const double *thr, int st, int sr, int sh, int m,
+                            const int32_t *m_dev, int32_t *counts, void *stream);
 
 extern "C" int b200_collision_counts(const double *scene, int n, const double *T, const double *R,
                                      const double *thr, int m, int32_t *counts, void *stream) {
-  return collision_launch(scene, n, nullptr, T, R, thr, 3, 9, 10, m, counts, stream);
+  return collision_launch(scene, n, nullptr, T, R, thr, 3, 9, 10, m, nullptr, counts, stream);
 }
 
 extern "C" int b200_collision_counts_dn(const double *scene, const int32_t *n_dev, int n_max,
                                         const double *T, const double *R, const double *thr, int m,
                                         int32_t *counts, void *stream) {
   if (!n_dev) return B200_EINVAL;
-  return collision_launch(scene, n_max, n_dev, T, R, thr, 3, 9, 10, m, counts, stream);
+  return collision_launch(scene, n_max, n_dev, T, R, thr, 3, 9, 10, m, nullptr, counts, stream);
 }
 
 extern "C" int b200_collision_counts_packed(const double *scene, const int32_t *n_dev, int n_max,
                                             const double *packed, int m, int32_t *counts, void *stream) {
   if (!packed && m > 0) return B200_EINVAL;
-  return collision_launch(scene, n_max, n_dev, packed, packed + 3, packed + 12, 22, 22, 22, m, counts, stream);
+  return collision_launch(scene, n_max, n_dev, packed, packed + 3, packed + 12, 22, 22, 22, m, nullptr, counts, stream);
 }
 
 static int collision_launch(const double *scene, int n, const int32_t *n_dev, const double *T,
-                            const double *R, const double *thr, int st, int sr, int sh, int m, int32_t *counts,
-                            void *stream) {
+                            const double *R, const double *thr, int st, int sr, int sh, int m,
+                            const int32_t *m_dev, int32_t *counts, void *stream) {
   if (n < 0 || m < 0) return B200_EINVAL;
   if (m == 0) return 0;
   if (!counts) return B200_EINVAL;
@@ -126,7 +129,96 @@ static int collision_launch(const double *scene, int n, const int32_t *n_dev, co
   if (!scene || !T || !R || !thr) return B200_EINVAL;
   if (ceil_div(n, CPT) > 65535) return B200_ECAPACITY;
   dim3 grid((unsigned)ceil_div(m, CTH), (unsigned)ceil_div(n, CPT));
-  collision_kernel<<<grid, CTH, 0, cs>>>(scene, n, n_dev, T, R, thr, st, sr, sh, m, counts);
+  collision_kernel<<<grid, CTH, 0, cs>>>(scene, n, n_dev, T, R, thr, st, sr, sh, m, m_dev, counts);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Device-resident detect(): grasp rows that are already on the device (pred_decode's output) -> collision mask,
+// with the reference's own arithmetic and dtype rules for everything around the point-in-gripper counts
+// (utils/collision_detector.py:69-93 thresholds, :103-112 volumes / IoU / mask).  The rows are fp32 (what
+// `.cpu().numpy()` of the network output gives the reference, test.py:88-89), so numpy evaluates the per-grasp
+// expressions in fp32 (Python floats are weak scalars) and only the IoU division in fp64 (int64 / float32).
+namespace {
+
+constexpr double FINGER_WIDTH = 0.01;    // collision_detector.py:29
+constexpr double FINGER_LENGTH = 0.06;   // collision_detector.py:30
+
+// one thread per grasp: T | R | thr of detect() as a packed fp64 row (the layout collision_kernel reads)
+__global__ void collision_prep_kernel(const float *__restrict__ grasps, const int32_t *__restrict__ m_dev, int m,
+                                      float fl, float fw, float ad, double *__restrict__ packed) {
+  if (m_dev) m = min(m, __ldg(m_dev));
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= m) return;
+  const float *r = grasps + (size_t)g * 17;
+  double *o = packed + (size_t)g * 22;
+  o[0] = (double)r[13]; o[1] = (double)r[14]; o[2] = (double)r[15];
+#pragma unroll
+  for (int e = 0; e < 9; ++e) o[3 + e] = (double)r[4 + e];
+  const float w = r[1], h = r[2], d = r[3];
+  const float h2 = __fdiv_rn(h, 2.f), w2 = __fdiv_rn(w, 2.f);
+  const float dl = __fsub_rn(d, fl), dlw = __fsub_rn(dl, fw);
+  o[12] = (double)(-h2);                       // -h/2
+  o[13] = (double)h2;                          //  h/2
+  o[14] = (double)dl;                          //  d - finger_length
+  o[15] = (double)d;
+  o[16] = (double)(-__fadd_rn(w2, fw));        // -(w/2 + finger_width)
+  o[17] = (double)(-w2);
+  o[18] = (double)__fadd_rn(w2, fw);
+  o[19] = (double)w2;
+  o[20] = (double)dlw;                         //  d - finger_length - finger_width
+  o[21] = (double)__fsub_rn(dlw, ad);          //  ... - approach_dist
+}
+
+// counts -> mask: global_iou = count / (volume + 1e-6) > collision_thresh
+__global__ void collision_finalize_kernel(const float *__restrict__ grasps, const int32_t *__restrict__ counts,
+                                          const int32_t *__restrict__ m_dev, int m, float fl, float fw, float ad,
+                                          float vox3, double thresh, uint8_t *__restrict__ mask) {
+  if (m_dev) m = min(m, __ldg(m_dev));
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= m) return;
+  const float w = grasps[(size_t)g * 17 + 1], h = grasps[(size_t)g * 17 + 2];
+  const float fw2 = __fmul_rn(2.f, fw);                                                   // 2*finger_width (weak scalar)
+  const float lrv = __fdiv_rn(__fmul_rn(__fmul_rn(h, fl), fw), vox3);
+  const float hw = __fmul_rn(h, __fadd_rn(w, fw2));
+  const float bot = __fdiv_rn(__fmul_rn(hw, fw), vox3);
+  const float shf = __fdiv_rn(__fmul_rn(hw, ad), vox3);
+  const float vol = __fadd_rn(__fadd_rn(__fmul_rn(lrv, 2.f), bot), shf);
+  const double iou = __ddiv_rn((double)counts[(size_t)g * 6], (double)__fadd_rn(vol, 1e-6f));
+  mask[g] = iou > thresh ? 1 : 0;
+}
+
+}  // namespace
+
+extern "C" size_t b200_collision_mask_workspace(int m_max) {
+  const size_t m = (size_t)(m_max > 0 ? m_max : 1);
+  return (m * 22 * sizeof(double) + 255) / 256 * 256 + (m * 6 * sizeof(int32_t) + 255) / 256 * 256;
+}
+
+extern "C" int b200_collision_mask_device(const double *scene, const int32_t *n_dev, int n_max, const float *grasps,
+                                          const int32_t *m_dev, int m_max, double voxel_size, double approach_dist,
+                                          double collision_thresh, uint8_t *mask, void *workspace,
+                                          size_t workspace_bytes, void *stream) {
+  if (m_max < 0 || n_max < 0 || !(voxel_size > 0.0)) return B200_EINVAL;
+  if (m_max == 0) return 0;
+  if (!grasps || !mask || !workspace) return B200_EINVAL;
+  if (workspace_bytes < b200_collision_mask_workspace(m_max)) return B200_EWORKSPACE;
+  cudaStream_t cs = (cudaStream_t)stream;
+  double *packed = (double *)workspace;
+  int32_t *counts = (int32_t *)((char *)workspace + ((size_t)m_max * 22 * sizeof(double) + 255) / 256 * 256);
+  if (approach_dist < FINGER_WIDTH) approach_dist = FINGER_WIDTH;            // collision_detector.py:62
+  // Python floats enter the reference's fp32 expressions as fp32 scalars
+  const float fl = (float)FINGER_LENGTH, fw = (float)FINGER_WIDTH, ad = (float)approach_dist;
+  const float vox3 = (float)std::pow(voxel_size, 3.0);                      // voxel_size ** 3 (a Python float)
+  const int blocks = ceil_div(m_max, 128);
+  collision_prep_kernel<<<blocks, 128, 0, cs>>>(grasps, m_dev, m_max, fl, fw, ad, packed);
+  B200_LAUNCH_CHECK();
+  const int rc = collision_launch(scene, n_max, n_dev, packed, packed + 3, packed + 12, 22, 22, 22, m_max, m_dev,
+                                  counts, stream);
+  if (rc) return rc;
+  collision_finalize_kernel<<<blocks, 128, 0, cs>>>(grasps, counts, m_dev, m_max, fl, fw, ad, vox3, collision_thresh,
+                                                    mask);
   B200_LAUNCH_CHECK();
   return 0;
 }

@@ -24,8 +24,11 @@ constexpr int G = 17;       // floats per grasp row (models/graspnet.py:131-133)
 constexpr int RT = 256;
 
 __global__ void __launch_bounds__(RT)
-nms_rank_kernel(const float *__restrict__ grasps, int m, int32_t *__restrict__ order) {
+nms_rank_kernel(const float *__restrict__ grasps, int m, const int32_t *__restrict__ m_dev,
+                int32_t *__restrict__ order) {
   __shared__ float sc[RT];
+  if (m_dev) m = min(m, __ldg(m_dev));         // row count produced on the device (decode / compaction)
+  if ((int)(blockIdx.x * RT) >= m) return;
   const int i = blockIdx.x * RT + threadIdx.x;
   const float si = i < m ? __ldg(grasps + (size_t)i * G) : 0.f;
   int rank = 0;
@@ -44,10 +47,12 @@ nms_rank_kernel(const float *__restrict__ grasps, int m, int32_t *__restrict__ o
 }
 
 __global__ void __launch_bounds__(64)
-nms_mask_kernel(const float *__restrict__ grasps, const int32_t *__restrict__ order, int m, int W,
-                double tthr, double cthr, unsigned long long *__restrict__ mask) {
+nms_mask_kernel(const float *__restrict__ grasps, const int32_t *__restrict__ order, int m,
+                const int32_t *__restrict__ m_dev, int W, double tthr, double cthr,
+                unsigned long long *__restrict__ mask) {
   const int rb = blockIdx.y, cb = blockIdx.x;
-  if (cb < rb) return;                       // lower triangle never read by the sweep
+  if (m_dev) m = min(m, __ldg(m_dev));
+  if (cb < rb || cb * 64 >= m) return;       // lower triangle never read by the sweep; W = row stride (max rows)
   __shared__ double ct[64][3];
   __shared__ double cr[64][9];
   const int t = threadIdx.x;
@@ -94,20 +99,23 @@ constexpr int MAXW = 512;                    // 32768 grasps / 64
 // reduction -- a single memory latency per block instead of one per kept row.
 __global__ void __launch_bounds__(ST)
 nms_sweep_kernel(const unsigned long long *__restrict__ mask, const int32_t *__restrict__ order, int m,
-                 int W, int32_t *__restrict__ keep, int32_t *__restrict__ nkeep) {
+                 const int32_t *__restrict__ m_dev, int Ws, int32_t *__restrict__ keep,
+                 int32_t *__restrict__ nkeep) {
   __shared__ unsigned long long removed[MAXW];
   __shared__ unsigned long long diag[64];
   __shared__ unsigned long long s_keep;
   __shared__ int s_prefix[ST];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (m_dev) m = min(m, __ldg(m_dev));
+  const int W = (m + 63) / 64;                 // words in use; Ws = row stride of the mask
   for (int w = tid; w < W; w += ST) removed[w] = 0ull;
   unsigned long long dnext = 0ull;             // diagonal word of row (wb*64 + tid), fetched one block ahead
-  if (tid < 64 && tid < m) dnext = mask[(size_t)tid * W];
+  if (tid < 64 && tid < m) dnext = mask[(size_t)tid * Ws];
   for (int wb = 0; wb < W; ++wb) {
     if (tid < 64) {
       diag[tid] = dnext;
       const int a = (wb + 1) * 64 + tid;
-      dnext = (wb + 1 < W && a < m) ? mask[(size_t)a * W + wb + 1] : 0ull;
+      dnext = (wb + 1 < W && a < m) ? mask[(size_t)a * Ws + wb + 1] : 0ull;
     }
     __syncthreads();
     if (tid == 0) {
@@ -127,7 +135,7 @@ nms_sweep_kernel(const unsigned long long *__restrict__ mask, const int32_t *__r
     const unsigned long long kb = s_keep;
     const unsigned kbl = (unsigned)kb, kbh = (unsigned)(kb >> 32);
     const bool k0 = (kbl >> lane) & 1u, k1 = (kbh >> lane) & 1u;
-    const unsigned long long *r0 = mask + (size_t)(wb * 64 + lane) * W, *r1 = r0 + (size_t)32 * W;
+    const unsigned long long *r0 = mask + (size_t)(wb * 64 + lane) * Ws, *r1 = r0 + (size_t)32 * Ws;
     for (int w = wb + 1 + warp; w < W; w += ST / 32) {
       const unsigned long long v0 = k0 ? r0[w] : 0ull, v1 = k1 ? r1[w] : 0ull;
       const unsigned long long v = v0 | v1;
@@ -171,11 +179,10 @@ extern "C" size_t b200_grasp_nms_workspace(int m) {
   return align_up(sizeof(int32_t) * (size_t)m, 256) + align_up(8 * W, 256) + align_up(8 * W * (size_t)m, 256);
 }
 
-extern "C" int b200_grasp_nms(const float *grasps, int m, double translation_thresh,
-                              double cos_rotation_thresh, int32_t *keep, int32_t *nkeep,
-                              void *workspace, size_t workspace_bytes, void *stream) {
+static int nms_launch(const float *grasps, int m, const int32_t *m_dev, double translation_thresh,
+                      double cos_rotation_thresh, int32_t *keep, int32_t *nkeep, void *workspace,
+                      size_t workspace_bytes, cudaStream_t st) {
   if (m < 0 || !nkeep) return B200_EINVAL;
-  cudaStream_t st = (cudaStream_t)stream;
   if (m == 0) {
     B200_CUDA(cudaMemsetAsync(nkeep, 0, sizeof(int32_t), st));
     return 0;
@@ -187,15 +194,29 @@ extern "C" int b200_grasp_nms(const float *grasps, int m, double translation_thr
   char *ws = (char *)workspace;
   int32_t *order = (int32_t *)ws;
   ws += align_up(sizeof(int32_t) * (size_t)m, 256);
-  unsigned long long *removed = (unsigned long long *)ws;
-  ws += align_up(8 * (size_t)W, 256);
+  ws += align_up(8 * (size_t)W, 256);          // (formerly the removed-words scratch; kept so the layout is stable)
   unsigned long long *mask = (unsigned long long *)ws;
-  nms_rank_kernel<<<ceil_div(m, RT), RT, 0, st>>>(grasps, m, order);
+  nms_rank_kernel<<<ceil_div(m, RT), RT, 0, st>>>(grasps, m, m_dev, order);
   B200_LAUNCH_CHECK();
-  nms_mask_kernel<<<dim3((unsigned)W, (unsigned)W), 64, 0, st>>>(grasps, order, m, W, translation_thresh,
+  nms_mask_kernel<<<dim3((unsigned)W, (unsigned)W), 64, 0, st>>>(grasps, order, m, m_dev, W, translation_thresh,
                                                                 cos_rotation_thresh, mask);
   B200_LAUNCH_CHECK();
-  nms_sweep_kernel<<<1, ST, 0, st>>>(mask, order, m, W, keep, nkeep);
+  nms_sweep_kernel<<<1, ST, 0, st>>>(mask, order, m, m_dev, W, keep, nkeep);
   B200_LAUNCH_CHECK();
   return 0;
+}
+
+extern "C" int b200_grasp_nms(const float *grasps, int m, double translation_thresh,
+                              double cos_rotation_thresh, int32_t *keep, int32_t *nkeep,
+                              void *workspace, size_t workspace_bytes, void *stream) {
+  return nms_launch(grasps, m, nullptr, translation_thresh, cos_rotation_thresh, keep, nkeep, workspace,
+                    workspace_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int b200_grasp_nms_device(const float *grasps, const int32_t *m_dev, int m_max,
+                                     double translation_thresh, double cos_rotation_thresh, int32_t *keep,
+                                     int32_t *nkeep, void *workspace, size_t workspace_bytes, void *stream) {
+  if (!m_dev) return B200_EINVAL;
+  return nms_launch(grasps, m_max, m_dev, translation_thresh, cos_rotation_thresh, keep, nkeep, workspace,
+                    workspace_bytes, (cudaStream_t)stream);
 }

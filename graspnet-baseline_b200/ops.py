@@ -308,6 +308,59 @@ def pred_decode(objectness, score, angle_cls, width, tolerance, xyz, view_xyz):
     return rows, nrows
 
 
+def collision_mask_device(scene, n_dev, grasps, m_dev, voxel_size, approach_dist, collision_thresh):
+    """scene (N,3) f64 (+ n_dev (1,) i32 or None), grasps (Mmax,17) f32 of which m_dev (1,) i32 rows are valid ->
+    mask (Mmax,) u8 on the device, 1 = collides   [collision_detector.py:37-112, default return]"""
+    _chk(scene, "scene", torch.float64)
+    _chk(grasps, "grasps", torch.float32)
+    _chk(m_dev, "m_dev", torch.int32)
+    if n_dev is not None:
+        _chk(n_dev, "n_dev", torch.int32)
+    m = grasps.shape[0]
+    mask = torch.zeros((m,), dtype=torch.uint8, device=grasps.device)
+    nbytes = _lib.b200_collision_mask_workspace(m)
+    ws = torch.empty((nbytes,), dtype=torch.uint8, device=grasps.device)
+    with torch.cuda.device(grasps.device):
+        _abi.check(_lib.b200_collision_mask_device(_ptr(scene), _ptr(n_dev) if n_dev is not None else None,
+                                                   scene.shape[0], _ptr(grasps), _ptr(m_dev), m, float(voxel_size),
+                                                   float(approach_dist), float(collision_thresh), _ptr(mask), _ptr(ws),
+                                                   nbytes, _stream()), "collision_mask_device")
+    return mask
+
+
+def compact_rows(rows, drop, m_dev):
+    """rows (Mmax,C) f32, drop (Mmax,) u8, m_dev (1,) i32 -> (rows[~drop] in order, padded to Mmax; count (1,) i32)"""
+    _chk(rows, "rows", torch.float32)
+    _chk(drop, "drop", torch.uint8)
+    _chk(m_dev, "m_dev", torch.int32)
+    m, c = rows.shape
+    out = torch.empty_like(rows)
+    nout = torch.empty((1,), dtype=torch.int32, device=rows.device)
+    with torch.cuda.device(rows.device):
+        _abi.check(_lib.b200_compact_rows(_ptr(rows), c, _ptr(drop), _ptr(m_dev), m, _ptr(out), _ptr(nout), _stream()),
+                   "compact_rows")
+    return out, nout
+
+
+def grasp_nms_device(grasps, m_dev, translation_thresh, cos_rotation_thresh):
+    """grasps (Mmax,17) f32 with m_dev (1,) i32 valid rows -> (kept rows (Mmax,17) in score order, nkeep (1,) i32)"""
+    _chk(grasps, "grasps", torch.float32)
+    _chk(m_dev, "m_dev", torch.int32)
+    m = grasps.shape[0]
+    keep = torch.empty((max(m, 1),), dtype=torch.int32, device=grasps.device)
+    nkeep = torch.empty((1,), dtype=torch.int32, device=grasps.device)
+    out = torch.empty_like(grasps)
+    nbytes = _lib.b200_grasp_nms_workspace(m)
+    ws = torch.empty((nbytes,), dtype=torch.uint8, device=grasps.device)
+    with torch.cuda.device(grasps.device):
+        _abi.check(_lib.b200_grasp_nms_device(_ptr(grasps), _ptr(m_dev), m, float(translation_thresh),
+                                              float(cos_rotation_thresh), _ptr(keep), _ptr(nkeep), _ptr(ws), nbytes,
+                                              _stream()), "grasp_nms_device")
+        _abi.check(_lib.b200_gather_rows(_ptr(grasps), grasps.shape[1], _ptr(keep), _ptr(nkeep), m, _ptr(out),
+                                         _stream()), "gather_rows")
+    return out, nkeep
+
+
 def voxel_down_sample(points, voxel_size):
     """points (N,3) f64 -> (out (N,3) f64 of which the first nvox rows are valid, nvox (1,) i32), both on
     the device   [utils/collision_detector.py:32-35 -> open3d voxel_down_sample, restated]"""

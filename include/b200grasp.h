@@ -88,6 +88,28 @@ int b200_pred_decode(const float *objectness, const float *score, const float *a
                      const float *tolerance, const float *xyz, const float *view_xyz, int b, int ns,
                      int num_angle, int num_depth, float *rows, int32_t *nrows, void *stream);
 
+/* Device-resident post-processing: pred_decode's rows -> collision mask -> surviving rows -> NMS -> kept rows, with
+ * every row count read from / written to device memory (no host synchronisation between the stages).
+ *  b200_collision_mask_device: ModelFreeCollisionDetector.detect's default return (collision_detector.py:37-112) for
+ *    fp32 grasp rows [m_max,17] of which the first *m_dev are valid; mask[g] = 1 iff global_iou > collision_thresh,
+ *    with the reference's fp32 threshold / volume arithmetic.  scene as in b200_collision_counts_dn.
+ *    workspace: b200_collision_mask_workspace(m_max) bytes.
+ *  b200_compact_rows: out = rows[~drop] in order (test.py:96), *nout = how many.
+ *  b200_grasp_nms_device: b200_grasp_nms with the row count on the device; workspace b200_grasp_nms_workspace(m_max).
+ *  b200_gather_rows: out[i] = rows[index[i]] for i < *k_dev (the GraspGroup that nms() returns). */
+size_t b200_collision_mask_workspace(int m_max);
+int b200_collision_mask_device(const double *scene, const int32_t *n_dev, int n_max, const float *grasps,
+                               const int32_t *m_dev, int m_max, double voxel_size, double approach_dist,
+                               double collision_thresh, uint8_t *mask, void *workspace, size_t workspace_bytes,
+                               void *stream);
+int b200_compact_rows(const float *rows, int cols, const uint8_t *drop, const int32_t *m_dev, int m_max, float *out,
+                      int32_t *nout, void *stream);
+int b200_grasp_nms_device(const float *grasps, const int32_t *m_dev, int m_max, double translation_thresh,
+                          double cos_rotation_thresh, int32_t *keep, int32_t *nkeep, void *workspace,
+                          size_t workspace_bytes, void *stream);
+int b200_gather_rows(const float *rows, int cols, const int32_t *index, const int32_t *k_dev, int k_max, float *out,
+                     void *stream);
+
 /* Grid-accelerated forms of b200_ball_query / b200_cylinder_query_multi: identical results (the first
  * nsample hits IN INDEX ORDER, padded with the first hit, zeros if none), but the cloud is first binned
  * into a uniform grid held in `workspace` (b200_query_grid_workspace(b, n) bytes of device memory, no

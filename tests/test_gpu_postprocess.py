@@ -1,0 +1,83 @@
+"""Device-resident decode -> collision -> NMS chain against the call sequence of the reference-facing drop-ins
+(which are themselves pinned to the oracle / golden vectors): same collision mask, same kept rows (bit-exact)."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def make_grasps(b200, cloud, m, seed):
+    rng = np.random.default_rng(seed)
+    g = np.zeros((m, 17), np.float32)
+    g[:, 0] = rng.uniform(0, 1, m)
+    g[:, 1] = rng.uniform(0, 0.1, m)
+    g[:, 2] = 0.02
+    g[:, 3] = rng.integers(1, 5, m) * np.float32(0.01)
+    g[:, 4:13] = b200.synth.seed_rotations(m, seed + 7).reshape(m, 9)
+    g[:, 13:16] = cloud[rng.choice(len(cloud), m, replace=len(cloud) < m)]
+    k = m // 3                                                          # crowds for NMS to thin out:
+    g[:k, 13:16] = g[k:2 * k, 13:16] + rng.normal(0, 0.004, (k, 3)).astype(np.float32)
+    g[:k, 4:13] = g[k:2 * k, 4:13]                                      # a third of the grasps shadow another one
+    g[:, 16] = -1
+    return g
+
+
+@pytest.mark.parametrize("n,m,pad,voxel,ad,thr", [(20000, 1024, 0, 0.01, 0.05, 0.01), (6000, 300, 212, 0.005, 0.03, 0.05),
+                                                  (3000, 64, 0, 0.01, 0.005, 0.01), (500, 5, 3, 0.01, 0.05, 0.2),
+                                                  (800, 0, 4, 0.01, 0.05, 0.01)])
+def test_device_chain_equals_dropin_sequence(b200, oracle_mod, n, m, pad, voxel, ad, thr):
+    cloud = b200.synth.tabletop_cloud(n, 100 + n)
+    g = make_grasps(b200, cloud, max(m, 1), n + m)[:m]
+    # the drop-in sequence (numpy in / numpy out), as test.py:94-96 + gg.nms()
+    det = b200.ModelFreeCollisionDetector(cloud, voxel_size=voxel)
+    gg = b200.GraspGroup(g.copy())
+    want_mask = det.detect(gg, approach_dist=ad, collision_thresh=thr) if m else np.zeros(0, bool)
+    want = gg[~want_mask].nms().grasp_group_array if m else np.zeros((0, 17), np.float32)
+    # and the oracle's mask for the same voxelised scene
+    if m:
+        scene = oracle_mod.voxel_down_sample(np.asarray(cloud, np.float64), voxel)
+        assert (oracle_mod.collision_detect(scene, g, voxel, ad, thr) == want_mask).all()
+    # device chain on rows padded with garbage beyond the valid count
+    rows = np.concatenate([g, np.full((pad, 17), np.nan, np.float32)]) if pad else g
+    rows_d = torch.from_numpy(np.ascontiguousarray(rows)).cuda() if len(rows) else torch.zeros((0, 17), device="cuda")
+    nrows = torch.full((1,), m, dtype=torch.int32, device="cuda")
+    if len(rows) == 0:
+        return
+    kept, nkept, mask = b200.grasp_postprocess_device(torch.from_numpy(cloud).cuda(), rows_d, nrows, voxel, ad, thr)
+    k = int(nkept.item())
+    assert (mask[:m].cpu().numpy().astype(bool) == want_mask).all()
+    got = kept[:k].cpu().numpy()
+    assert got.shape == want.shape and (got == want).all()
+    if m:
+        assert (b200.grasp_postprocess(cloud, g, voxel, ad, thr) == want).all()
+
+
+def test_decode_then_postprocess_on_device(b200, oracle_mod):
+    """pred_decode_device feeding the chain without a host round trip == oracle decode -> drop-in sequence."""
+    rng = np.random.default_rng(5)
+    ns, a, d = 1024, 12, 4
+    f = np.float32
+    cloud = b200.synth.tabletop_cloud(20000, 9)
+    heads = [rng.standard_normal((1, 2, ns)).astype(f), (rng.random((1, a, ns, d)) * 1.2 - 0.1).astype(f),
+             rng.standard_normal((1, a, ns, d)).astype(f), (rng.random((1, a, ns, d)) * 0.12 - 0.01).astype(f),
+             (rng.random((1, a, ns, d)) * 0.06).astype(f), cloud[None, :ns].copy()]
+    v = rng.standard_normal((1, ns, 3)).astype(f)
+    v[..., 2] = -np.abs(v[..., 2]) - 0.3                        # views from above the table
+    heads.append(v)
+    keys = ("objectness_score", "grasp_score_pred", "grasp_angle_cls_pred", "grasp_width_pred", "grasp_tolerance_pred",
+            "fp2_xyz", "grasp_top_view_xyz")
+    ep = {k: torch.from_numpy(h).cuda() for k, h in zip(keys, heads)}
+    rows, nrows = b200.pred_decode_device(ep)
+    kept, nkept, mask = b200.grasp_postprocess_device(torch.from_numpy(cloud).cuda(), rows[0], nrows[0:1])
+    m = int(nrows[0].item())
+    g = rows[0, :m].cpu().numpy()                              # the decoded rows (checked against the oracle elsewhere)
+    det = b200.ModelFreeCollisionDetector(cloud, voxel_size=0.01)
+    gg = b200.GraspGroup(g)
+    want_mask = det.detect(gg, approach_dist=0.05, collision_thresh=0.01)
+    want = gg[~want_mask].nms().grasp_group_array
+    assert (mask[:m].cpu().numpy().astype(bool) == want_mask).all()
+    assert (kept[: int(nkept.item())].cpu().numpy() == want).all()
+    assert 0 < len(want) < m
