@@ -23,6 +23,8 @@ CYL = dict(radius=0.05, hmin=-0.02, hmax_list=[0.01, 0.02, 0.03, 0.04], nsample=
 # cell edge of the one uniform grid that serves SA1's ball query (bounding radius 0.04) and CloudCrop's cylinder
 # query (0.064); any value gives the same lists, 0.026 was the fastest of a sweep (profiles/r01_query_grid.txt)
 GRID_CELL = 0.026
+POST = dict(approach_dist=0.05, collision_thresh=0.01, translation_thresh=0.03,      # test.py:95, GraspGroup.nms()
+            rotation_thresh=30.0 / 180.0 * math.pi)
 POST_STREAMS = 16         # streams the per-scene collision + NMS launches of a batch are spread over
 
 
@@ -57,32 +59,30 @@ class GeometryScene:
 
     # ---- inputs a caller would hand over from the host
     def make_host_inputs(self, seed):
-        from .voxel import voxel_down_sample
         h = {"cloud": np.stack([synth.tabletop_cloud(self.N, seed + s) for s in range(self.B)])}
         nseed = self.sa_cfg[1][0]
         h["rot"] = np.stack([synth.seed_rotations(nseed, seed + s) for s in range(self.B)])
         h["grasps"] = [synth.synthetic_grasps(h["cloud"][s], self.M, seed + s) for s in range(self.B)]
-        h["scene64"] = [voxel_down_sample(h["cloud"][s], self.voxel_size, self.dev) for s in range(self.B)]
         return h
 
     def upload(self):
         h, d = self.host, self.dev
         self.cloud = torch.from_numpy(h["cloud"]).to(d)
         self.rot = torch.from_numpy(h["rot"]).to(d)
+        # grasp rows as pred_decode leaves them: a padded (M,17) buffer and its row count, both on the device
         self.grasps = [torch.from_numpy(g).to(d) for g in h["grasps"]]
-        self.scene64 = [torch.from_numpy(s).to(d) for s in h["scene64"]]
-        self.coll_in = [self.collision_inputs(g) for g in h["grasps"]]
+        self.ngrasp = [torch.full((1,), g.shape[0], dtype=torch.int32, device=d) for g in h["grasps"]]
 
-    def collision_inputs(self, g, approach_dist=0.05):
-        """T, R, thr (fp64, device) for one scene's grasp rows -- the host half of detect()."""
-        from .collision_detector import ModelFreeCollisionDetector as D
-        from .grasp import GraspGroup
-        det = D.__new__(D)
-        det.finger_width, det.finger_length = 0.01, 0.06
-        gg = GraspGroup(g)
-        thr = det._thresholds(gg, max(approach_dist, 0.01))
-        f = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(self.dev)
-        return f(gg.translations), f(gg.rotation_matrices.reshape(-1, 9)), f(thr)
+    def post_scene(self, s):
+        """decode's rows of scene s -> voxel down-sample of its cloud, collision mask, surviving rows, NMS: the
+        device-resident form of test.py:94-96 + GraspGroup.nms() (postprocess.py)."""
+        voxel = self._op('voxel', ops.voxel_down_sample, self.cloud[s].double(), self.voxel_size)
+        mask = self._op('collision', ops.collision_mask_device, voxel[0], voxel[1], self.grasps[s], self.ngrasp[s],
+                        self.voxel_size, POST["approach_dist"], POST["collision_thresh"])
+        free = self._op('compact', ops.compact_rows, self.grasps[s], mask, self.ngrasp[s])
+        kept = self._op('nms', ops.grasp_nms_device, free[0], free[1], POST["translation_thresh"],
+                        math.cos(POST["rotation_thresh"]))
+        return mask, kept
 
     # ---- optional per-op CUDA-event timing (bench.py's roofline pass)
     def _op(self, name, fn, *args, **kw):
@@ -139,7 +139,7 @@ class GeometryScene:
         hold = []
         # post-processing: independent of the backbone; per-scene launches (the NMS sweep is a one-CTA
         # serial chain) are dealt round-robin over a few streams so that scenes of a batch overlap
-        counts, keeps = [None] * B, [None] * B
+        masks, keeps = [None] * B, [None] * B
         if post:
             if self._post_streams is None:
                 self._post_streams = [s_p] + [torch.cuda.Stream(device=self.dev) for _ in range(min(B, POST_STREAMS) - 1)]
@@ -147,10 +147,8 @@ class GeometryScene:
                 after(sp, main)
             for s in range(B):
                 with torch.cuda.stream(self._post_streams[s % len(self._post_streams)]):
-                    T, R, thr = self.coll_in[s]
-                    counts[s] = ops.collision_counts(self.scene64[s], T, R, thr)
-                    keeps[s] = ops.grasp_nms(self.grasps[s], 0.03, math.cos(30.0 / 180.0 * math.pi))
-            out["collision_counts"], out["nms"] = counts, keeps
+                    masks[s], keeps[s] = self.post_scene(s)
+            out["collision_mask"], out["kept"] = masks, keeps
         after(s_c, main)
         with torch.cuda.stream(s_c):
             cloud_t = self.cloud.transpose(1, 2).contiguous()
@@ -205,13 +203,13 @@ class GeometryScene:
     def run(self):
         out = self.run_geometry()
         L = self.launches
-        counts, keeps = [], []
+        masks, keeps = [], []
         for s in range(self.B):
-            T, R, thr = self.coll_in[s]
-            counts.append(self._op('collision', ops.collision_counts, self.scene64[s], T, R, thr))
-            keeps.append(self._op('nms', ops.grasp_nms, self.grasps[s], 0.03, math.cos(30.0 / 180.0 * math.pi)))
-            L += 1 + 3
-        out["collision_counts"], out["nms"] = counts, keeps
+            mask, kept = self.post_scene(s)
+            masks.append(mask)
+            keeps.append(kept)
+            L += 7 + 3 + 1 + 4
+        out["collision_mask"], out["kept"] = masks, keeps
         self.launches = L
         return out
 

@@ -70,6 +70,6 @@ def test_cfg3_batch64_equals_scene_by_scene(b200):
         for key in ("sa1_inds", "sa2_inds", "sa4_inds", "sa1_idx", "sa3_idx", "fp2_idx", "sa2_grouped_feat", "fp1_interp"):
             assert torch.equal(out[key][s], ref[key][0]), (s, key)
         assert torch.equal(out["crop_idx"][:, s], ref["crop_idx"][:, 0])
-        assert torch.equal(out["collision_counts"][s], ref["collision_counts"][0])
-        (k1, n1), (k2, n2) = out["nms"][s], ref["nms"][0]
+        assert torch.equal(out["collision_mask"][s], ref["collision_mask"][0])
+        (k1, n1), (k2, n2) = out["kept"][s], ref["kept"][0]
         assert int(n1.item()) == int(n2.item()) and torch.equal(k1[: int(n1.item())], k2[: int(n2.item())])
