@@ -279,38 +279,27 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- e2e: host buffers in, host results out, every step
     host = sc.host
-    pin = {k: torch.from_numpy(host[k]).pin_memory() for k in ("cloud", "rot")}
-    pin_g = torch.from_numpy(host["grasps"][0]).pin_memory()
-    pin_n = torch.tensor([host["grasps"][0].shape[0]], dtype=torch.int32).pin_memory()
-    M = host["grasps"][0].shape[0]
-    res = {"seeds": torch.empty((1, SA_CFG[1][0]), dtype=torch.int32).pin_memory(),
-           "mask": torch.empty((M,), dtype=torch.uint8).pin_memory(),
-           "kept": torch.empty((M, 17), dtype=torch.float32).pin_memory(),
-           "nkept": torch.empty((1,), dtype=torch.int32).pin_memory()}
-    h2d = sum(t.numel() * t.element_size() for t in (pin["cloud"], pin["rot"], pin_g, pin_n))
-    d2h = sum(t.numel() * t.element_size() for t in res.values())
+    pin_in = sc.host_io_in(pinned=True)                     # cloud | seed rotations | grasp rows | row count
+    pin_out = torch.zeros(sc.io_out.numel(), dtype=torch.uint8).pin_memory()
+    res = sc.io_views(pin_out, "out")                       # seed indices | collision mask | kept rows | kept count
+    h2d, d2h = pin_in.numel(), pin_out.numel()
 
     def e2e_step():
-        # pinned host buffers -> the graph's static inputs -> ONE graph launch (geometry + voxel down-sample +
-        # collision mask + compaction + NMS, all device-resident) -> results into pinned host buffers
-        sc.cloud.copy_(pin["cloud"], non_blocking=True)
-        sc.rot.copy_(pin["rot"], non_blocking=True)
-        sc.grasps[0].copy_(pin_g, non_blocking=True)
-        sc.ngrasp[0].copy_(pin_n, non_blocking=True)
-        out = sc.run_graph()
-        kept, nkept = out["kept"][0]
-        res["seeds"].copy_(out["sa2_inds"], non_blocking=True)
-        res["mask"].copy_(out["collision_mask"][0], non_blocking=True)
-        res["kept"].copy_(kept, non_blocking=True)
-        res["nkept"].copy_(nkept, non_blocking=True)
+        # one pinned host buffer -> the graph's static inputs -> ONE graph launch (geometry + voxel down-sample +
+        # collision mask + compaction + NMS, all device-resident) -> one pinned host buffer of results
+        sc.io_in.copy_(pin_in, non_blocking=True)
+        sc.run_graph()
+        pin_out.copy_(sc.io_out, non_blocking=True)
         torch.cuda.current_stream().synchronize()           # the caller reads the results now
-        return res["kept"][: int(res["nkept"][0])], res["mask"]
+        return res["kept0"][: int(res["nkept0"][0])], res["mask0"]
 
     e2e_ms = timed(e2e_step, args.steps, args.warmup)
 
     # the same scene through the numpy-in / numpy-out drop-ins, called one after the other as test.py:94-96 does
     # (detector rebuilt per scene), on a second stream beside the geometry graph: reported for comparison
     side = torch.cuda.Stream(device=dev)
+
+    pin = {k: torch.from_numpy(host[k]).pin_memory() for k in ("cloud", "rot")}
 
     def dropin_step():
         sc.cloud.copy_(pin["cloud"], non_blocking=True)
@@ -421,9 +410,10 @@ def run_ours(args, rank, world, local_rank):
             "clocks": clk, "gpu_launches": launches * args.steps,
             "e2e": {"value": round(e2e, 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": round(e2e_ms / args.steps, 4),
-                    "api": "GeometryScene.run_graph(): pinned host buffers copied into the graph's static inputs, one "
-                           "graph launch (geometry + voxel + collision + NMS on the device), results copied to pinned "
-                           "host buffers, stream synchronised",
+                    "api": "GeometryScene.run_graph(): one pinned host buffer (cloud | rotations | grasp rows) copied "
+                           "into the graph's static inputs, one graph launch (geometry + voxel + collision + NMS on "
+                           "the device), one copy of the results (seeds | mask | kept rows) to pinned host memory, "
+                           "stream synchronised",
                     "dropin_calls_ms_per_step": round(dropin_ms / args.steps, 4)},
             "roofline": roof, "legacy_cuda": legacy, "batch64": batch64, "kernels": kern}
     return line

@@ -66,12 +66,60 @@ class GeometryScene:
         return h
 
     def upload(self):
+        """Host inputs -> static device buffers.  All of a step's inputs live in ONE device allocation (`io_in`) and
+        all of its host-bound results in another (`io_out`), so a caller moves each with a single copy:
+        io_in  = cloud (B,N,3) f32 | rot (B,S,3,3) f32 | per scene: grasp rows (M,17) f32, row count i32
+        io_out = seed indices (B,S) i32 | per scene: collision mask (M) u8, kept rows (M,17) f32, kept count i32
+        (every segment 256-byte aligned; `io_views` maps names to typed views of either buffer or of a host copy)."""
         h, d = self.host, self.dev
-        self.cloud = torch.from_numpy(h["cloud"]).to(d)
-        self.rot = torch.from_numpy(h["rot"]).to(d)
-        # grasp rows as pred_decode leaves them: a padded (M,17) buffer and its row count, both on the device
-        self.grasps = [torch.from_numpy(g).to(d) for g in h["grasps"]]
-        self.ngrasp = [torch.full((1,), g.shape[0], dtype=torch.int32, device=d) for g in h["grasps"]]
+        B, N, M, S = self.B, self.N, self.M, self.sa_cfg[1][0]
+        self._in_layout = [("cloud", np.float32, (B, N, 3)), ("rot", np.float32, tuple(h["rot"].shape))]
+        for s in range(B):
+            self._in_layout += [("grasps%d" % s, np.float32, (M, 17)), ("ngrasp%d" % s, np.int32, (1,))]
+        self._out_layout = [("seeds", np.int32, (B, S))]
+        for s in range(B):
+            self._out_layout += [("mask%d" % s, np.uint8, (M,)), ("kept%d" % s, np.float32, (M, 17)),
+                                 ("nkept%d" % s, np.int32, (1,))]
+        self.io_in = torch.zeros(self._io_bytes(self._in_layout), dtype=torch.uint8, device=d)
+        self.io_out = torch.zeros(self._io_bytes(self._out_layout), dtype=torch.uint8, device=d)
+        vin = self.io_views(self.io_in, "in")
+        self.cloud, self.rot = vin["cloud"], vin["rot"]
+        self.grasps = [vin["grasps%d" % s] for s in range(B)]
+        self.ngrasp = [vin["ngrasp%d" % s] for s in range(B)]
+        self._out_views = self.io_views(self.io_out, "out")
+        self.io_in.copy_(self.host_io_in())
+
+    @staticmethod
+    def _io_bytes(layout):
+        off = 0
+        for _, dt, shape in layout:
+            off += (int(np.prod(shape)) * np.dtype(dt).itemsize + 255) // 256 * 256
+        return off
+
+    def io_views(self, buf, which):
+        """name -> typed view of `buf` (a uint8 torch tensor on any device, or a uint8 numpy array)"""
+        layout = self._in_layout if which == "in" else self._out_layout
+        tdt = {np.float32: torch.float32, np.int32: torch.int32, np.uint8: torch.uint8}
+        views, off = {}, 0
+        for name, dt, shape in layout:
+            nb = int(np.prod(shape)) * np.dtype(dt).itemsize
+            seg = buf[off: off + nb]
+            views[name] = seg.view(tdt[dt]).view(shape) if isinstance(buf, torch.Tensor) else seg.view(dt).reshape(shape)
+            off += (nb + 255) // 256 * 256
+        return views
+
+    def host_io_in(self, pinned=False):
+        """The step's inputs as one host buffer in the io_in layout (a caller fills such a buffer per scene)."""
+        buf = torch.zeros(self.io_in.numel(), dtype=torch.uint8)
+        if pinned:
+            buf = buf.pin_memory()
+        v = self.io_views(buf, "in")
+        v["cloud"].copy_(torch.from_numpy(self.host["cloud"]))
+        v["rot"].copy_(torch.from_numpy(self.host["rot"]))
+        for s, g in enumerate(self.host["grasps"]):
+            v["grasps%d" % s].copy_(torch.from_numpy(g))
+            v["ngrasp%d" % s].fill_(g.shape[0])
+        return buf
 
     def post_scene(self, s):
         """decode's rows of scene s -> voxel down-sample of its cloud, collision mask, surviving rows, NMS: the
@@ -196,6 +244,14 @@ class GeometryScene:
                 out[name + "_idx"] = idx3
                 out[name + "_interp"] = ops.three_interpolate(self.feat[name + "_known"], idx3, w)
         after(main, s_q, s_c, s_f, *(self._post_streams if post else []))
+        if post:                                      # host-bound results into the one output buffer
+            ov = self._out_views
+            ov["seeds"].copy_(out["sa2_inds"])
+            for s in range(B):
+                ov["mask%d" % s].copy_(masks[s])
+                ov["kept%d" % s].copy_(keeps[s][0])
+                ov["nkept%d" % s].copy_(keeps[s][1])
+            self.glue += 1 + 3 * B
         self._hold = hold
         return out
 
