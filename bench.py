@@ -120,37 +120,61 @@ def time_cpu(steps, warmup):
 # ---------------------------------------------------------------- clocks sampler
 
 class Clocks(threading.Thread):
+    """SM clock + throttle reasons sampled WHILE the timed regions run: NVML in-process (a query costs well under
+    a millisecond, so even a 10 ms region is seen several times), nvidia-smi as the fallback."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    BITS = {"sw_power_cap": 0x4, "hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40}
 
-    def __init__(self, index):
+    def __init__(self, index, uuid=None):
         super().__init__(daemon=True)
-        self.index, self.rows, self.stop_flag = index, [], False
+        self.index, self.stop_flag = index, False
+        self.sm, self.mx, self.reasons, self.source = [], [], set(), "nvidia-smi"
+        self.nvml = self.handle = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            try:
+                self.handle = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(uuid)) if uuid else "")
+            except Exception:
+                self.handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.mx.append(float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM)))
+            self.nvml, self.source = pynvml, "nvml"
+        except Exception:
+            self.nvml = None
+
+    def sample(self):
+        if self.nvml is not None:
+            n = self.nvml
+            self.sm.append(float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)))
+            try:
+                mask = n.nvmlDeviceGetCurrentClocksEventReasons(self.handle)
+            except Exception:
+                mask = n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+            self.reasons |= {k for k, bit in self.BITS.items() if mask & bit}
+            return
+        o = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                            "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+        r = [c.strip() for c in o.strip().split(",")]
+        self.sm.append(float(r[0])); self.mx.append(float(r[1]))
+        for nme, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[2:6]):
+            if v.lower().startswith("active"):
+                self.reasons.add(nme)
 
     def run(self):
         while not self.stop_flag:
             try:
-                o = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                    "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                self.rows.append([c.strip() for c in o.strip().split(",")])
+                self.sample()
             except Exception:
                 pass
-            time.sleep(0.1)
+            time.sleep(0.001 if self.nvml is not None else 0.1)
 
     def summary(self):
         self.stop_flag = True
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            try:
-                sm.append(float(r[0])); mx.append(float(r[1]))
-                for nme, v in zip(names, r[2:6]):
-                    if v.lower().startswith("active"):
-                        reasons.add(nme)
-            except Exception:
-                pass
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        self.join(timeout=6)
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None,
+                "sm_max_mhz": max(self.mx) if self.mx else None,
+                "reasons": sorted(self.reasons), "samples": len(self.sm), "source": self.source}
 
 
 # per-launch DRAM bytes from the committed ncu --set full capture (profiles/r01_top_kernels_full.txt)
@@ -268,7 +292,14 @@ def run_ours(args, rank, world, local_rank):
 
     sc.run_graph()                                          # capture (untimed, once)
     torch.cuda.synchronize()
-    clocks = Clocks(local_rank); clocks.start()
+    try:
+        uuid = torch.cuda.get_device_properties(dev).uuid
+    except Exception:
+        uuid = None
+    clocks = Clocks(local_rank, uuid)
+    for _ in range(args.warmup):
+        sc.run_graph()
+    clocks.start()                                          # samples only while the timed region below runs
     total_ms = timed(sc.run_graph, args.steps, args.warmup)
     clk = clocks.summary()
     launches = sc.launches                                  # our kernels per step (library counter at capture)

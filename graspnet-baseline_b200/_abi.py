@@ -41,6 +41,9 @@ SIGNATURES = {
     "b200_compact_rows": [_vp, _i, _vp, _vp, _i, _vp, _vp, _vp],
     "b200_grasp_nms_device": [_vp, _vp, _i, _d, _d, _vp, _vp, _vp, _sz, _vp],
     "b200_gather_rows": [_vp, _i, _vp, _vp, _i, _vp, _vp],
+    "b200_fps_prefix_check": [_vp, _i, _i, _i, ctypes.c_longlong, _vp, _vp],
+    "b200_furthest_point_sampling_spec": [_vp, _i, _i, _i, _vp, _i, _vp, _i, _vp, _i, _vp, _vp],
+    "b200_gather_xyz": [_vp, _vp, _i, _i, _i, _vp, _vp, _vp],
     "b200_pred_decode": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp],
     "b200_ball_query_grid": [_vp, _vp, _i, _i, _i, _f, _i, _vp, _vp, _sz, _vp],
     "b200_cylinder_query_multi_grid": [_vp, _vp, _vp, _i, _i, _i, _f, _f, ctypes.POINTER(_f), _i, _i, _vp, _vp, _sz, _vp],

@@ -63,7 +63,7 @@ constexpr int TAB_LIMIT = 200 * 1024;   // bytes of shared memory the per-CTA po
 // ET > 0: cluster of C CTAs, C * NW <= 32 * ET entries, ET per lane in the select stage.
 template <int PP, int NT, int ET>
 __global__ void __launch_bounds__(NT, 1)
-fps_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, int spec, int32_t *idx) {
+fps_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, FpsVerdicts spec, int32_t *idx) {
   constexpr bool CLUSTER = ET > 0;
   constexpr int PPT = 2 * PP;
   constexpr int NW = NT / 32;
@@ -98,7 +98,7 @@ fps_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, int spe
   // Speculative mode: the prefix-check kernels below left out[0] == 0 iff the answer is the
   // identity permutation (the input is already in furthest-point order); then nothing is left
   // to do but write it.  The test is uniform over the cluster, so every CTA leaves together.
-  if (spec && out[0] == 0) {
+  if (fps_identity(spec, cloud)) {
     if (rank == 0)
       for (int j = tid; j < m; j += NT) out[j] = j;
     return;
@@ -364,7 +364,7 @@ fps_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, int spe
 }
 
 template <int PP, int NT, int ET>
-int launch(const float *xyz, int b, int n, int m, int C, int bits, int spec, int32_t *idx, cudaStream_t st) {
+int launch(const float *xyz, int b, int n, int m, int C, int bits, FpsVerdicts spec, int32_t *idx, cudaStream_t st) {
   constexpr int tab_bytes = (2 * PP * NT * 16 <= TAB_LIMIT) ? 2 * PP * NT * 16 : 0;
   auto kern = fps_kernel<PP, NT, ET>;
   static bool configured = false;                  // per instantiation
@@ -397,7 +397,7 @@ int launch(const float *xyz, int b, int n, int m, int C, int bits, int spec, int
 }
 
 template <int PP, int NT>
-int launch_et(const float *xyz, int b, int n, int m, int C, int bits, int spec, int32_t *idx, cudaStream_t st) {
+int launch_et(const float *xyz, int b, int n, int m, int C, int bits, FpsVerdicts spec, int32_t *idx, cudaStream_t st) {
   const int E = C * (NT / 32);
   if (C == 1) return launch<PP, NT, 0>(xyz, b, n, m, C, bits, spec, idx, st);
   if (E <= 32) return launch<PP, NT, 1>(xyz, b, n, m, C, bits, spec, idx, st);
@@ -425,10 +425,10 @@ constexpr int SPEC_MAX_N = 4096;
 // D_j = min(1e10, min_{i<j} |p_j - p_i|^2) for 1 <= j < m.  Eight lanes per j, each takes every
 // eighth i; min is order-independent, so the result equals the chain's running minimum.
 __global__ void __launch_bounds__(SPEC_NT)
-fps_prefix_dist_kernel(const float *__restrict__ xyz, int n, int m, int32_t *__restrict__ idx) {
+fps_prefix_dist_kernel(const float *__restrict__ xyz, long long cstride, int n, int m, int32_t *__restrict__ idx) {
   __shared__ float4 sel[SPEC_MAX_M];
   const int cloud = blockIdx.y;
-  const float *p = xyz + (size_t)cloud * n * 3;
+  const float *p = xyz + (size_t)cloud * cstride * 3;           // clouds are `cstride` points apart (>= n)
   int32_t *out = idx + (size_t)cloud * m;
   const int sub = threadIdx.x & (SPEC_SUB - 1);
   const int j = blockIdx.x * SPEC_PTS + (threadIdx.x >> 3);
@@ -455,10 +455,10 @@ fps_prefix_dist_kernel(const float *__restrict__ xyz, int n, int m, int32_t *__r
 // min-distance at the start of each range; pass 2 walks the range again comparing with D_j.
 // A violation (k would have been picked instead of j) or a skipped j clears the verdict.
 __global__ void __launch_bounds__(SPEC_NT)
-fps_prefix_check_kernel(const float *__restrict__ xyz, int n, int m, int bits, int32_t *idx) {
+fps_prefix_check_kernel(const float *__restrict__ xyz, long long cstride, int n, int m, int bits, int32_t *idx) {
   __shared__ float4 sel[SPEC_MAX_M];                            // x, y, z of point j, D_j in .w
   const int cloud = blockIdx.y;
-  const float *p = xyz + (size_t)cloud * n * 3;
+  const float *p = xyz + (size_t)cloud * cstride * 3;
   int32_t *out = idx + (size_t)cloud * m;
   bool bad = false;
   for (int j = threadIdx.x; j < m; j += SPEC_NT) {
@@ -523,6 +523,10 @@ int round_ppt(int want, int nt) {
   return 0;
 }
 
+bool spec_eligible(int b, int n, int m) {
+  return m >= 2 && m <= n && m <= SPEC_MAX_M && n <= SPEC_MAX_N && b <= 65535;
+}
+
 int g_force_cluster = 0, g_force_threads = 0, g_spec_enabled = 1, g_multi_enabled = 1;
 
 // Largest cluster size the device will co-schedule for this kernel family (16 needs the
@@ -564,8 +568,9 @@ extern "C" int b200_fps_read_profile(unsigned long long *out5) {
 }
 #endif
 
-extern "C" int b200_furthest_point_sampling(const float *xyz, int b, int n, int m, int32_t *idx,
-                                            void *stream) {
+// `ext` != nullptr: the caller ran b200_fps_prefix_check ahead of time (possibly for ancestor levels too) and the
+// shortcut is decided by those verdicts; nullptr: the check is run here when the shape allows it
+static int fps_impl(const float *xyz, int b, int n, int m, const FpsVerdicts *ext, int32_t *idx, void *stream) {
   if (b < 0 || m < 0 || n < 0) return B200_EINVAL;
   if (b == 0 || m == 0) return 0;
   if (n <= 0 || !xyz || !idx) return B200_EINVAL;
@@ -609,12 +614,16 @@ extern "C" int b200_furthest_point_sampling(const float *xyz, int b, int n, int 
   const int ppt = round_ppt(blocks * 512 / NT, NT);
   if (ppt == 0) return B200_ECAPACITY;
   // small clouds may be FPS-ordered already (SA2..SA4): decide that first, flat and parallel
-  const int spec = (g_spec_enabled && m >= 2 && m <= n && m <= SPEC_MAX_M && n <= SPEC_MAX_N && b <= 65535) ? 1 : 0;
-  if (spec) {
-    fps_prefix_dist_kernel<<<dim3((unsigned)ceil_div(m, SPEC_PTS), (unsigned)b), SPEC_NT, 0, st>>>(xyz, n, m, idx);
+  FpsVerdicts spec = {{nullptr, nullptr, nullptr}, {0, 0, 0}};
+  if (ext) {
+    spec = *ext;
+  } else if (g_spec_enabled && spec_eligible(b, n, m)) {
+    fps_prefix_dist_kernel<<<dim3((unsigned)ceil_div(m, SPEC_PTS), (unsigned)b), SPEC_NT, 0, st>>>(xyz, n, n, m, idx);
     B200_LAUNCH_CHECK();
-    fps_prefix_check_kernel<<<dim3((unsigned)ceil_div(n, SPEC_PTS), (unsigned)b), SPEC_NT, 0, st>>>(xyz, n, m, bits, idx);
+    fps_prefix_check_kernel<<<dim3((unsigned)ceil_div(n, SPEC_PTS), (unsigned)b), SPEC_NT, 0, st>>>(xyz, n, n, m, bits, idx);
     B200_LAUNCH_CHECK();
+    spec.p[0] = idx;                                            // verdict of cloud c in idx[c * m]
+    spec.stride[0] = m;
   }
   if (g_multi_enabled && C >= 2) {                              // several samples per exchange where covered
     const int rc = b200_fps_multi_launch(xyz, b, n, m, C, NT, ppt, bits, spec, idx, st);
@@ -630,4 +639,39 @@ extern "C" int b200_furthest_point_sampling(const float *xyz, int b, int n, int 
   FPS_CASE(32, 128) FPS_CASE(40, 128) FPS_CASE(48, 128)
 #undef FPS_CASE
   return B200_ECAPACITY;
+}
+
+extern "C" int b200_furthest_point_sampling(const float *xyz, int b, int n, int m, int32_t *idx,
+                                            void *stream) {
+  return fps_impl(xyz, b, n, m, nullptr, idx, stream);
+}
+
+extern "C" int b200_fps_prefix_check(const float *xyz, int b, int n, int m, long long cloud_stride,
+                                     int32_t *verdict, void *stream) {
+  if (b < 0 || n < 0 || m < 0 || cloud_stride < n) return B200_EINVAL;
+  if (b == 0 || m == 0) return 0;
+  if (!xyz || !verdict || n == 0) return B200_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!g_spec_enabled || !spec_eligible(b, n, m)) {             // undecidable here: "run the chain" for every cloud
+    B200_CUDA(cudaMemsetAsync(verdict, 0xff, sizeof(int32_t) * (size_t)b * m, st));
+    return 0;
+  }
+  int bs = 1, bits = 0;
+  while (bs * 2 <= n && bs < 512) { bs *= 2; ++bits; }
+  fps_prefix_dist_kernel<<<dim3((unsigned)ceil_div(m, SPEC_PTS), (unsigned)b), SPEC_NT, 0, st>>>(xyz, cloud_stride, n, m,
+                                                                                               verdict);
+  B200_LAUNCH_CHECK();
+  fps_prefix_check_kernel<<<dim3((unsigned)ceil_div(n, SPEC_PTS), (unsigned)b), SPEC_NT, 0, st>>>(xyz, cloud_stride, n,
+                                                                                                m, bits, verdict);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200_furthest_point_sampling_spec(const float *xyz, int b, int n, int m, const int32_t *verdict0,
+                                                 int stride0, const int32_t *verdict1, int stride1,
+                                                 const int32_t *verdict2, int stride2, int32_t *idx, void *stream) {
+  // the chain of verdicts must start at slot 0 (fps_identity treats an empty slot 0 as "no shortcut")
+  FpsVerdicts v = {{verdict0, verdict0 ? verdict1 : nullptr, (verdict0 && verdict1) ? verdict2 : nullptr},
+                   {stride0, stride1, stride2}};
+  return fps_impl(xyz, b, n, m, &v, idx, stream);
 }

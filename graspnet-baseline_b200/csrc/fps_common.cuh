@@ -5,7 +5,23 @@
 
 // fps_multi.cu: several samples per cluster exchange.  Returns B200_ECAPACITY when (C, NT, ppt) is not one of
 // its instantiations; b200_furthest_point_sampling then runs the one-sample-per-step chain kernel of fps.cu.
-int b200_fps_multi_launch(const float *xyz, int b, int n, int m, int C, int NT, int ppt, int bits, int spec,
+// Where the speculative prefix check left its verdicts (0 = "the answer is the identity permutation"): up to three
+// arrays, entry [cloud * stride]; ALL of them must say 0 for the shortcut.  The plain entry point keeps its single
+// verdict in idx[cloud * m]; the *_spec entry point takes verdicts computed ahead of time (also for ancestors: a
+// level's input is only the prefix the check looked at if the level above returned the identity too).
+struct FpsVerdicts {
+  const int32_t *p[3];
+  int stride[3];
+};
+__device__ __forceinline__ bool fps_identity(const FpsVerdicts &v, int cloud) {
+  bool ok = v.p[0] != nullptr;
+#pragma unroll
+  for (int k = 0; k < 3; ++k)
+    if (v.p[k]) ok = ok && (v.p[k][(size_t)cloud * v.stride[k]] == 0);
+  return ok;
+}
+
+int b200_fps_multi_launch(const float *xyz, int b, int n, int m, int C, int NT, int ppt, int bits, FpsVerdicts spec,
                           int32_t *idx, cudaStream_t st);
 
 namespace {

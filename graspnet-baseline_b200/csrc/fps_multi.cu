@@ -54,7 +54,7 @@ __device__ unsigned long long g_fpsm_prof[8];
 // its CTA's chunk, register slot order == tie-priority order); the per-CTA table holds x, y, z, prio.
 template <int PP, int NT, int EL>
 __global__ void __launch_bounds__(NT, 1)
-fps_multi_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, int spec, int32_t *idx) {
+fps_multi_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, FpsVerdicts spec, int32_t *idx) {
   constexpr int PPT = 2 * PP;
   constexpr int NW = NT / 32;
   constexpr int R = 512 / NT;
@@ -75,7 +75,7 @@ fps_multi_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, i
   int32_t *out = idx + (size_t)cloud * m;
   const int E = C * NW;
   const int base = rank * (PPT * NT);
-  if (spec && out[0] == 0) {                       // the prefix check found the identity (see fps.cu)
+  if (fps_identity(spec, cloud)) {                 // the prefix check found the identity (see fps.cu)
     if (rank == 0)
       for (int j = tid; j < m; j += NT) out[j] = j;
     return;
@@ -276,7 +276,7 @@ fps_multi_kernel(const float *__restrict__ xyz, int n, int m, int C, int bits, i
 }
 
 template <int PP, int NT, int EL>
-int launch_multi(const float *xyz, int b, int n, int m, int C, int bits, int spec, int32_t *idx, cudaStream_t st) {
+int launch_multi(const float *xyz, int b, int n, int m, int C, int bits, FpsVerdicts spec, int32_t *idx, cudaStream_t st) {
   constexpr int tab_bytes = 2 * PP * NT * 16;
   auto kern = fps_multi_kernel<PP, NT, EL>;
   static bool configured = false;                  // per instantiation
@@ -312,7 +312,7 @@ extern "C" int b200_fps_multi_read_profile(unsigned long long *out7) {
 #endif
 
 // B200_ECAPACITY = this configuration is not covered here (the caller then runs the chain kernel of fps.cu)
-int b200_fps_multi_launch(const float *xyz, int b, int n, int m, int C, int NT, int ppt, int bits, int spec,
+int b200_fps_multi_launch(const float *xyz, int b, int n, int m, int C, int NT, int ppt, int bits, FpsVerdicts spec,
                           int32_t *idx, cudaStream_t st) {
   if (C < 2 || C > 16 || bits != 9) return B200_ECAPACITY;
   const int E = C * (NT / 32);

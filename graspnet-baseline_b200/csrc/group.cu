@@ -117,7 +117,38 @@ int scatter_launch(const float *grad_out, const int32_t *idx, int b, int c, int 
   return 0;
 }
 
+// new_xyz = gather_operation(xyz^T, inds)^T with both layouts written by one launch: the reference's SA module
+// runs transpose+contiguous, gather, transpose+contiguous (pointnet2_modules.py:230-240) -- three launches on the
+// serial FPS chain per level.  thread = one sampled point.
+__global__ void __launch_bounds__(GT)
+gather_xyz_kernel(const float *__restrict__ xyz, const int32_t *__restrict__ idx, int n, int m,
+                  float *__restrict__ out, float *__restrict__ out_t) {
+  const int bi = blockIdx.y;
+  const int j = blockIdx.x * GT + threadIdx.x;
+  if (j >= m) return;
+  const float *p = xyz + ((size_t)bi * n + __ldg(idx + (size_t)bi * m + j)) * 3;
+  const float x = __ldg(p), y = __ldg(p + 1), z = __ldg(p + 2);
+  float *o = out + ((size_t)bi * m + j) * 3;
+  o[0] = x; o[1] = y; o[2] = z;
+  if (out_t) {
+    float *t = out_t + (size_t)bi * 3 * m + j;
+    t[0] = x; t[m] = y; t[2 * (size_t)m] = z;
+  }
+}
+
 }  // namespace
+
+extern "C" int b200_gather_xyz(const float *xyz, const int32_t *idx, int b, int n, int m, float *out, float *out_t,
+                               void *stream) {
+  if (b < 0 || n < 0 || m < 0) return B200_EINVAL;
+  if (b == 0 || m == 0) return 0;
+  if (!xyz || !idx || !out || n == 0) return B200_EINVAL;
+  if (b > 65535) return B200_ECAPACITY;
+  gather_xyz_kernel<<<dim3((unsigned)ceil_div(m, GT), (unsigned)b), GT, 0, (cudaStream_t)stream>>>(xyz, idx, n, m, out,
+                                                                                                  out_t);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
 
 extern "C" int b200_gather_points(const float *points, const int32_t *idx, int b, int c, int n, int m,
                                   float *out, void *stream) {

@@ -46,6 +46,41 @@ def furthest_point_sampling(points, nsamples):
     return out
 
 
+def fps_prefix_check(xyz, n, m):
+    """Is FPS over the first n points of each cloud of xyz (B,Ntot,3), m samples, the identity permutation?
+    -> verdict tensor (B,m) i32 whose column 0 is 0 (yes) or -1 (run the chain); pass it to
+    furthest_point_sampling(..., verdicts=[...]).  No synchronisation."""
+    _chk(xyz, "xyz", torch.float32)
+    b, ntot, _ = xyz.shape
+    if n > ntot:
+        raise ValueError("b200grasp: prefix longer than the cloud")
+    verdict = torch.empty((b, m), dtype=torch.int32, device=xyz.device)
+    with torch.cuda.device(xyz.device):
+        _abi.check(_lib.b200_fps_prefix_check(_ptr(xyz), b, n, m, ntot, _ptr(verdict), _stream()), "fps_prefix_check")
+    return verdict
+
+
+def furthest_point_sampling_spec(xyz, npoint, verdicts):
+    """furthest_point_sampling whose identity shortcut is decided by verdict tensors from fps_prefix_check (this
+    level's and its ancestors'): same result as furthest_point_sampling, always."""
+    _chk(xyz, "xyz", torch.float32)
+    if not 1 <= len(verdicts) <= 3:
+        raise ValueError("b200grasp: one to three verdict tensors")
+    b, n, _ = xyz.shape
+    out = torch.empty((b, npoint), dtype=torch.int32, device=xyz.device)
+    args = []
+    for k in range(3):
+        if k < len(verdicts):
+            _chk(verdicts[k], "verdict", torch.int32)
+            args += [_ptr(verdicts[k]), verdicts[k].shape[1]]
+        else:
+            args += [None, 0]
+    with torch.cuda.device(xyz.device):
+        _abi.check(_lib.b200_furthest_point_sampling_spec(_ptr(xyz), b, n, npoint, *args, _ptr(out), _stream()),
+                   "furthest_point_sampling_spec")
+    return out
+
+
 def gather_points(points, idx):
     """points (B,C,N) f32, idx (B,M) i32 -> (B,C,M)   [sampling.cpp:20-43]"""
     _chk(points, "points", torch.float32)
@@ -57,6 +92,21 @@ def gather_points(points, idx):
         _abi.check(_lib.b200_gather_points(_ptr(points), _ptr(idx), b, c, n, m, _ptr(out), _stream()),
                    "gather_points")
     return out
+
+
+def gather_xyz(xyz, idx, transposed=True):
+    """xyz (B,N,3) f32, idx (B,M) i32 -> new_xyz (B,M,3) [, new_xyz_t (B,3,M)] in one launch
+    (= gather_operation(xyz^T, idx) and its transpose, pointnet2_modules.py:230-240)"""
+    _chk(xyz, "xyz", torch.float32)
+    _chk(idx, "idx", torch.int32)
+    b, n, _ = xyz.shape
+    m = idx.shape[1]
+    out = torch.empty((b, m, 3), dtype=torch.float32, device=xyz.device)
+    out_t = torch.empty((b, 3, m), dtype=torch.float32, device=xyz.device) if transposed else None
+    with torch.cuda.device(xyz.device):
+        _abi.check(_lib.b200_gather_xyz(_ptr(xyz), _ptr(idx), b, n, m, _ptr(out),
+                                        _ptr(out_t) if transposed else None, _stream()), "gather_xyz")
+    return (out, out_t) if transposed else out
 
 
 def gather_points_grad(grad_out, idx, n):

@@ -46,6 +46,7 @@ class GeometryScene:
         self._hold = None
         self._streams = None
         self._post_streams = None
+        self._check_streams = None
         g = torch.Generator(device="cpu").manual_seed(seed)
         # stand-ins for MLP outputs (resident, never regenerated)
         self.feat = {}
@@ -196,7 +197,12 @@ class GeometryScene:
             for s in range(B):
                 with torch.cuda.stream(self._post_streams[s % len(self._post_streams)]):
                     masks[s], keeps[s] = self.post_scene(s)
+                    ov = self._out_views              # host-bound results into the one output buffer
+                    ov["mask%d" % s].copy_(masks[s])
+                    ov["kept%d" % s].copy_(keeps[s][0])
+                    ov["nkept%d" % s].copy_(keeps[s][1])
             out["collision_mask"], out["kept"] = masks, keeps
+            self.glue += 1 + 3 * B
         after(s_c, main)
         with torch.cuda.stream(s_c):
             cloud_t = self.cloud.transpose(1, 2).contiguous()
@@ -204,17 +210,35 @@ class GeometryScene:
             # while the main stream is busy with SA1's FPS
             grid = ops.query_grid_build(self.cloud, GRID_CELL) if self.cloud.shape[1] >= ops.GRID_QUERY_MIN_N else None
             hold.append(grid)
-        xyz, xyz_t = self.cloud, None
+        xyz, xyz_t = self.cloud, cloud_t
+        npts = [c[0] for c in self.sa_cfg]
+        nested = all(npts[l + 1] <= npts[l] for l in range(len(npts) - 1)) and len(npts) <= 4
+        verdicts = []
         for lvl, (npoint, radius, nsample, cin) in enumerate(self.sa_cfg):
             name = "sa%d" % (lvl + 1)
             # main stream = the serial chain: FPS -> gather -> next level's FPS
-            inds = ops.furthest_point_sampling(xyz, npoint)
-            if xyz_t is None:
-                xyz_t = xyz.transpose(1, 2).contiguous()
-            new_xyz_t = ops.gather_points(xyz_t, inds)
-            new_xyz = new_xyz_t.transpose(1, 2).contiguous()
+            if lvl == 0:
+                inds = ops.furthest_point_sampling(xyz, npoint)
+            elif nested:
+                if lvl == 1:
+                    after(main, *self._check_streams)
+                inds = ops.furthest_point_sampling_spec(xyz, npoint, verdicts[:lvl])
+            else:
+                inds = ops.furthest_point_sampling(xyz, npoint)
+            new_xyz, new_xyz_t = ops.gather_xyz(xyz, inds)
             hold += [xyz_t, new_xyz_t]
             out[name + "_inds"], out[name + "_xyz"] = inds, new_xyz
+            if lvl == 0 and nested:
+                # SA2..SA4 sample prefixes of SA1's output (if each level returns the identity): all their
+                # prefix checks run now, side by side, instead of one after the other on the serial chain
+                if self._check_streams is None:
+                    self._check_streams = [torch.cuda.Stream(device=self.dev) for _ in range(len(npts) - 1)]
+                for l in range(1, len(npts)):
+                    cs = self._check_streams[l - 1]
+                    after(cs, main)
+                    with torch.cuda.stream(cs):
+                        verdicts.append(ops.fps_prefix_check(new_xyz, npts[l - 1], npts[l]))
+                hold += verdicts
             after(s_q, main, *([s_c] if lvl == 0 else []))
             with torch.cuda.stream(s_q):              # neighbourhood queries + grouping of this level
                 idx = ops.ball_query(new_xyz, xyz, radius, nsample, grid=grid if lvl == 0 else None)
@@ -229,6 +253,8 @@ class GeometryScene:
                     cidx = ops.cylinder_query_multi(new_xyz, self.cloud, rot9, CYL["radius"], CYL["hmin"],
                                                     CYL["hmax_list"], CYL["nsample"], grid=grid)
                     out["crop_idx"] = cidx
+                    if post:
+                        self._out_views["seeds"].copy_(inds)
                     cat = cidx.permute(1, 0, 2, 3).reshape(B, cidx.shape[0] * cidx.shape[2], cidx.shape[3])
                     if B > 1:
                         cat = cat.contiguous()
@@ -244,14 +270,6 @@ class GeometryScene:
                 out[name + "_idx"] = idx3
                 out[name + "_interp"] = ops.three_interpolate(self.feat[name + "_known"], idx3, w)
         after(main, s_q, s_c, s_f, *(self._post_streams if post else []))
-        if post:                                      # host-bound results into the one output buffer
-            ov = self._out_views
-            ov["seeds"].copy_(out["sa2_inds"])
-            for s in range(B):
-                ov["mask%d" % s].copy_(masks[s])
-                ov["kept%d" % s].copy_(keeps[s][0])
-                ov["nkept%d" % s].copy_(keeps[s][1])
-            self.glue += 1 + 3 * B
         self._hold = hold
         return out
 

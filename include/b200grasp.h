@@ -57,6 +57,27 @@ int b200_gather_points(const float *points, const int32_t *idx, int b, int c, in
 int b200_gather_points_grad(const float *grad_out, const int32_t *idx, int b, int c, int n, int m,
                             float *grad_points, void *stream);
 
+/* Speculative FPS (PointNet++ feeds SA2..SA4 the points SA1 chose IN THE ORDER it chose them, models/backbone.py:
+ * 110-119; FPS over such a prefix returns 0,1,2,... unless a tie or the skip rule intervenes).
+ *  b200_fps_prefix_check: decides, without the serial chain, whether FPS over the first n points of every cloud
+ *    (clouds `cloud_stride` >= n points apart, so a prefix VIEW of a larger array works) returning m samples is the
+ *    identity: verdict[c*m] = 0 if so, -1 if the chain must run (verdict is b*m int32 of scratch).
+ *  b200_furthest_point_sampling_spec: b200_furthest_point_sampling that takes the shortcut for cloud c iff every
+ *    given verdict array (up to three, entry [c*stride]; NULL = unused, from slot 0) says 0.  Several arrays are
+ *    for levels whose input is a prefix only if the levels above returned the identity as well; this lets all the
+ *    checks of a backbone run concurrently right after SA1.  The result is always the exact FPS answer. */
+int b200_fps_prefix_check(const float *xyz, int b, int n, int m, long long cloud_stride, int32_t *verdict,
+                          void *stream);
+int b200_furthest_point_sampling_spec(const float *xyz, int b, int n, int m, const int32_t *verdict0, int stride0,
+                                      const int32_t *verdict1, int stride1, const int32_t *verdict2, int stride2,
+                                      int32_t *idx, void *stream);
+
+/* SA-module fast path: new_xyz[B,M,3] = xyz[B,N,3] rows picked by idx[B,M], and (if out_t != NULL) the same
+ * points channel-major [B,3,M] -- what gather_operation(xyz^T, inds) and its .transpose(1,2).contiguous() give
+ * (pointnet2_modules.py:230-240), in one launch. */
+int b200_gather_xyz(const float *xyz, const int32_t *idx, int b, int n, int m, float *out, float *out_t,
+                    void *stream);
+
 /* Replaces ball_query(new_xyz[B,M,3], xyz[B,N,3], radius, nsample) -> [B,M,nsample] i32
  * (ball_query.cpp:13-37, ball_query.h:9-10; ball_query_gpu.cu:14-49). */
 int b200_ball_query(const float *new_xyz, const float *xyz, int b, int n, int m, float radius,

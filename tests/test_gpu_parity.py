@@ -114,6 +114,57 @@ def test_fps_on_fps_ordered_prefix(b200, oracle_mod, kind, n0, n, m):
     assert (chain == want).all()
 
 
+def test_fps_spec_with_external_verdicts(b200, oracle_mod):
+    """The split form of the speculative path: prefix checks launched ahead (for several nested levels at once),
+    FPS given this level's verdict and its ancestors'.  Cloud 0 is FPS-ordered (identity holds on every level),
+    cloud 1 is FPS-ordered only after its first 600 points were reversed (level 1024->512 fails, deeper ones
+    would pass on their own but their input is not a prefix any more), cloud 2 is in file order."""
+    ops = b200.ops
+    x0 = clouds(b200, 3, 6000, "table", 5)
+    first = oracle_mod.furthest_point_sampling(x0, 1024)
+    x = np.stack([x0[i][first[i]] for i in range(3)])
+    x[1, :600] = x[1, :600][::-1]
+    x[2] = x0[2, :1024]
+    x = np.ascontiguousarray(x)
+    xd = dev(x)
+    sizes = [1024, 512, 256, 128]
+    verdicts = [ops.fps_prefix_check(xd, sizes[l], sizes[l + 1]) for l in range(3)]
+    heads = [v[:, 0].cpu().numpy() for v in verdicts]
+    assert (heads[0] == [0, -1, -1]).all() and heads[1][0] == 0 and heads[2][0] == 0
+    cur, cur_np = xd, x
+    for l in range(3):
+        got = ops.furthest_point_sampling_spec(cur, sizes[l + 1], verdicts[: l + 1])
+        want = oracle_mod.furthest_point_sampling(cur_np, sizes[l + 1])
+        assert (got.cpu().numpy() == want).all(), l
+        assert (want[0] == np.arange(sizes[l + 1])).all()
+        plain = ops.furthest_point_sampling(cur, sizes[l + 1]).cpu().numpy()
+        assert (plain == want).all(), l
+        cur_np = np.stack([cur_np[i][want[i]] for i in range(3)])
+        cur = dev(cur_np)
+    # a verdict that says "run the chain" for every cloud: still the same answer
+    no = torch.full((3, 512), -1, dtype=torch.int32, device="cuda")
+    got = ops.furthest_point_sampling_spec(xd, 512, [no]).cpu().numpy()
+    assert (got == oracle_mod.furthest_point_sampling(x, 512)).all()
+    with pytest.raises(ValueError):
+        ops.furthest_point_sampling_spec(xd, 512, [])
+    with pytest.raises(ValueError):
+        ops.fps_prefix_check(xd, 2048, 512)
+
+
+@pytest.mark.parametrize("b,n,m", [(1, 20000, 1024), (3, 777, 300), (2, 5, 9), (1, 1, 1)])
+def test_gather_xyz_both_layouts(b200, b, n, m):
+    x = clouds(b200, b, n, "table", n + m)
+    rng = np.random.default_rng(m)
+    idx = rng.integers(0, n, (b, m)).astype(np.int32)
+    rows, cols = b200.ops.gather_xyz(dev(x), dev(idx))
+    want = np.stack([x[i][idx[i]] for i in range(b)])
+    assert rows.shape == (b, m, 3) and cols.shape == (b, 3, m)
+    assert np.array_equal(rows.cpu().numpy(), want)
+    assert np.array_equal(cols.cpu().numpy(), want.transpose(0, 2, 1))
+    via = b200.ops.gather_points(dev(np.ascontiguousarray(x.transpose(0, 2, 1))), dev(idx)).cpu().numpy()
+    assert np.array_equal(cols.cpu().numpy(), via)
+
+
 # ------------------------------------------------------------------ queries
 
 @pytest.mark.parametrize("b,n,m,r,ns,kind", [
