@@ -1,0 +1,351 @@
+// mlp_fused.cu -- group -> centre / normalise / rotate -> shared MLP (3 x [1x1 conv + BN + ReLU]) -> max-pool over the
+// neighbourhood, as ONE sm_100a kernel with the two wide layers on the 5th-generation tensor cores.
+//
+// Replaces, for the modules whose grouped input is xyz only (SA1 of the backbone and CloudCrop), the chain
+//   QueryAndGroup / CylinderQueryAndGroup.forward   (reference pointnet2/pointnet2_utils.py:313-372, 488-555)
+//   -> pt_utils.SharedMLP                            (pointnet2/pytorch_utils.py:11-36: Conv2d 1x1, BatchNorm2d, ReLU)
+//   -> F.max_pool2d(kernel=[1, nsample])             (pointnet2/pointnet2_modules.py:243-257, models/modules.py:127-141)
+// in eval mode (BatchNorm folded into the conv weights by the host wrapper).  The reference materialises the
+// (B, C, npoint, nsample) activations of every layer in HBM (CloudCrop: 262,144 rows x (64 + 128 + 256) channels x 4 B,
+// written and re-read by conv, BN and ReLU kernels); here a row's activations never leave the SM.
+//
+// Shape of the work: a "row" is one neighbour of one neighbourhood list; a tile is 128 rows (= 128 / nsample lists).
+//   layer 1 (3 -> C1)  : K = 3 is no tensor-core shape: each row thread gathers its point, centres / scales /
+//                        rotates it and evaluates the C1 outputs with FFMA.
+//   layer 2 (C1 -> C2) : D2[128, C2] = A2[128, C1] . W2^T     tcgen05.mma kind::tf32, M = 128, N = C2, K = 8 per MMA
+//   layer 3 (C2 -> C3) : D3[128, C3] = A3[128, C2] . W3^T     accumulators in TMEM (columns [0, C2) and [C2, C2 + C3))
+//   max-pool           : over the nsample rows of a list, on the layer-3 epilogue registers.
+// fp32-grade results from tf32 tensor cores ("3xTF32"): x = hi + lo with hi = tf32(x), lo = tf32(x - hi), and
+// a.b ~= a_lo.b_hi + a_hi.b_lo + a_hi.b_hi, accumulated in fp32; the dropped a_lo.b_lo term is 2^-22 relative.
+// `passes` = 1 runs plain TF32 (what cuDNN does for the reference's convs under torch's default allow_tf32).
+//
+// Pipeline inside a CTA (persistent over tiles), 6 warps:
+//   warps 0-3  one thread per row: gather + layer 1, then the epilogues.  They PRODUCE the A operand of the next layer
+//              in K-slabs of 16 channels (hi and lo parts, 16 KB) into a 4-slot ring: the epilogue of layer l for
+//              channels [16 s, 16 s + 16) is the K-slab s of layer l + 1, so the tensor core starts layer l + 1 while
+//              the CUDA cores are still converting layer l, and no layer's activations are ever held whole.
+//   warp 4     lane 0 issues the MMAs: per slab 2 K-steps x 3 passes, then tcgen05.commit releases the A slot and the
+//              weight slot; after a layer's last slab a commit tells the row threads its accumulators are complete.
+//   warp 5     lane 0 streams the weight slabs (host-packed: hi | lo, core-matrix order) global/L2 -> shared with
+//              cp.async.bulk into a 4-slot ring (W2 + W3 in 3xTF32 form are 320 KB: they cannot stay resident).
+// Shared-memory operand layout (both A and B are "K-major, no swizzle" UMMA operands): for each 16-byte K-chunk
+// (4 tf32) the rows are contiguous, i.e. byte offset = chunk * rows * 16 + row * 16; a thread stores its row's
+// chunk with one st.shared.v4 and a warp's stores are 512 contiguous bytes.
+#include "tc_common.cuh"
+
+namespace {
+
+constexpr int TM = 128;                        // rows per tile = TMEM lanes = row threads
+constexpr int KS = 16;                         // channels per K-slab
+constexpr int NA = 4;                          // A ring slots
+constexpr int NWS = 4;                         // weight ring slots
+constexpr int A_PART = TM * KS * 4;            // 8 KB: the hi (or lo) part of an A slab
+constexpr int A_SLOT = 2 * A_PART;
+constexpr int MAXC = 256;                      // widest layer
+constexpr int W_SLOT = MAXC * KS * 4 * 2;      // 32 KB: hi | lo of a weight slab of the widest layer
+constexpr int MAXE = 8;                        // pooling entries per tile (128 / nsample, at least one per warp)
+constexpr int NTHREADS = 192;
+
+struct Params {
+  const float *xyz, *new_xyz, *rot;
+  const int32_t *idx;
+  int G, B, N, m, ns;
+  float radius;                                // > 0: grouped_xyz /= radius (normalize_xyz)
+  const float *w1, *b1;                        // (C1, 3), (C1): layer 1, BN folded
+  const float *w2p, *b2;                       // packed (mlp_pack_kernel), (C2)
+  const float *w3p, *b3;
+  int C1, C2, C3, passes;
+  long long Q;                                 // lists = B * m * G
+  int tiles;
+  float *out;                                  // (B, C3, m, G)
+};
+
+struct Smem {
+  // offsets into the dynamic shared memory block
+  static constexpr int a_ring = 0;
+  static constexpr int w_ring = a_ring + NA * A_SLOT;
+  static constexpr int consts = w_ring + NWS * W_SLOT;               // w1 (C1*3) | b1 | b2 | b3
+  static constexpr int pool = consts + (MAXC * 3 + 3 * MAXC) * 4;   // MAXE x C3
+  static constexpr int bars = pool + MAXE * MAXC * 4;                // a_full, a_empty, w_full, w_empty, acc_full[2]
+  static constexpr int holder = bars + (2 * NA + 2 * NWS + 2) * 8;
+  static constexpr int total = holder + 16;
+};
+
+__device__ __forceinline__ float relu_keep_nan(float v) { return (v <= 0.f) ? 0.f : v; }
+
+// one 16-channel slab of this row into the A ring (waits for the slot, splits hi / lo, publishes)
+__device__ __forceinline__ void put_slab(uint32_t sm, const float (&v)[16], int row, uint32_t &na, int passes) {
+  const uint32_t slot = na % NA, ph = (na / NA) & 1u;
+  const uint32_t a_full = sm + Smem::bars + slot * 8, a_empty = sm + Smem::bars + (NA + slot) * 8;
+  tc::mbar_wait(a_empty, ph ^ 1u);
+  const uint32_t base = sm + Smem::a_ring + slot * A_SLOT + row * 16;
+#pragma unroll
+  for (int kc = 0; kc < 4; ++kc) {
+    float hi[4], lo[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      hi[e] = tc::tf32_rna(v[4 * kc + e]);
+      lo[e] = tc::tf32_rna(v[4 * kc + e] - hi[e]);
+    }
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(base + kc * (TM * 16)), "f"(hi[0]), "f"(hi[1]),
+                 "f"(hi[2]), "f"(hi[3]) : "memory");
+    if (passes == 3)
+      asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(base + A_PART + kc * (TM * 16)), "f"(lo[0]),
+                   "f"(lo[1]), "f"(lo[2]), "f"(lo[3]) : "memory");
+  }
+  tc::fence_proxy_async();
+  tc::fence_before_sync();
+  tc::mbar_arrive(a_full);
+  ++na;
+}
+
+__global__ void __launch_bounds__(NTHREADS, 1)
+group_mlp_maxpool_kernel(const Params p) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  const uint32_t sm = tc::smem_u32(smem_raw);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  float *cst = reinterpret_cast<float *>(smem_raw + Smem::consts);
+  float *w1s = cst, *b1s = cst + MAXC * 3, *b2s = b1s + MAXC, *b3s = b2s + MAXC;
+  float *pool = reinterpret_cast<float *>(smem_raw + Smem::pool);
+  volatile uint32_t *holder = reinterpret_cast<volatile uint32_t *>(smem_raw + Smem::holder);
+
+  for (int i = tid; i < p.C1 * 3; i += NTHREADS) w1s[i] = __ldg(p.w1 + i);
+  for (int i = tid; i < p.C1; i += NTHREADS) b1s[i] = __ldg(p.b1 + i);
+  for (int i = tid; i < p.C2; i += NTHREADS) b2s[i] = __ldg(p.b2 + i);
+  for (int i = tid; i < p.C3; i += NTHREADS) b3s[i] = __ldg(p.b3 + i);
+  if (tid == 0) {
+    for (int s = 0; s < NA; ++s) {
+      tc::mbar_init(sm + Smem::bars + s * 8, TM);                    // a_full: every row thread arrives
+      tc::mbar_init(sm + Smem::bars + (NA + s) * 8, 1);              // a_empty: one tcgen05.commit
+    }
+    for (int s = 0; s < NWS; ++s) {
+      tc::mbar_init(sm + Smem::bars + (2 * NA + s) * 8, 1);          // w_full: expect_tx arrival + bytes
+      tc::mbar_init(sm + Smem::bars + (2 * NA + NWS + s) * 8, 1);    // w_empty: one tcgen05.commit
+    }
+    tc::mbar_init(sm + Smem::bars + (2 * NA + 2 * NWS) * 8, 1);      // acc_full[0]: layer-2 accumulators complete
+    tc::mbar_init(sm + Smem::bars + (2 * NA + 2 * NWS + 1) * 8, 1);  // acc_full[1]: layer-3
+    tc::fence_barrier_init();
+  }
+  if (warp == 4) tc::tmem_alloc_512(sm + Smem::holder);
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = *holder;
+  const uint32_t acc_full0 = sm + Smem::bars + (2 * NA + 2 * NWS) * 8, acc_full1 = acc_full0 + 8;
+
+  if (warp < 4) {
+    // ------------------------------------------------------------------ row threads
+    const int row = tid;
+    const int lpt = TM / p.ns;                                        // lists per tile
+    const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+    uint32_t na = 0;
+    for (int tile = blockIdx.x, it = 0; tile < p.tiles; tile += gridDim.x, ++it) {
+      // gather: this row's neighbour, in the frame of its list's centre
+      const long long q = (long long)tile * lpt + row / p.ns;
+      float g0 = 0.f, g1 = 0.f, g2 = 0.f;
+      if (q < p.Q) {
+        const int gi = (int)(q % p.G);
+        const long long t = q / p.G;
+        const int seed = (int)(t % p.m), bi = (int)(t / p.m);
+        const int i = __ldg(p.idx + ((((long long)gi * p.B + bi) * p.m + seed) * p.ns + row % p.ns));
+        const float *pt = p.xyz + ((long long)bi * p.N + i) * 3;
+        const float *ct = p.new_xyz + ((long long)bi * p.m + seed) * 3;
+        float d0 = __fsub_rn(__ldg(pt), __ldg(ct)), d1 = __fsub_rn(__ldg(pt + 1), __ldg(ct + 1)),
+              d2 = __fsub_rn(__ldg(pt + 2), __ldg(ct + 2));
+        if (p.radius > 0.f) {
+          d0 = __fdiv_rn(d0, p.radius); d1 = __fdiv_rn(d1, p.radius); d2 = __fdiv_rn(d2, p.radius);
+        }
+        if (p.rot) {                                                  // row vector times the seed's 3x3
+          const float *R = p.rot + ((long long)bi * p.m + seed) * 9;
+          g0 = __fmaf_rn(d2, __ldg(R + 6), __fmaf_rn(d1, __ldg(R + 3), __fmul_rn(d0, __ldg(R))));
+          g1 = __fmaf_rn(d2, __ldg(R + 7), __fmaf_rn(d1, __ldg(R + 4), __fmul_rn(d0, __ldg(R + 1))));
+          g2 = __fmaf_rn(d2, __ldg(R + 8), __fmaf_rn(d1, __ldg(R + 5), __fmul_rn(d0, __ldg(R + 2))));
+        } else {
+          g0 = d0; g1 = d1; g2 = d2;
+        }
+      }
+      // layer 1 on the CUDA cores -> K-slabs of layer 2
+      for (int s = 0; s < p.C1 / KS; ++s) {
+        float v[16];
+#pragma unroll
+        for (int c = 0; c < 16; ++c) {
+          const float *w = w1s + (s * KS + c) * 3;
+          const float a = __fmaf_rn(w[2], g2, __fmaf_rn(w[1], g1, __fmul_rn(w[0], g0)));
+          v[c] = relu_keep_nan(__fadd_rn(a, b1s[s * KS + c]));
+        }
+        put_slab(sm, v, row, na, p.passes);
+      }
+      // layer-2 epilogue -> K-slabs of layer 3
+      tc::mbar_wait(acc_full0, it & 1);
+      tc::fence_after_sync();
+      for (int s = 0; s < p.C2 / KS; ++s) {
+        float v[16];
+        tc::tmem_ld16(lane_base + s * KS, v);
+#pragma unroll
+        for (int c = 0; c < 16; ++c) v[c] = relu_keep_nan(__fadd_rn(v[c], b2s[s * KS + c]));
+        put_slab(sm, v, row, na, p.passes);
+      }
+      // layer-3 epilogue: bias, ReLU, max over the rows of a pooling entry (values are >= +0 or NaN, so the
+      // unsigned order of the bit patterns is the float order and NaN wins, as in max_pool2d)
+      tc::mbar_wait(acc_full1, it & 1);
+      tc::fence_after_sync();
+      const int entry = p.ns >= 32 ? warp : row / p.ns;
+      for (int s = 0; s < p.C3 / KS; ++s) {
+        float v[16];
+        tc::tmem_ld16(lane_base + p.C2 + s * KS, v);
+        unsigned mine = 0;
+#pragma unroll
+        for (int c = 0; c < 16; ++c) {
+          unsigned u = __float_as_uint(relu_keep_nan(__fadd_rn(v[c], b3s[s * KS + c])));
+          if (p.ns >= 32) {
+            u = __reduce_max_sync(0xffffffffu, u);
+          } else {
+            for (int o = p.ns >> 1; o >= 1; o >>= 1) u = max(u, __shfl_xor_sync(0xffffffffu, u, o));
+          }
+          if ((lane & 15) == c) mine = u;
+        }
+        // one lane per (entry, channel): a warp is one entry (lanes 0-15 write) or, for 16-row lists, two
+        if (p.ns >= 32 ? lane < 16 : true) pool[entry * MAXC + s * KS + (lane & 15)] = __uint_as_float(mine);
+      }
+      tc::fence_before_sync();
+      tc::named_barrier(1, TM);
+      // combine the entries of each list and write (B, C3, m, G)
+      const int epl = p.ns >= 32 ? p.ns / 32 : 1;                     // entries per list
+      for (int c = tid; c < p.C3; c += TM) {
+        for (int l = 0; l < lpt; ++l) {
+          const long long ql = (long long)tile * lpt + l;
+          if (ql >= p.Q) break;
+          unsigned u = 0;
+          for (int e = 0; e < epl; ++e) u = max(u, __float_as_uint(pool[(l * epl + e) * MAXC + c]));
+          const int gi = (int)(ql % p.G);
+          const long long t = ql / p.G;
+          const int seed = (int)(t % p.m), bi = (int)(t / p.m);
+          p.out[(((long long)bi * p.C3 + c) * p.m + seed) * p.G + gi] = __uint_as_float(u);
+        }
+      }
+    }
+  } else if (warp == 4) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      uint32_t na = 0, nw = 0;
+      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
+        for (int layer = 0; layer < 2; ++layer) {
+          const int K = layer ? p.C2 : p.C1, N = layer ? p.C3 : p.C2;
+          const uint32_t d = tmem + (layer ? (uint32_t)p.C2 : 0u);
+          const uint32_t idesc = tc::idesc_tf32_m128(N);
+          const uint32_t b_lbo = (uint32_t)N * 16u, b_part = (uint32_t)N * KS * 4u;
+          for (int s = 0; s < K / KS; ++s) {
+            const uint32_t ws = nw % NWS, as = na % NA;
+            tc::mbar_wait(sm + Smem::bars + (2 * NA + ws) * 8, (nw / NWS) & 1u);
+            tc::mbar_wait(sm + Smem::bars + as * 8, (na / NA) & 1u);
+            tc::fence_after_sync();
+            const uint32_t a_base = sm + Smem::a_ring + as * A_SLOT, w_base = sm + Smem::w_ring + ws * W_SLOT;
+#pragma unroll
+            for (int kk = 0; kk < KS / 8; ++kk) {
+              const uint64_t ah = tc::smem_desc(a_base + kk * 2 * (TM * 16), TM * 16, 128);
+              const uint64_t al = tc::smem_desc(a_base + A_PART + kk * 2 * (TM * 16), TM * 16, 128);
+              const uint64_t bh = tc::smem_desc(w_base + kk * 2 * b_lbo, b_lbo, 128);
+              const uint64_t bl = tc::smem_desc(w_base + b_part + kk * 2 * b_lbo, b_lbo, 128);
+              const uint32_t acc = (s > 0 || kk > 0) ? 1u : 0u;
+              if (p.passes == 3) {
+                tc::mma_tf32(d, al, bh, idesc, acc);
+                tc::mma_tf32(d, ah, bl, idesc, 1u);
+                tc::mma_tf32(d, ah, bh, idesc, 1u);
+              } else {
+                tc::mma_tf32(d, ah, bh, idesc, acc);
+              }
+            }
+            tc::mma_commit(sm + Smem::bars + (NA + as) * 8);              // A slot free once these MMAs have read it
+            tc::mma_commit(sm + Smem::bars + (2 * NA + NWS + ws) * 8);    // weight slot too
+            ++na; ++nw;
+          }
+          tc::mma_commit(layer ? acc_full1 : acc_full0);
+        }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ weight loader
+    if (lane == 0) {
+      uint32_t nw = 0;
+      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
+        for (int layer = 0; layer < 2; ++layer) {
+          const int K = layer ? p.C2 : p.C1, N = layer ? p.C3 : p.C2;
+          const float *src = layer ? p.w3p : p.w2p;
+          const uint32_t slab_floats = (uint32_t)N * KS * 2u;
+          const uint32_t bytes = (uint32_t)N * KS * 4u * (p.passes == 3 ? 2u : 1u);
+          for (int s = 0; s < K / KS; ++s) {
+            const uint32_t ws = nw % NWS;
+            tc::mbar_wait(sm + Smem::bars + (2 * NA + NWS + ws) * 8, ((nw / NWS) & 1u) ^ 1u);
+            const uint32_t full = sm + Smem::bars + (2 * NA + ws) * 8;
+            tc::mbar_arrive_expect_tx(full, bytes);
+            tc::bulk_g2s(sm + Smem::w_ring + ws * W_SLOT, src + (size_t)s * slab_floats, bytes, full);
+            ++nw;
+          }
+        }
+      }
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 4) {
+    __syncwarp();
+    tc::tmem_dealloc_512(tmem);
+  }
+}
+
+// (cout, cin) fp32 weights -> per K-slab s of 16 input channels: [hi | lo][k-chunk kc (4)][n (cout)][e (4)],
+// k = 16 s + 4 kc + e; hi = tf32(w), lo = tf32(w - hi)
+__global__ void mlp_pack_kernel(const float *__restrict__ w, int cout, int cin, float *__restrict__ packed) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= cout * cin) return;
+  const int n = i / cin, k = i % cin;
+  const int s = k / KS, kc = (k % KS) / 4, e = k % 4;
+  const float v = __ldg(w + i);
+  const float hi = tc::tf32_rna(v), lo = tc::tf32_rna(v - hi);
+  const size_t base = (size_t)s * cout * KS * 2;
+  packed[base + ((size_t)kc * cout + n) * 4 + e] = hi;
+  packed[base + (size_t)cout * KS + ((size_t)kc * cout + n) * 4 + e] = lo;
+}
+
+}  // namespace
+
+extern "C" int b200_mlp_pack_weights(const float *w, int cout, int cin, float *packed, void *stream) {
+  if (!w || !packed || cout < 16 || cin < KS || cout % 16 || cin % KS || cout > MAXC || cin > MAXC) return B200_EINVAL;
+  const int n = cout * cin;
+  mlp_pack_kernel<<<ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(w, cout, cin, packed);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200_group_mlp_maxpool(const float *xyz, const float *new_xyz, const float *rot, const int32_t *idx,
+                                      int g, int b, int n, int m, int ns, float radius, const float *w1,
+                                      const float *b1, const float *w2_packed, const float *b2,
+                                      const float *w3_packed, const float *b3, int c1, int c2, int c3, int passes,
+                                      float *out, void *stream) {
+  if (g < 1 || b < 0 || n < 1 || m < 0 || ns < 1) return B200_EINVAL;
+  if (passes != 1 && passes != 3) return B200_EINVAL;
+  // shapes the tensor-core path covers: whole lists per tile, K in slabs of 16, N a multiple of 16 up to 256
+  if (ns != 16 && ns != 32 && ns != 64 && ns != 128) return B200_ECAPACITY;
+  if (c1 % KS || c2 % KS || c3 % 16 || c1 < KS || c2 < KS || c3 < 16 || c1 > MAXC || c2 > MAXC || c3 > MAXC)
+    return B200_ECAPACITY;
+  if (c2 + c3 > 512) return B200_ECAPACITY;
+  const long long lists = (long long)b * m * g;
+  if (lists == 0) return 0;
+  if (!xyz || !new_xyz || !idx || !w1 || !b1 || !w2_packed || !b2 || !w3_packed || !b3 || !out) return B200_EINVAL;
+  const long long tiles = ceil_div_ll(lists * ns, TM);
+  if (tiles > 0x7fffffffLL) return B200_ECAPACITY;
+  Params p;
+  p.xyz = xyz; p.new_xyz = new_xyz; p.rot = rot; p.idx = idx;
+  p.G = g; p.B = b; p.N = n; p.m = m; p.ns = ns; p.radius = radius;
+  p.w1 = w1; p.b1 = b1; p.w2p = w2_packed; p.b2 = b2; p.w3p = w3_packed; p.b3 = b3;
+  p.C1 = c1; p.C2 = c2; p.C3 = c3; p.passes = passes; p.Q = lists; p.tiles = (int)tiles; p.out = out;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CUDA(cudaFuncSetAttribute(group_mlp_maxpool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem::total));
+    attr_set = true;
+  }
+  const int grid = (int)(tiles < b200_sm_count() ? tiles : b200_sm_count());
+  group_mlp_maxpool_kernel<<<grid, NTHREADS, Smem::total, (cudaStream_t)stream>>>(p);
+  B200_LAUNCH_CHECK();
+  return 0;
+}

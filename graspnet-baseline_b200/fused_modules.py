@@ -1,0 +1,146 @@
+"""Set-abstraction and CloudCrop modules whose eval-mode forward is the fused tensor-core kernel
+(csrc/mlp_fused.cu): neighbourhood query -> group -> shared MLP -> max-pool with no grouped or per-layer
+activation tensor in HBM.
+
+Constructor arguments, forward signatures, outputs and state_dict keys follow the reference classes
+  SharedMLP               pointnet2/pytorch_utils.py:11-36   (layer{i}.conv.weight, layer{i}.bn.bn.{weight,bias,...})
+  PointnetSAModuleVotes   pointnet2/pointnet2_modules.py:164-275  (mlp_module.*)
+  CloudCrop               models/modules.py:80-142                 (mlps.*)
+so a reference checkpoint loads unchanged.  In training mode (BatchNorm needs the batch statistics and autograd
+the activations) the modules run the composed path: the same CUDA group ops followed by the torch layers.
+"""
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import ops, pointnet2_utils
+
+
+class _BN(nn.Sequential):
+    def __init__(self, channels):
+        super().__init__()
+        self.add_module("bn", nn.BatchNorm2d(channels))
+
+
+class _ConvBNReLU(nn.Sequential):
+    def __init__(self, cin, cout, bn):
+        super().__init__()
+        conv = nn.Conv2d(cin, cout, kernel_size=(1, 1), bias=not bn)
+        nn.init.kaiming_normal_(conv.weight)
+        if conv.bias is not None:
+            nn.init.constant_(conv.bias, 0)
+        self.add_module("conv", conv)
+        if bn:
+            self.add_module("bn", _BN(cout))
+        self.add_module("activation", nn.ReLU(inplace=True))
+
+
+class SharedMLP(nn.Sequential):
+    """1x1 conv + BatchNorm2d + ReLU per layer over (B, C, npoint, nsample)."""
+
+    def __init__(self, args, *, bn=False):
+        super().__init__()
+        for i in range(len(args) - 1):
+            self.add_module("layer%d" % i, _ConvBNReLU(args[i], args[i + 1], bn))
+
+    def folded(self):
+        """[(w (Cout,Cin), b (Cout))] with eval-mode BatchNorm folded in: y = relu(w x + b) per layer"""
+        out = []
+        for layer in self:
+            w = layer.conv.weight.detach()[:, :, 0, 0].float()
+            b = layer.conv.bias.detach().float() if layer.conv.bias is not None else torch.zeros_like(w[:, 0])
+            if hasattr(layer, "bn"):
+                bn = layer.bn.bn
+                scale = bn.weight.detach() / torch.sqrt(bn.running_var + bn.eps)
+                w = w * scale[:, None]
+                b = (b - bn.running_mean) * scale + bn.bias.detach()
+            out.append((w.contiguous(), b.contiguous()))
+        return out
+
+
+class _FusedMLP:
+    """Packed weights of a 3-layer SharedMLP for ops.group_mlp_maxpool; rebuilt when the parameters change."""
+
+    def __init__(self, mlp):
+        self.mlp, self.key, self.layers = mlp, None, None
+
+    def get(self):
+        params = list(self.mlp.parameters()) + list(self.mlp.buffers())
+        key = tuple((p.data_ptr(), p._version) for p in params)
+        if key != self.key:
+            (w1, b1), (w2, b2), (w3, b3) = self.mlp.folded()
+            self.layers = [(w1, b1), (ops.mlp_pack_weights(w2), b2, w2.shape[0]),
+                           (ops.mlp_pack_weights(w3), b3, w3.shape[0])]
+            self.key = key
+        return self.layers
+
+
+def fusable(mlp, nsample):
+    dims = [mlp[0].conv.in_channels] + [l.conv.out_channels for l in mlp]
+    return (len(mlp) == 3 and dims[0] == 3 and nsample in (16, 32, 64, 128) and
+            all(d % 16 == 0 and 16 <= d <= 256 for d in dims[1:]))
+
+
+class PointnetSAModuleVotes(nn.Module):
+    """Set abstraction: FPS -> ball query -> group -> shared MLP -> max-pool; returns (new_xyz, new_features, inds)."""
+
+    def __init__(self, *, mlp, npoint=None, radius=None, nsample=None, bn=True, use_xyz=True, pooling="max",
+                 sigma=None, normalize_xyz=False, sample_uniformly=False, ret_unique_cnt=False, passes=3):
+        super().__init__()
+        if npoint is None or pooling != "max" or sample_uniformly or ret_unique_cnt:
+            raise NotImplementedError("b200grasp: only the configuration GraspNet uses (npoint set, max pooling)")
+        self.npoint, self.radius, self.nsample = npoint, radius, nsample
+        self.use_xyz, self.normalize_xyz, self.passes = use_xyz, normalize_xyz, passes
+        self.grouper = pointnet2_utils.QueryAndGroup(radius, nsample, use_xyz=use_xyz, ret_grouped_xyz=True,
+                                                     normalize_xyz=normalize_xyz)
+        spec = list(mlp)
+        if use_xyz and len(spec) > 0:
+            spec[0] += 3
+        self.mlp_module = SharedMLP(spec, bn=bn)
+        self._fused = _FusedMLP(self.mlp_module)
+
+    def forward(self, xyz, features=None, inds=None):
+        if inds is None:
+            inds = pointnet2_utils.furthest_point_sample(xyz, self.npoint)
+        else:
+            assert inds.shape[1] == self.npoint
+        new_xyz = ops.gather_xyz(xyz, inds, transposed=False)
+        if (not self.training and features is None and self.use_xyz and not torch.is_grad_enabled()
+                and fusable(self.mlp_module, self.nsample)):
+            idx = pointnet2_utils.ball_query(self.radius, self.nsample, xyz, new_xyz)
+            new_features = ops.group_mlp_maxpool(xyz, new_xyz, idx, self._fused.get(),
+                                                 radius=self.radius if self.normalize_xyz else 0.0,
+                                                 passes=self.passes)
+            return new_xyz, new_features, inds
+        grouped_features, _ = self.grouper(xyz, new_xyz, features)
+        new_features = self.mlp_module(grouped_features)
+        new_features = F.max_pool2d(new_features, kernel_size=[1, new_features.size(3)]).squeeze(-1)
+        return new_xyz, new_features, inds
+
+
+class CloudCrop(nn.Module):
+    """Cylinder crop around every seed in its approach frame, for each grasp depth; shared MLP + max-pool.
+    forward(seed_xyz (B,S,3), pointcloud (B,N,3), vp_rot (B,S,3,3)) -> (B, mlps[-1], S, num_depth)."""
+
+    def __init__(self, nsample, seed_feature_dim, cylinder_radius=0.05, hmin=-0.02,
+                 hmax_list=(0.01, 0.02, 0.03, 0.04), passes=3):
+        super().__init__()
+        self.nsample, self.in_dim, self.cylinder_radius = nsample, seed_feature_dim, cylinder_radius
+        self.hmin, self.hmax_list, self.passes = hmin, list(hmax_list), passes
+        self.groupers = [pointnet2_utils.CylinderQueryAndGroup(cylinder_radius, hmin, hmax, nsample, use_xyz=True)
+                         for hmax in self.hmax_list]
+        self.mlps = SharedMLP([self.in_dim, 64, 128, 256], bn=True)
+        self._fused = _FusedMLP(self.mlps)
+
+    def forward(self, seed_xyz, pointcloud, vp_rot):
+        B, num_seed, _, _ = vp_rot.size()
+        num_depth = len(self.groupers)
+        if not self.training and not torch.is_grad_enabled() and fusable(self.mlps, self.nsample):
+            rot = vp_rot.reshape(B, num_seed, 9).contiguous()
+            idx = ops.cylinder_query_multi(seed_xyz, pointcloud, rot, self.cylinder_radius, self.hmin,
+                                           self.hmax_list, self.nsample)
+            return ops.group_mlp_maxpool(pointcloud, seed_xyz, idx, self._fused.get(), rot=rot, passes=self.passes)
+        grouped = [g(pointcloud, seed_xyz, vp_rot) for g in self.groupers]
+        grouped = torch.stack(grouped, dim=3).view(B, -1, num_seed * num_depth, self.nsample)
+        vp_features = F.max_pool2d(self.mlps(grouped), kernel_size=[1, self.nsample])
+        return vp_features.view(B, -1, num_seed, num_depth)

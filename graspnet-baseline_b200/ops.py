@@ -109,6 +109,43 @@ def gather_xyz(xyz, idx, transposed=True):
     return (out, out_t) if transposed else out
 
 
+def mlp_pack_weights(w):
+    """w (Cout,Cin) f32 (1x1 conv weight with BatchNorm folded in) -> the hi | lo K-slab packing
+    group_mlp_maxpool streams (2 * Cout * Cin floats)"""
+    _chk(w, "w", torch.float32)
+    cout, cin = w.shape
+    packed = torch.empty(2 * cout * cin, dtype=torch.float32, device=w.device)
+    with torch.cuda.device(w.device):
+        _abi.check(_lib.b200_mlp_pack_weights(_ptr(w), cout, cin, _ptr(packed), _stream()), "mlp_pack_weights")
+    return packed
+
+
+def group_mlp_maxpool(xyz, new_xyz, idx, layers, radius=0.0, rot=None, passes=3):
+    """Fused group -> (centre, /radius, rotate) -> 3 x (1x1 conv + folded BN + ReLU) -> max over nsample.
+    xyz (B,N,3), new_xyz (B,M,3), idx (B,M,ns) or (G,B,M,ns) i32, rot (B,M,3,3)/(B,M,9) or None,
+    layers = [(w1 (C1,3), b1), (w2_packed, b2, C2), (w3_packed, b3, C3)] -> (B,C3,M) or (B,C3,M,G)."""
+    _chk(xyz, "xyz", torch.float32)
+    _chk(new_xyz, "new_xyz", torch.float32)
+    _chk(idx, "idx", torch.int32)
+    squeeze = idx.dim() == 3
+    g = 1 if squeeze else idx.shape[0]
+    b, n, _ = xyz.shape
+    m, ns = idx.shape[-2], idx.shape[-1]
+    (w1, b1), (w2p, b2, c2), (w3p, b3, c3) = layers
+    for t, name in ((w1, "w1"), (b1, "b1"), (w2p, "w2"), (b2, "b2"), (w3p, "w3"), (b3, "b3")):
+        _chk(t, name, torch.float32)
+    c1 = w1.shape[0]
+    if rot is not None:
+        _chk(rot, "rot", torch.float32)
+    out = torch.empty((b, c3, m, g), dtype=torch.float32, device=xyz.device)
+    with torch.cuda.device(xyz.device):
+        _abi.check(_lib.b200_group_mlp_maxpool(_ptr(xyz), _ptr(new_xyz), _ptr(rot) if rot is not None else None,
+                                               _ptr(idx), g, b, n, m, ns, float(radius), _ptr(w1), _ptr(b1),
+                                               _ptr(w2p), _ptr(b2), _ptr(w3p), _ptr(b3), c1, c2, c3, int(passes),
+                                               _ptr(out), _stream()), "group_mlp_maxpool")
+    return out.view(b, c3, m) if squeeze else out
+
+
 def gather_points_grad(grad_out, idx, n):
     """grad_out (B,C,M) f32, idx (B,M) i32 -> (B,C,n)   [sampling.cpp:45-69]"""
     _chk(grad_out, "grad_out", torch.float32)

@@ -96,3 +96,18 @@ def synthetic_grasps(scene, m, seed=0, dtype=np.float32):
     g[:, 13:16] = np.asarray(scene, dtype=np.float64)[rng.choice(len(scene), m, replace=len(scene) < m)]
     g[:, 16] = -1
     return np.ascontiguousarray(g, dtype=dtype)
+
+
+def mlp_params(seed, dims):
+    """Seeded parameters of a shared MLP (SharedMLP(dims, bn=True), reference pytorch_utils.py:11-36):
+    [(conv weight (Cout,Cin), bn gamma, beta, running mean, running var)] per layer.  numpy only, so the golden
+    generator and the tests build exactly the same values."""
+    rng = np.random.default_rng(seed)
+    out = []
+    for cin, cout in zip(dims[:-1], dims[1:]):
+        w = (rng.standard_normal((cout, cin)) * np.sqrt(2.0 / cin)).astype(np.float32)
+        out.append((w, rng.uniform(0.5, 1.5, cout).astype(np.float32),
+                    (0.2 * rng.standard_normal(cout)).astype(np.float32),
+                    (0.3 * rng.standard_normal(cout)).astype(np.float32),
+                    rng.uniform(0.5, 2.0, cout).astype(np.float32)))
+    return out

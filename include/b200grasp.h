@@ -78,6 +78,24 @@ int b200_furthest_point_sampling_spec(const float *xyz, int b, int n, int m, con
 int b200_gather_xyz(const float *xyz, const int32_t *idx, int b, int n, int m, float *out, float *out_t,
                     void *stream);
 
+/* ---- group -> shared MLP -> max-pool as one kernel (csrc/mlp_fused.cu) -------------------
+ * Replaces, in eval mode and for modules whose grouped input is xyz only (SA1, CloudCrop), the chain
+ * QueryAndGroup / CylinderQueryAndGroup.forward (pointnet2_utils.py:313-372, 488-555) -> pt_utils.SharedMLP
+ * (pytorch_utils.py:11-36) -> F.max_pool2d over nsample (pointnet2_modules.py:243-257, models/modules.py:127-141).
+ *   xyz[B,N,3], new_xyz[B,M,3], rot[B,M,9] or NULL (rotate_xyz), idx[G,B,M,ns] (G = 1, or CloudCrop's depth lists)
+ *   radius > 0: grouped_xyz /= radius (normalize_xyz); <= 0: left as is
+ *   layer 1: w1[C1,3], b1[C1]; layers 2, 3: weights packed by b200_mlp_pack_weights, b2[C2], b3[C3]; BatchNorm is
+ *   folded into (w, b) by the caller.  out[B,C3,M,G] (= [B,C3,M] for G = 1; CloudCrop's view(B,-1,num_seed,num_depth)).
+ *   passes = 3: fp32-grade ("3xTF32" on the tensor cores), passes = 1: TF32 (cuDNN's default for the reference convs).
+ * Supported: ns in {16,32,64,128}; C1, C2 multiples of 16, C3 a multiple of 16, all <= 256 (else B200_ECAPACITY). */
+int b200_group_mlp_maxpool(const float *xyz, const float *new_xyz, const float *rot, const int32_t *idx, int g, int b,
+                           int n, int m, int ns, float radius, const float *w1, const float *b1,
+                           const float *w2_packed, const float *b2, const float *w3_packed, const float *b3, int c1,
+                           int c2, int c3, int passes, float *out, void *stream);
+/* w[cout,cin] fp32 (conv weight, BN folded) -> packed[2*cout*cin] in the order the kernel's bulk copies read:
+ * K-slabs of 16 input channels, each [hi | lo][k-chunk of 4][cout][4], hi = tf32(w), lo = tf32(w - hi). */
+int b200_mlp_pack_weights(const float *w, int cout, int cin, float *packed, void *stream);
+
 /* Replaces ball_query(new_xyz[B,M,3], xyz[B,N,3], radius, nsample) -> [B,M,nsample] i32
  * (ball_query.cpp:13-37, ball_query.h:9-10; ball_query_gpu.cu:14-49). */
 int b200_ball_query(const float *new_xyz, const float *xyz, int b, int n, int m, float radius,

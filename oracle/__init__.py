@@ -7,4 +7,4 @@ library instead of falling back to anything in here.
 """
 from .cpu import *  # noqa: F401,F403
 from .post import *  # noqa: F401,F403
-from . import cpu, post  # noqa: F401
+from . import cpu, post, mlp  # noqa: F401

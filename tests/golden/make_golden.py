@@ -16,6 +16,13 @@ neither exists on the GPU box, which only reads the committed .npz files.
                     reference file with `ast` at generation time and executed with the reference's own
                     utils/loss_utils.py::batch_viewpoint_params_to_matrix) on seeded synthetic head
                     outputs; stores the inputs and the (M,17) rows it returns.
+  mlp_*.npz       : pointnet2/pytorch_utils.py::SharedMLP (the reference's own class, imported; pure torch, runs on
+                    the CPU in fp32) in eval mode with seeded weights and BatchNorm statistics, applied to the
+                    grouped xyz tensor the QueryAndGroup / CylinderQueryAndGroup composites build
+                    (pointnet2_utils.py:345-350, 523-530; the CUDA-only grouping_operation replaced by the
+                    equivalent torch indexing), then F.max_pool2d over nsample and CloudCrop's view
+                    (models/modules.py:138-141).  Stores the geometry inputs, the seed of the parameters
+                    (tests regenerate them with synth.mlp_params) and the pooled features.
 No pointnet2 fixture can be produced here: every pointnet2 op of the reference is
 CUDA-only and this container has no GPU -- those are pinned on the GPU box against
 oracle/_ref directly (tests/test_gpu_vs_legacy.py).
@@ -192,8 +199,68 @@ def make_decode():
         print("decode", name, b, ns, [tuple(o.shape) for o in out])
 
 
+def make_mlp():
+    import torch
+    import torch.nn.functional as F
+    sys.path.insert(0, os.path.join(REF, "pointnet2"))
+    import pytorch_utils as pt_utils                       # the reference's SharedMLP
+    sys.path.insert(0, ROOT)
+    import oracle
+    oracle.cpu.build()
+    sys.path.insert(0, os.path.join(ROOT, "graspnet-baseline_b200"))
+    import synth
+    cases = (("a", 5, [3, 64, 64, 128], 1, 600, 10, 64, 0.04, False, 1),      # SA1-like: /radius, no rotation
+             ("b", 6, [3, 64, 128, 256], 2, 800, 6, 64, 0.05, True, 4),       # CloudCrop-like: 4 depth lists, rotated
+             ("c", 7, [3, 32, 48, 80], 1, 300, 9, 16, 0.3, True, 2))          # odd widths, 16-row lists
+    for name, seed, dims, b, n, m, ns, radius, crop, g in cases:
+        xyz = np.stack([synth.tabletop_cloud(n, seed + i) for i in range(b)])
+        first = oracle.furthest_point_sampling(xyz, m)
+        new_xyz = np.stack([xyz[i][first[i]] for i in range(b)])
+        if crop:
+            rot = np.stack([synth.seed_rotations(m, seed + i) for i in range(b)]).reshape(b, m, 9)
+            hmax = [0.01 * (k + 1) for k in range(g)]
+            idx = np.stack([oracle.cylinder_query(new_xyz, xyz, rot, radius, -0.02, h, ns) for h in hmax])
+            norm_radius = 0.0
+        else:
+            rot = None
+            idx = oracle.ball_query(new_xyz, xyz, radius, ns)[None]
+            norm_radius = radius
+        params = synth.mlp_params(seed, dims)
+        mlp = pt_utils.SharedMLP(list(dims), bn=True)
+        with torch.no_grad():
+            for layer, (w, gamma, beta, mean, var) in zip(mlp, params):
+                layer.conv.weight.copy_(torch.from_numpy(w)[:, :, None, None])
+                layer.bn.bn.weight.copy_(torch.from_numpy(gamma))
+                layer.bn.bn.bias.copy_(torch.from_numpy(beta))
+                layer.bn.bn.running_mean.copy_(torch.from_numpy(mean))
+                layer.bn.bn.running_var.copy_(torch.from_numpy(var))
+        mlp.eval()
+        feats = []
+        tx, tc = torch.from_numpy(xyz), torch.from_numpy(new_xyz)
+        for k in range(idx.shape[0]):
+            ti = torch.from_numpy(idx[k]).long()
+            grouped = torch.stack([tx[i].t()[:, ti[i]] for i in range(b)])          # (B,3,m,ns) = grouping_operation
+            grouped = grouped - tc.transpose(1, 2).unsqueeze(-1)
+            if norm_radius:
+                grouped = grouped / norm_radius
+            if rot is not None:
+                g_ = grouped.permute(0, 2, 3, 1).contiguous()
+                g_ = torch.matmul(g_, torch.from_numpy(rot).view(b, m, 3, 3))
+                grouped = g_.permute(0, 3, 1, 2).contiguous()
+            feats.append(grouped)
+        x = torch.stack(feats, dim=3).view(b, 3, m * idx.shape[0], ns)                # modules.py:131-132
+        with torch.no_grad():
+            y = F.max_pool2d(mlp(x), kernel_size=[1, ns]).view(b, -1, m, idx.shape[0])
+        np.savez_compressed(os.path.join(HERE, f"mlp_{name}.npz"), xyz=xyz, new_xyz=new_xyz, idx=idx,
+                            rot=np.zeros(0, np.float32) if rot is None else rot, radius=np.float32(norm_radius),
+                            seed=seed, dims=np.array(dims), out=y.numpy())
+        print("mlp", name, dims, tuple(y.shape), float(y.abs().max()))
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["collision", "knn", "decode"]
+    which = sys.argv[1:] or ["collision", "knn", "decode", "mlp"]
+    if "mlp" in which:
+        make_mlp()
     if "collision" in which:
         make_collision()
     if "knn" in which:
