@@ -19,15 +19,20 @@
 // a.b ~= a_lo.b_hi + a_hi.b_lo + a_hi.b_hi, accumulated in fp32; the dropped a_lo.b_lo term is 2^-22 relative.
 // `passes` = 1 runs plain TF32 (what cuDNN does for the reference's convs under torch's default allow_tf32).
 //
-// Pipeline inside a CTA (persistent over tiles), 6 warps:
-//   warps 0-3  one thread per row: gather + layer 1, then the epilogues.  They PRODUCE the A operand of the next layer
-//              in K-slabs of 16 channels (hi and lo parts, 16 KB) into a 4-slot ring: the epilogue of layer l for
-//              channels [16 s, 16 s + 16) is the K-slab s of layer l + 1, so the tensor core starts layer l + 1 while
-//              the CUDA cores are still converting layer l, and no layer's activations are ever held whole.
-//   warp 4     lane 0 issues the MMAs: per slab 2 K-steps x 3 passes, then tcgen05.commit releases the A slot and the
+// Pipeline inside a CTA (persistent over tiles), 10 warps:
+//   warps 0-7  row threads.  Warp w works on rows 32 (w % 4) .. + 31 (the TMEM lanes a warp may read) and on the
+//              K-slabs s with s % 2 == w / 4, so every scheduler holds two row warps.  They gather + run layer 1, then
+//              the epilogues, and PRODUCE the A operand of the next layer in K-slabs of 16 channels (hi and lo parts,
+//              16 KB) into a 4-slot ring: the epilogue of layer l for channels [16 s, 16 s + 16) is the K-slab s of
+//              layer l + 1, so the tensor core starts layer l + 1 while the CUDA cores are still converting layer l,
+//              and no layer's activations are ever held whole.
+//   warp 8     lane 0 issues the MMAs: per slab 2 K-steps x 3 passes, then tcgen05.commit releases the A slot and the
 //              weight slot; after a layer's last slab a commit tells the row threads its accumulators are complete.
-//   warp 5     lane 0 streams the weight slabs (host-packed: hi | lo, core-matrix order) global/L2 -> shared with
+//   warp 9     lane 0 streams the weight slabs (host-packed: hi | lo, core-matrix order) global/L2 -> shared with
 //              cp.async.bulk into a 4-slot ring (W2 + W3 in 3xTF32 form are 320 KB: they cannot stay resident).
+// Max-pool: max commutes with the (monotone) bias add and ReLU, so the layer-3 epilogue reduces the RAW accumulators
+// over the 32 rows of a warp with one redux.sync.max.NaN.f32 per channel and bias + ReLU are applied once per
+// (list, channel) when the warps' partial maxima are combined.
 // Shared-memory operand layout (both A and B are "K-major, no swizzle" UMMA operands): for each 16-byte K-chunk
 // (4 tf32) the rows are contiguous, i.e. byte offset = chunk * rows * 16 + row * 16; a thread stores its row's
 // chunk with one st.shared.v4 and a warp's stores are 512 contiguous bytes.
@@ -44,7 +49,8 @@ constexpr int A_SLOT = 2 * A_PART;
 constexpr int MAXC = 256;                      // widest layer
 constexpr int W_SLOT = MAXC * KS * 4 * 2;      // 32 KB: hi | lo of a weight slab of the widest layer
 constexpr int MAXE = 8;                        // pooling entries per tile (128 / nsample, at least one per warp)
-constexpr int NTHREADS = 192;
+constexpr int ROW_THREADS = 256;               // two per row: even / odd K-slabs
+constexpr int NTHREADS = ROW_THREADS + 64;
 
 struct Params {
   const float *xyz, *new_xyz, *rot;
@@ -64,17 +70,29 @@ struct Smem {
   // offsets into the dynamic shared memory block
   static constexpr int a_ring = 0;
   static constexpr int w_ring = a_ring + NA * A_SLOT;
-  static constexpr int consts = w_ring + NWS * W_SLOT;               // w1 (C1*3) | b1 | b2 | b3
-  static constexpr int pool = consts + (MAXC * 3 + 3 * MAXC) * 4;   // MAXE x C3
-  static constexpr int bars = pool + MAXE * MAXC * 4;                // a_full, a_empty, w_full, w_empty, acc_full[2]
+  static constexpr int consts = w_ring + NWS * W_SLOT;               // {w1[c][0..2], b1[c]} (C1 float4) | b2 | b3
+  static constexpr int pool = consts + (MAXC * 4 + 2 * MAXC) * 4;   // MAXE x C3
+  static constexpr int bars = pool + 2 * MAXE * MAXC * 4;            // (two pools: tiles alternate)                // a_full, a_empty, w_full, w_empty, acc_full[2]
   static constexpr int holder = bars + (2 * NA + 2 * NWS + 2) * 8;
   static constexpr int total = holder + 16;
 };
 
 __device__ __forceinline__ float relu_keep_nan(float v) { return (v <= 0.f) ? 0.f : v; }
 
-// one 16-channel slab of this row into the A ring (waits for the slot, splits hi / lo, publishes)
-__device__ __forceinline__ void put_slab(uint32_t sm, const float (&v)[16], int row, uint32_t &na, int passes) {
+__device__ __forceinline__ float max_nan(float a, float b) {
+  float r;
+  asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ float warp_max_nan(float v) {
+  float r;
+  asm volatile("redux.sync.max.NaN.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+  return r;
+}
+
+// one 16-channel slab of this row into ring slot (na % NA): waits for the slot, splits hi / lo, publishes.
+// hi = tf32(v) rounded to nearest; lo = v - hi exactly (the tensor core drops its low 13 mantissa bits: 2^-21 of v).
+__device__ __forceinline__ void put_slab(uint32_t sm, const float (&v)[16], int row, uint32_t na, int passes) {
   const uint32_t slot = na % NA, ph = (na / NA) & 1u;
   const uint32_t a_full = sm + Smem::bars + slot * 8, a_empty = sm + Smem::bars + (NA + slot) * 8;
   tc::mbar_wait(a_empty, ph ^ 1u);
@@ -85,7 +103,7 @@ __device__ __forceinline__ void put_slab(uint32_t sm, const float (&v)[16], int 
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
       hi[e] = tc::tf32_rna(v[4 * kc + e]);
-      lo[e] = tc::tf32_rna(v[4 * kc + e] - hi[e]);
+      lo[e] = __fsub_rn(v[4 * kc + e], hi[e]);
     }
     asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(base + kc * (TM * 16)), "f"(hi[0]), "f"(hi[1]),
                  "f"(hi[2]), "f"(hi[3]) : "memory");
@@ -96,7 +114,6 @@ __device__ __forceinline__ void put_slab(uint32_t sm, const float (&v)[16], int 
   tc::fence_proxy_async();
   tc::fence_before_sync();
   tc::mbar_arrive(a_full);
-  ++na;
 }
 
 __global__ void __launch_bounds__(NTHREADS, 1)
@@ -104,18 +121,18 @@ group_mlp_maxpool_kernel(const Params p) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   const uint32_t sm = tc::smem_u32(smem_raw);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  float *cst = reinterpret_cast<float *>(smem_raw + Smem::consts);
-  float *w1s = cst, *b1s = cst + MAXC * 3, *b2s = b1s + MAXC, *b3s = b2s + MAXC;
-  float *pool = reinterpret_cast<float *>(smem_raw + Smem::pool);
+  float4 *w1s = reinterpret_cast<float4 *>(smem_raw + Smem::consts);
+  float *b2s = reinterpret_cast<float *>(w1s + MAXC), *b3s = b2s + MAXC;
+  float *pools = reinterpret_cast<float *>(smem_raw + Smem::pool);
   volatile uint32_t *holder = reinterpret_cast<volatile uint32_t *>(smem_raw + Smem::holder);
 
-  for (int i = tid; i < p.C1 * 3; i += NTHREADS) w1s[i] = __ldg(p.w1 + i);
-  for (int i = tid; i < p.C1; i += NTHREADS) b1s[i] = __ldg(p.b1 + i);
+  for (int i = tid; i < p.C1; i += NTHREADS)
+    w1s[i] = make_float4(__ldg(p.w1 + 3 * i), __ldg(p.w1 + 3 * i + 1), __ldg(p.w1 + 3 * i + 2), __ldg(p.b1 + i));
   for (int i = tid; i < p.C2; i += NTHREADS) b2s[i] = __ldg(p.b2 + i);
   for (int i = tid; i < p.C3; i += NTHREADS) b3s[i] = __ldg(p.b3 + i);
   if (tid == 0) {
     for (int s = 0; s < NA; ++s) {
-      tc::mbar_init(sm + Smem::bars + s * 8, TM);                    // a_full: every row thread arrives
+      tc::mbar_init(sm + Smem::bars + s * 8, TM);                    // a_full: the 128 row threads of one half
       tc::mbar_init(sm + Smem::bars + (NA + s) * 8, 1);              // a_empty: one tcgen05.commit
     }
     for (int s = 0; s < NWS; ++s) {
@@ -126,20 +143,25 @@ group_mlp_maxpool_kernel(const Params p) {
     tc::mbar_init(sm + Smem::bars + (2 * NA + 2 * NWS + 1) * 8, 1);  // acc_full[1]: layer-3
     tc::fence_barrier_init();
   }
-  if (warp == 4) tc::tmem_alloc_512(sm + Smem::holder);
+  if (warp == 8) tc::tmem_alloc_512(sm + Smem::holder);
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem = *holder;
   const uint32_t acc_full0 = sm + Smem::bars + (2 * NA + 2 * NWS) * 8, acc_full1 = acc_full0 + 8;
 
-  if (warp < 4) {
+  if (warp < 8) {
     // ------------------------------------------------------------------ row threads
-    const int row = tid;
+    const int half = warp >> 2;                                       // K-slabs s with (s & 1) == half
+    const int row = (warp & 3) * 32 + lane;
     const int lpt = TM / p.ns;                                        // lists per tile
-    const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
-    uint32_t na = 0;
+    const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+    const int s1 = p.C1 / KS, s2 = p.C2 / KS, s3 = p.C3 / KS;
+    uint32_t na = 0;                                                  // A slabs published so far (by both halves)
     for (int tile = blockIdx.x, it = 0; tile < p.tiles; tile += gridDim.x, ++it) {
+      // the pooling scratch alternates between tiles: a warp may start tile t + 1's layer-3 epilogue while
+      // another still combines tile t (they meet again at tile t + 1's barrier before the buffer is reused)
+      float *pool = pools + (it & 1) * (MAXE * MAXC);
       // gather: this row's neighbour, in the frame of its list's centre
       const long long q = (long long)tile * lpt + row / p.ns;
       float g0 = 0.f, g1 = 0.f, g2 = 0.f;
@@ -165,66 +187,74 @@ group_mlp_maxpool_kernel(const Params p) {
         }
       }
       // layer 1 on the CUDA cores -> K-slabs of layer 2
-      for (int s = 0; s < p.C1 / KS; ++s) {
+      for (int s = half; s < s1; s += 2) {
         float v[16];
 #pragma unroll
         for (int c = 0; c < 16; ++c) {
-          const float *w = w1s + (s * KS + c) * 3;
-          const float a = __fmaf_rn(w[2], g2, __fmaf_rn(w[1], g1, __fmul_rn(w[0], g0)));
-          v[c] = relu_keep_nan(__fadd_rn(a, b1s[s * KS + c]));
+          const float4 w = w1s[s * KS + c];
+          const float a = __fmaf_rn(w.z, g2, __fmaf_rn(w.y, g1, __fmul_rn(w.x, g0)));
+          v[c] = relu_keep_nan(__fadd_rn(a, w.w));
         }
-        put_slab(sm, v, row, na, p.passes);
+        put_slab(sm, v, row, na + s, p.passes);
       }
+      na += s1;
       // layer-2 epilogue -> K-slabs of layer 3
       tc::mbar_wait(acc_full0, it & 1);
       tc::fence_after_sync();
-      for (int s = 0; s < p.C2 / KS; ++s) {
+      for (int s = half; s < s2; s += 2) {
         float v[16];
         tc::tmem_ld16(lane_base + s * KS, v);
 #pragma unroll
         for (int c = 0; c < 16; ++c) v[c] = relu_keep_nan(__fadd_rn(v[c], b2s[s * KS + c]));
-        put_slab(sm, v, row, na, p.passes);
+        put_slab(sm, v, row, na + s, p.passes);
       }
-      // layer-3 epilogue: bias, ReLU, max over the rows of a pooling entry (values are >= +0 or NaN, so the
-      // unsigned order of the bit patterns is the float order and NaN wins, as in max_pool2d)
+      na += s2;
+      // layer-3 epilogue: max of the raw accumulators over the rows of a pooling entry (a warp's 32 rows, or 16)
       tc::mbar_wait(acc_full1, it & 1);
       tc::fence_after_sync();
-      const int entry = p.ns >= 32 ? warp : row / p.ns;
-      for (int s = 0; s < p.C3 / KS; ++s) {
+      for (int s = half; s < s3; s += 2) {
         float v[16];
         tc::tmem_ld16(lane_base + p.C2 + s * KS, v);
-        unsigned mine = 0;
+        if (p.ns >= 32) {
 #pragma unroll
-        for (int c = 0; c < 16; ++c) {
-          unsigned u = __float_as_uint(relu_keep_nan(__fadd_rn(v[c], b3s[s * KS + c])));
-          if (p.ns >= 32) {
-            u = __reduce_max_sync(0xffffffffu, u);
-          } else {
-            for (int o = p.ns >> 1; o >= 1; o >>= 1) u = max(u, __shfl_xor_sync(0xffffffffu, u, o));
+          for (int c = 0; c < 16; ++c) v[c] = warp_max_nan(v[c]);
+          if (lane == 0) {
+            float4 *dst = reinterpret_cast<float4 *>(pool + (warp & 3) * MAXC + s * KS);
+#pragma unroll
+            for (int c4 = 0; c4 < 4; ++c4) dst[c4] = make_float4(v[4 * c4], v[4 * c4 + 1], v[4 * c4 + 2], v[4 * c4 + 3]);
           }
-          if ((lane & 15) == c) mine = u;
+        } else {                                                      // 16-row lists: two entries per warp
+#pragma unroll
+          for (int c = 0; c < 16; ++c) {
+#pragma unroll
+            for (int o = 8; o >= 1; o >>= 1) v[c] = max_nan(v[c], __shfl_xor_sync(0xffffffffu, v[c], o));
+          }
+          if ((lane & 15) == 0) {
+            float4 *dst = reinterpret_cast<float4 *>(pool + (row / 16) * MAXC + s * KS);
+#pragma unroll
+            for (int c4 = 0; c4 < 4; ++c4) dst[c4] = make_float4(v[4 * c4], v[4 * c4 + 1], v[4 * c4 + 2], v[4 * c4 + 3]);
+          }
         }
-        // one lane per (entry, channel): a warp is one entry (lanes 0-15 write) or, for 16-row lists, two
-        if (p.ns >= 32 ? lane < 16 : true) pool[entry * MAXC + s * KS + (lane & 15)] = __uint_as_float(mine);
       }
       tc::fence_before_sync();
-      tc::named_barrier(1, TM);
-      // combine the entries of each list and write (B, C3, m, G)
+      tc::named_barrier(1, ROW_THREADS);
+      // combine the entries of each list, bias + ReLU, write (B, C3, m, G)
       const int epl = p.ns >= 32 ? p.ns / 32 : 1;                     // entries per list
-      for (int c = tid; c < p.C3; c += TM) {
+      for (int c = tid; c < p.C3; c += ROW_THREADS) {
+        const float bias = b3s[c];
         for (int l = 0; l < lpt; ++l) {
           const long long ql = (long long)tile * lpt + l;
           if (ql >= p.Q) break;
-          unsigned u = 0;
-          for (int e = 0; e < epl; ++e) u = max(u, __float_as_uint(pool[(l * epl + e) * MAXC + c]));
+          float u = pool[(l * epl) * MAXC + c];
+          for (int e = 1; e < epl; ++e) u = max_nan(u, pool[(l * epl + e) * MAXC + c]);
           const int gi = (int)(ql % p.G);
           const long long t = ql / p.G;
           const int seed = (int)(t % p.m), bi = (int)(t / p.m);
-          p.out[(((long long)bi * p.C3 + c) * p.m + seed) * p.G + gi] = __uint_as_float(u);
+          p.out[(((long long)bi * p.C3 + c) * p.m + seed) * p.G + gi] = relu_keep_nan(__fadd_rn(u, bias));
         }
       }
     }
-  } else if (warp == 4) {
+  } else if (warp == 8) {
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0) {
       uint32_t na = 0, nw = 0;
@@ -287,7 +317,7 @@ group_mlp_maxpool_kernel(const Params p) {
   }
   tc::fence_before_sync();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == 8) {
     __syncwarp();
     tc::tmem_dealloc_512(tmem);
   }
