@@ -158,11 +158,9 @@ group_mlp_maxpool_kernel(const Params p) {
     const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
     const int s1 = p.C1 / KS, s2 = p.C2 / KS, s3 = p.C3 / KS;
     uint32_t na = 0;                                                  // A slabs published so far (by both halves)
-    for (int tile = blockIdx.x, it = 0; tile < p.tiles; tile += gridDim.x, ++it) {
-      // the pooling scratch alternates between tiles: a warp may start tile t + 1's layer-3 epilogue while
-      // another still combines tile t (they meet again at tile t + 1's barrier before the buffer is reused)
-      float *pool = pools + (it & 1) * (MAXE * MAXC);
-      // gather: this row's neighbour, in the frame of its list's centre
+    // gather + layer 1 of a tile: this row's neighbour in the frame of its list's centre, then the C1 outputs on
+    // the CUDA cores -> K-slabs of layer 2
+    auto gather_layer1 = [&](int tile) {
       const long long q = (long long)tile * lpt + row / p.ns;
       float g0 = 0.f, g1 = 0.f, g2 = 0.f;
       if (q < p.Q) {
@@ -186,7 +184,6 @@ group_mlp_maxpool_kernel(const Params p) {
           g0 = d0; g1 = d1; g2 = d2;
         }
       }
-      // layer 1 on the CUDA cores -> K-slabs of layer 2
       for (int s = half; s < s1; s += 2) {
         float v[16];
 #pragma unroll
@@ -198,6 +195,17 @@ group_mlp_maxpool_kernel(const Params p) {
         put_slab(sm, v, row, na + s, p.passes);
       }
       na += s1;
+    };
+    // Software pipeline over tiles: the next tile's gather + layer 1 is issued BEFORE this tile's layer-3 epilogue,
+    // so the CUDA cores work on tile t + 1 while the tensor core finishes layer 3 of tile t, and the tensor core
+    // runs layer 2 of tile t + 1 under the layer-3 epilogue of tile t.  No extra TMEM: layer 2 of t + 1 writes the
+    // columns whose epilogue (tile t) is already done, and layer 3 of t + 1 only starts on slabs produced after
+    // this thread's layer-3 epilogue of tile t.
+    if ((int)blockIdx.x < p.tiles) gather_layer1(blockIdx.x);
+    for (int tile = blockIdx.x, it = 0; tile < p.tiles; tile += gridDim.x, ++it) {
+      // the pooling scratch alternates between tiles: a warp may start tile t + 1's layer-3 epilogue while
+      // another still combines tile t (they meet again at tile t + 1's barrier before the buffer is reused)
+      float *pool = pools + (it & 1) * (MAXE * MAXC);
       // layer-2 epilogue -> K-slabs of layer 3
       tc::mbar_wait(acc_full0, it & 1);
       tc::fence_after_sync();
@@ -209,6 +217,7 @@ group_mlp_maxpool_kernel(const Params p) {
         put_slab(sm, v, row, na + s, p.passes);
       }
       na += s2;
+      if (tile + (int)gridDim.x < p.tiles) gather_layer1(tile + gridDim.x);
       // layer-3 epilogue: max of the raw accumulators over the rows of a pooling entry (a warp's 32 rows, or 16)
       tc::mbar_wait(acc_full1, it & 1);
       tc::fence_after_sync();
