@@ -43,7 +43,8 @@ SIGNATURES = {
     "b200_gather_rows": [_vp, _i, _vp, _vp, _i, _vp, _vp],
     "b200_fps_prefix_check": [_vp, _i, _i, _i, ctypes.c_longlong, _vp, _vp],
     "b200_furthest_point_sampling_spec": [_vp, _i, _i, _i, _vp, _i, _vp, _i, _vp, _i, _vp, _vp],
-    "b200_group_mlp_maxpool": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp],
+    "b200_group_mlp_maxpool": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp],
+    "b200_group_feat_mlp_maxpool": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp],
     "b200_mlp_pack_weights": [_vp, _i, _i, _vp, _vp],
     "b200_gather_xyz": [_vp, _vp, _i, _i, _i, _vp, _vp, _vp],
     "b200_pred_decode": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp],

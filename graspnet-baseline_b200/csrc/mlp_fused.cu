@@ -18,6 +18,11 @@
 // fp32-grade results from tf32 tensor cores ("3xTF32"): x = hi + lo with hi = tf32(x), lo = tf32(x - hi), and
 // a.b ~= a_lo.b_hi + a_hi.b_lo + a_hi.b_hi, accumulated in fp32; the dropped a_lo.b_lo term is 2^-22 relative.
 // `passes` = 1 runs plain TF32 (what cuDNN does for the reference's convs under torch's default allow_tf32).
+// Modules with point features (SA2-SA4: grouped input = [xyz | C features], K = 131 / 259): the first layer is a
+// tensor-core layer too.  Its A operand is gathered straight into K-slabs -- the features are read CHANNELS-LAST
+// (B, N, C), one neighbour's 16 channels = four 16-byte loads, the K order is [features | x y z | zero pad to 16]
+// (the host packs W1's columns the same way) -- and the three accumulators (C1 + C2 + C3 = 512 columns for
+// 128/128/256) fill TMEM exactly.  The kernel writes its output a second time channels-last for the next module.
 //
 // Pipeline inside a CTA (persistent over tiles), 10 warps:
 //   warps 0-7  row threads.  Warp w works on rows 32 (w % 4) .. + 31 (the TMEM lanes a warp may read) and on the
@@ -57,23 +62,30 @@ struct Params {
   const int32_t *idx;
   int G, B, N, m, ns;
   float radius;                                // > 0: grouped_xyz /= radius (normalize_xyz)
-  const float *w1, *b1;                        // (C1, 3), (C1): layer 1, BN folded
-  const float *w2p, *b2;                       // packed (mlp_pack_kernel), (C2)
-  const float *w3p, *b3;
-  int C1, C2, C3, passes;
+  const float *feat_t;                         // (B, N, C) channels-last point features, or NULL (xyz-only module)
+  int C;
+  const float *w1, *b1;                        // xyz-only: first layer (C0, 3), (C0) for the CUDA cores, BN folded
+  int C0;
+  int NG;                                      // tensor-core layers: 2 (xyz-only) or 3 (with features)
+  const float *wp[3];                          // packed weights (mlp_pack_kernel) of the tensor-core layers
+  const float *bias[3];
+  int Kd[3], Nd[3];
+  int passes;
   long long Q;                                 // lists = B * m * G
   int tiles;
   float *out;                                  // (B, C3, m, G)
+  float *out_t;                                // (B, m, G, C3) channels-last copy for the next module, or NULL
 };
 
 struct Smem {
   // offsets into the dynamic shared memory block
   static constexpr int a_ring = 0;
   static constexpr int w_ring = a_ring + NA * A_SLOT;
-  static constexpr int consts = w_ring + NWS * W_SLOT;               // {w1[c][0..2], b1[c]} (C1 float4) | b2 | b3
-  static constexpr int pool = consts + (MAXC * 4 + 2 * MAXC) * 4;   // MAXE x C3
-  static constexpr int bars = pool + 2 * MAXE * MAXC * 4;            // (two pools: tiles alternate)                // a_full, a_empty, w_full, w_empty, acc_full[2]
-  static constexpr int holder = bars + (2 * NA + 2 * NWS + 2) * 8;
+  static constexpr int consts = w_ring + NWS * W_SLOT;               // {w1[c][0..2], b1[c]} (float4 x MAXC) | bias[3][MAXC]
+  static constexpr int pool = consts + (MAXC * 4 + 3 * MAXC) * 4;   // MAXE x C3
+  static constexpr int bars = pool + 2 * MAXE * MAXC * 4;            // (two pools: tiles alternate); then a_full,
+                                                                     // a_empty, w_full, w_empty, acc_full[3]
+  static constexpr int holder = bars + (2 * NA + 2 * NWS + 3) * 8;
   static constexpr int total = holder + 16;
 };
 
@@ -122,14 +134,16 @@ group_mlp_maxpool_kernel(const Params p) {
   const uint32_t sm = tc::smem_u32(smem_raw);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   float4 *w1s = reinterpret_cast<float4 *>(smem_raw + Smem::consts);
-  float *b2s = reinterpret_cast<float *>(w1s + MAXC), *b3s = b2s + MAXC;
+  float *biases = reinterpret_cast<float *>(w1s + MAXC);              // [layer][MAXC]
   float *pools = reinterpret_cast<float *>(smem_raw + Smem::pool);
   volatile uint32_t *holder = reinterpret_cast<volatile uint32_t *>(smem_raw + Smem::holder);
+  const bool with_feat = p.feat_t != nullptr;
 
-  for (int i = tid; i < p.C1; i += NTHREADS)
-    w1s[i] = make_float4(__ldg(p.w1 + 3 * i), __ldg(p.w1 + 3 * i + 1), __ldg(p.w1 + 3 * i + 2), __ldg(p.b1 + i));
-  for (int i = tid; i < p.C2; i += NTHREADS) b2s[i] = __ldg(p.b2 + i);
-  for (int i = tid; i < p.C3; i += NTHREADS) b3s[i] = __ldg(p.b3 + i);
+  if (!with_feat)
+    for (int i = tid; i < p.C0; i += NTHREADS)
+      w1s[i] = make_float4(__ldg(p.w1 + 3 * i), __ldg(p.w1 + 3 * i + 1), __ldg(p.w1 + 3 * i + 2), __ldg(p.b1 + i));
+  for (int l = 0; l < p.NG; ++l)
+    for (int i = tid; i < p.Nd[l]; i += NTHREADS) biases[l * MAXC + i] = __ldg(p.bias[l] + i);
   if (tid == 0) {
     for (int s = 0; s < NA; ++s) {
       tc::mbar_init(sm + Smem::bars + s * 8, TM);                    // a_full: the 128 row threads of one half
@@ -139,8 +153,8 @@ group_mlp_maxpool_kernel(const Params p) {
       tc::mbar_init(sm + Smem::bars + (2 * NA + s) * 8, 1);          // w_full: expect_tx arrival + bytes
       tc::mbar_init(sm + Smem::bars + (2 * NA + NWS + s) * 8, 1);    // w_empty: one tcgen05.commit
     }
-    tc::mbar_init(sm + Smem::bars + (2 * NA + 2 * NWS) * 8, 1);      // acc_full[0]: layer-2 accumulators complete
-    tc::mbar_init(sm + Smem::bars + (2 * NA + 2 * NWS + 1) * 8, 1);  // acc_full[1]: layer-3
+    for (int l = 0; l < 3; ++l)                                      // acc_full[l]: accumulators of tensor-core
+      tc::mbar_init(sm + Smem::bars + (2 * NA + 2 * NWS + l) * 8, 1);  // layer l complete (one tcgen05.commit)
     tc::fence_barrier_init();
   }
   if (warp == 8) tc::tmem_alloc_512(sm + Smem::holder);
@@ -148,7 +162,10 @@ group_mlp_maxpool_kernel(const Params p) {
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem = *holder;
-  const uint32_t acc_full0 = sm + Smem::bars + (2 * NA + 2 * NWS) * 8, acc_full1 = acc_full0 + 8;
+  const uint32_t acc_full = sm + Smem::bars + (2 * NA + 2 * NWS) * 8;     // + 8 l
+  uint32_t col[3];                                                    // first TMEM column of layer l's accumulators
+  col[0] = 0; col[1] = (uint32_t)p.Nd[0]; col[2] = (uint32_t)(p.Nd[0] + p.Nd[1]);
+  const int C3 = p.Nd[p.NG - 1];
 
   if (warp < 8) {
     // ------------------------------------------------------------------ row threads
@@ -156,19 +173,21 @@ group_mlp_maxpool_kernel(const Params p) {
     const int row = (warp & 3) * 32 + lane;
     const int lpt = TM / p.ns;                                        // lists per tile
     const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
-    const int s1 = p.C1 / KS, s2 = p.C2 / KS, s3 = p.C3 / KS;
+    const int s0 = with_feat ? p.Kd[0] / KS : p.C0 / KS;             // slabs gather (+ layer 1) produces per tile
     uint32_t na = 0;                                                  // A slabs published so far (by both halves)
     // gather + layer 1 of a tile: this row's neighbour in the frame of its list's centre, then the C1 outputs on
     // the CUDA cores -> K-slabs of layer 2
     auto gather_layer1 = [&](int tile) {
       const long long q = (long long)tile * lpt + row / p.ns;
       float g0 = 0.f, g1 = 0.f, g2 = 0.f;
+      const float4 *frow = nullptr;
       if (q < p.Q) {
         const int gi = (int)(q % p.G);
         const long long t = q / p.G;
         const int seed = (int)(t % p.m), bi = (int)(t / p.m);
         const int i = __ldg(p.idx + ((((long long)gi * p.B + bi) * p.m + seed) * p.ns + row % p.ns));
         const float *pt = p.xyz + ((long long)bi * p.N + i) * 3;
+        if (with_feat) frow = reinterpret_cast<const float4 *>(p.feat_t + ((long long)bi * p.N + i) * p.C);
         const float *ct = p.new_xyz + ((long long)bi * p.m + seed) * 3;
         float d0 = __fsub_rn(__ldg(pt), __ldg(ct)), d1 = __fsub_rn(__ldg(pt + 1), __ldg(ct + 1)),
               d2 = __fsub_rn(__ldg(pt + 2), __ldg(ct + 2));
@@ -184,7 +203,28 @@ group_mlp_maxpool_kernel(const Params p) {
           g0 = d0; g1 = d1; g2 = d2;
         }
       }
-      for (int s = half; s < s1; s += 2) {
+      if (with_feat) {
+        // K order of layer 1: [features (C) | x y z | zero pad]: whole feature slabs are four 16-byte loads
+        const int sf = p.C / KS;
+        for (int s = half; s < s0; s += 2) {
+          float v[16];
+          if (s < sf && frow) {
+#pragma unroll
+            for (int c4 = 0; c4 < 4; ++c4) {
+              const float4 f = __ldg(frow + s * 4 + c4);
+              v[4 * c4] = f.x; v[4 * c4 + 1] = f.y; v[4 * c4 + 2] = f.z; v[4 * c4 + 3] = f.w;
+            }
+          } else {
+#pragma unroll
+            for (int c = 0; c < 16; ++c) v[c] = 0.f;
+            if (s == sf) { v[0] = g0; v[1] = g1; v[2] = g2; }
+          }
+          put_slab(sm, v, row, na + s, p.passes);
+        }
+        na += s0;
+        return;
+      }
+      for (int s = half; s < s0; s += 2) {
         float v[16];
 #pragma unroll
         for (int c = 0; c < 16; ++c) {
@@ -194,7 +234,7 @@ group_mlp_maxpool_kernel(const Params p) {
         }
         put_slab(sm, v, row, na + s, p.passes);
       }
-      na += s1;
+      na += s0;
     };
     // Software pipeline over tiles: the next tile's gather + layer 1 is issued BEFORE this tile's layer-3 epilogue,
     // so the CUDA cores work on tile t + 1 while the tensor core finishes layer 3 of tile t, and the tensor core
@@ -206,24 +246,28 @@ group_mlp_maxpool_kernel(const Params p) {
       // the pooling scratch alternates between tiles: a warp may start tile t + 1's layer-3 epilogue while
       // another still combines tile t (they meet again at tile t + 1's barrier before the buffer is reused)
       float *pool = pools + (it & 1) * (MAXE * MAXC);
-      // layer-2 epilogue -> K-slabs of layer 3
-      tc::mbar_wait(acc_full0, it & 1);
-      tc::fence_after_sync();
-      for (int s = half; s < s2; s += 2) {
-        float v[16];
-        tc::tmem_ld16(lane_base + s * KS, v);
+      // epilogues of all tensor-core layers but the last -> K-slabs of the next layer
+      for (int l = 0; l + 1 < p.NG; ++l) {
+        tc::mbar_wait(acc_full + 8 * l, it & 1);
+        tc::fence_after_sync();
+        const int sl = p.Nd[l] / KS;
+        const float *bl = biases + l * MAXC;
+        for (int s = half; s < sl; s += 2) {
+          float v[16];
+          tc::tmem_ld16(lane_base + col[l] + s * KS, v);
 #pragma unroll
-        for (int c = 0; c < 16; ++c) v[c] = relu_keep_nan(__fadd_rn(v[c], b2s[s * KS + c]));
-        put_slab(sm, v, row, na + s, p.passes);
+          for (int c = 0; c < 16; ++c) v[c] = relu_keep_nan(__fadd_rn(v[c], bl[s * KS + c]));
+          put_slab(sm, v, row, na + s, p.passes);
+        }
+        na += sl;
       }
-      na += s2;
       if (tile + (int)gridDim.x < p.tiles) gather_layer1(tile + gridDim.x);
       // layer-3 epilogue: max of the raw accumulators over the rows of a pooling entry (a warp's 32 rows, or 16)
-      tc::mbar_wait(acc_full1, it & 1);
+      tc::mbar_wait(acc_full + 8 * (p.NG - 1), it & 1);
       tc::fence_after_sync();
-      for (int s = half; s < s3; s += 2) {
+      for (int s = half; s < C3 / KS; s += 2) {
         float v[16];
-        tc::tmem_ld16(lane_base + p.C2 + s * KS, v);
+        tc::tmem_ld16(lane_base + col[p.NG - 1] + s * KS, v);
         if (p.ns >= 32) {
 #pragma unroll
           for (int c = 0; c < 16; ++c) v[c] = warp_max_nan(v[c]);
@@ -249,8 +293,8 @@ group_mlp_maxpool_kernel(const Params p) {
       tc::named_barrier(1, ROW_THREADS);
       // combine the entries of each list, bias + ReLU, write (B, C3, m, G)
       const int epl = p.ns >= 32 ? p.ns / 32 : 1;                     // entries per list
-      for (int c = tid; c < p.C3; c += ROW_THREADS) {
-        const float bias = b3s[c];
+      for (int c = tid; c < C3; c += ROW_THREADS) {
+        const float bias = biases[(p.NG - 1) * MAXC + c];
         for (int l = 0; l < lpt; ++l) {
           const long long ql = (long long)tile * lpt + l;
           if (ql >= p.Q) break;
@@ -259,7 +303,9 @@ group_mlp_maxpool_kernel(const Params p) {
           const int gi = (int)(ql % p.G);
           const long long t = ql / p.G;
           const int seed = (int)(t % p.m), bi = (int)(t / p.m);
-          p.out[(((long long)bi * p.C3 + c) * p.m + seed) * p.G + gi] = relu_keep_nan(__fadd_rn(u, bias));
+          const float y = relu_keep_nan(__fadd_rn(u, bias));
+          p.out[(((long long)bi * C3 + c) * p.m + seed) * p.G + gi] = y;
+          if (p.out_t) p.out_t[ql * C3 + c] = y;
         }
       }
     }
@@ -268,9 +314,9 @@ group_mlp_maxpool_kernel(const Params p) {
     if (lane == 0) {
       uint32_t na = 0, nw = 0;
       for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
-        for (int layer = 0; layer < 2; ++layer) {
-          const int K = layer ? p.C2 : p.C1, N = layer ? p.C3 : p.C2;
-          const uint32_t d = tmem + (layer ? (uint32_t)p.C2 : 0u);
+        for (int layer = 0; layer < p.NG; ++layer) {
+          const int K = p.Kd[layer], N = p.Nd[layer];
+          const uint32_t d = tmem + col[layer];
           const uint32_t idesc = tc::idesc_tf32_m128(N);
           const uint32_t b_lbo = (uint32_t)N * 16u, b_part = (uint32_t)N * KS * 4u;
           for (int s = 0; s < K / KS; ++s) {
@@ -298,7 +344,7 @@ group_mlp_maxpool_kernel(const Params p) {
             tc::mma_commit(sm + Smem::bars + (2 * NA + NWS + ws) * 8);    // weight slot too
             ++na; ++nw;
           }
-          tc::mma_commit(layer ? acc_full1 : acc_full0);
+          tc::mma_commit(acc_full + 8 * layer);
         }
       }
     }
@@ -307,9 +353,9 @@ group_mlp_maxpool_kernel(const Params p) {
     if (lane == 0) {
       uint32_t nw = 0;
       for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
-        for (int layer = 0; layer < 2; ++layer) {
-          const int K = layer ? p.C2 : p.C1, N = layer ? p.C3 : p.C2;
-          const float *src = layer ? p.w3p : p.w2p;
+        for (int layer = 0; layer < p.NG; ++layer) {
+          const int K = p.Kd[layer], N = p.Nd[layer];
+          const float *src = p.wp[layer];
           const uint32_t slab_floats = (uint32_t)N * KS * 2u;
           const uint32_t bytes = (uint32_t)N * KS * 4u * (p.passes == 3 ? 2u : 1u);
           for (int s = 0; s < K / KS; ++s) {
@@ -346,10 +392,24 @@ __global__ void mlp_pack_kernel(const float *__restrict__ w, int cout, int cin, 
   packed[base + (size_t)cout * KS + ((size_t)kc * cout + n) * 4 + e] = lo;
 }
 
+int launch(Params &p, cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CUDA(cudaFuncSetAttribute(group_mlp_maxpool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem::total));
+    attr_set = true;
+  }
+  const int grid = p.tiles < b200_sm_count() ? p.tiles : b200_sm_count();
+  group_mlp_maxpool_kernel<<<grid, NTHREADS, Smem::total, stream>>>(p);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+bool width_ok(int c) { return c >= 16 && c <= MAXC && c % 16 == 0; }
+
 }  // namespace
 
 extern "C" int b200_mlp_pack_weights(const float *w, int cout, int cin, float *packed, void *stream) {
-  if (!w || !packed || cout < 16 || cin < KS || cout % 16 || cin % KS || cout > MAXC || cin > MAXC) return B200_EINVAL;
+  if (!w || !packed || !width_ok(cout) || cin < KS || cin % KS || cin > 2 * MAXC) return B200_EINVAL;
   const int n = cout * cin;
   mlp_pack_kernel<<<ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(w, cout, cin, packed);
   B200_LAUNCH_CHECK();
@@ -360,31 +420,52 @@ extern "C" int b200_group_mlp_maxpool(const float *xyz, const float *new_xyz, co
                                       int g, int b, int n, int m, int ns, float radius, const float *w1,
                                       const float *b1, const float *w2_packed, const float *b2,
                                       const float *w3_packed, const float *b3, int c1, int c2, int c3, int passes,
-                                      float *out, void *stream) {
+                                      float *out, float *out_t, void *stream) {
   if (g < 1 || b < 0 || n < 1 || m < 0 || ns < 1) return B200_EINVAL;
   if (passes != 1 && passes != 3) return B200_EINVAL;
   // shapes the tensor-core path covers: whole lists per tile, K in slabs of 16, N a multiple of 16 up to 256
   if (ns != 16 && ns != 32 && ns != 64 && ns != 128) return B200_ECAPACITY;
-  if (c1 % KS || c2 % KS || c3 % 16 || c1 < KS || c2 < KS || c3 < 16 || c1 > MAXC || c2 > MAXC || c3 > MAXC)
-    return B200_ECAPACITY;
-  if (c2 + c3 > 512) return B200_ECAPACITY;
+  if (!width_ok(c1) || !width_ok(c2) || !width_ok(c3) || c2 + c3 > 512) return B200_ECAPACITY;
   const long long lists = (long long)b * m * g;
   if (lists == 0) return 0;
   if (!xyz || !new_xyz || !idx || !w1 || !b1 || !w2_packed || !b2 || !w3_packed || !b3 || !out) return B200_EINVAL;
   const long long tiles = ceil_div_ll(lists * ns, TM);
   if (tiles > 0x7fffffffLL) return B200_ECAPACITY;
-  Params p;
+  Params p = {};
   p.xyz = xyz; p.new_xyz = new_xyz; p.rot = rot; p.idx = idx;
   p.G = g; p.B = b; p.N = n; p.m = m; p.ns = ns; p.radius = radius;
-  p.w1 = w1; p.b1 = b1; p.w2p = w2_packed; p.b2 = b2; p.w3p = w3_packed; p.b3 = b3;
-  p.C1 = c1; p.C2 = c2; p.C3 = c3; p.passes = passes; p.Q = lists; p.tiles = (int)tiles; p.out = out;
-  static bool attr_set = false;
-  if (!attr_set) {
-    B200_CUDA(cudaFuncSetAttribute(group_mlp_maxpool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem::total));
-    attr_set = true;
-  }
-  const int grid = (int)(tiles < b200_sm_count() ? tiles : b200_sm_count());
-  group_mlp_maxpool_kernel<<<grid, NTHREADS, Smem::total, (cudaStream_t)stream>>>(p);
-  B200_LAUNCH_CHECK();
-  return 0;
+  p.w1 = w1; p.b1 = b1; p.C0 = c1;
+  p.NG = 2;
+  p.wp[0] = w2_packed; p.bias[0] = b2; p.Kd[0] = c1; p.Nd[0] = c2;
+  p.wp[1] = w3_packed; p.bias[1] = b3; p.Kd[1] = c2; p.Nd[1] = c3;
+  p.passes = passes; p.Q = lists; p.tiles = (int)tiles; p.out = out; p.out_t = out_t;
+  return launch(p, (cudaStream_t)stream);
+}
+
+extern "C" int b200_group_feat_mlp_maxpool(const float *xyz, const float *new_xyz, const float *feat_t,
+                                           const int32_t *idx, int b, int n, int m, int ns, int c, float radius,
+                                           const float *w1_packed, const float *b1, const float *w2_packed,
+                                           const float *b2, const float *w3_packed, const float *b3, int c1, int c2,
+                                           int c3, int passes, float *out, float *out_t, void *stream) {
+  if (b < 0 || n < 1 || m < 0 || ns < 1 || c < 1) return B200_EINVAL;
+  if (passes != 1 && passes != 3) return B200_EINVAL;
+  if (ns != 16 && ns != 32 && ns != 64 && ns != 128) return B200_ECAPACITY;
+  if (c % KS || c > 2 * MAXC - KS) return B200_ECAPACITY;
+  if (!width_ok(c1) || !width_ok(c2) || !width_ok(c3) || c1 + c2 + c3 > 512) return B200_ECAPACITY;
+  const long long lists = (long long)b * m;
+  if (lists == 0) return 0;
+  if (!xyz || !new_xyz || !feat_t || !idx || !w1_packed || !b1 || !w2_packed || !b2 || !w3_packed || !b3 || !out)
+    return B200_EINVAL;
+  const long long tiles = ceil_div_ll(lists * ns, TM);
+  if (tiles > 0x7fffffffLL) return B200_ECAPACITY;
+  Params p = {};
+  p.xyz = xyz; p.new_xyz = new_xyz; p.rot = nullptr; p.idx = idx;
+  p.G = 1; p.B = b; p.N = n; p.m = m; p.ns = ns; p.radius = radius;
+  p.feat_t = feat_t; p.C = c;
+  p.NG = 3;
+  p.wp[0] = w1_packed; p.bias[0] = b1; p.Kd[0] = c + KS; p.Nd[0] = c1;
+  p.wp[1] = w2_packed; p.bias[1] = b2; p.Kd[1] = c1; p.Nd[1] = c2;
+  p.wp[2] = w3_packed; p.bias[2] = b3; p.Kd[2] = c2; p.Nd[2] = c3;
+  p.passes = passes; p.Q = lists; p.tiles = (int)tiles; p.out = out; p.out_t = out_t;
+  return launch(p, (cudaStream_t)stream);
 }

@@ -59,7 +59,8 @@ class SharedMLP(nn.Sequential):
 
 
 class _FusedMLP:
-    """Packed weights of a 3-layer SharedMLP for ops.group_mlp_maxpool; rebuilt when the parameters change."""
+    """Packed weights of a 3-layer SharedMLP for ops.group_mlp_maxpool / group_feat_mlp_maxpool; rebuilt when the
+    parameters change."""
 
     def __init__(self, mlp):
         self.mlp, self.key, self.layers = mlp, None, None
@@ -69,16 +70,26 @@ class _FusedMLP:
         key = tuple((p.data_ptr(), p._version) for p in params)
         if key != self.key:
             (w1, b1), (w2, b2), (w3, b3) = self.mlp.folded()
-            self.layers = [(w1, b1), (ops.mlp_pack_weights(w2), b2, w2.shape[0]),
+            if w1.shape[1] == 3:                         # xyz only: layer 1 runs on the CUDA cores
+                first = (w1, b1)
+            else:                                        # [xyz | features] -> [features | xyz | zero pad to 16]
+                pad = torch.zeros(w1.shape[0], 13, dtype=w1.dtype, device=w1.device)
+                first = (ops.mlp_pack_weights(torch.cat([w1[:, 3:], w1[:, :3], pad], dim=1).contiguous()), b1,
+                         w1.shape[0])
+            self.layers = [first, (ops.mlp_pack_weights(w2), b2, w2.shape[0]),
                            (ops.mlp_pack_weights(w3), b3, w3.shape[0])]
             self.key = key
         return self.layers
 
 
 def fusable(mlp, nsample):
+    """shapes csrc/mlp_fused.cu covers: three layers of widths 16..256 (multiples of 16), whole lists per 128-row
+    tile; input = xyz only, or xyz + C features with C a multiple of 16 and all accumulators within TMEM"""
     dims = [mlp[0].conv.in_channels] + [l.conv.out_channels for l in mlp]
-    return (len(mlp) == 3 and dims[0] == 3 and nsample in (16, 32, 64, 128) and
-            all(d % 16 == 0 and 16 <= d <= 256 for d in dims[1:]))
+    ok = (len(mlp) == 3 and nsample in (16, 32, 64, 128) and all(d % 16 == 0 and 16 <= d <= 256 for d in dims[1:]))
+    if dims[0] == 3:
+        return ok
+    return ok and (dims[0] - 3) % 16 == 0 and 16 <= dims[0] - 3 <= 496 and sum(dims[1:]) <= 512
 
 
 class PointnetSAModuleVotes(nn.Module):
@@ -98,19 +109,31 @@ class PointnetSAModuleVotes(nn.Module):
             spec[0] += 3
         self.mlp_module = SharedMLP(spec, bn=bn)
         self._fused = _FusedMLP(self.mlp_module)
+        self.features_t = None
 
-    def forward(self, xyz, features=None, inds=None):
+    def forward(self, xyz, features=None, inds=None, features_t=None):
+        """features (B,C,N) as in the reference; `features_t` (B,N,C) may be passed as well (the channels-last copy
+        the previous fused module left in its .features_t) to skip the transpose.  After a fused forward
+        self.features_t holds new_features channels-last (B,npoint,C_out)."""
         if inds is None:
             inds = pointnet2_utils.furthest_point_sample(xyz, self.npoint)
         else:
             assert inds.shape[1] == self.npoint
         new_xyz = ops.gather_xyz(xyz, inds, transposed=False)
-        if (not self.training and features is None and self.use_xyz and not torch.is_grad_enabled()
+        self.features_t = None
+        if (not self.training and self.use_xyz and not torch.is_grad_enabled()
                 and fusable(self.mlp_module, self.nsample)):
             idx = pointnet2_utils.ball_query(self.radius, self.nsample, xyz, new_xyz)
-            new_features = ops.group_mlp_maxpool(xyz, new_xyz, idx, self._fused.get(),
-                                                 radius=self.radius if self.normalize_xyz else 0.0,
-                                                 passes=self.passes)
+            radius = self.radius if self.normalize_xyz else 0.0
+            if features is None:
+                new_features, self.features_t = ops.group_mlp_maxpool(
+                    xyz, new_xyz, idx, self._fused.get(), radius=radius, passes=self.passes, channels_last=True)
+            else:
+                if features_t is None:
+                    features_t = features.transpose(1, 2).contiguous()
+                new_features, self.features_t = ops.group_feat_mlp_maxpool(
+                    xyz, new_xyz, features_t, idx, self._fused.get(), radius=radius, passes=self.passes,
+                    channels_last=True)
             return new_xyz, new_features, inds
         grouped_features, _ = self.grouper(xyz, new_xyz, features)
         new_features = self.mlp_module(grouped_features)

@@ -120,10 +120,11 @@ def mlp_pack_weights(w):
     return packed
 
 
-def group_mlp_maxpool(xyz, new_xyz, idx, layers, radius=0.0, rot=None, passes=3):
+def group_mlp_maxpool(xyz, new_xyz, idx, layers, radius=0.0, rot=None, passes=3, channels_last=False):
     """Fused group -> (centre, /radius, rotate) -> 3 x (1x1 conv + folded BN + ReLU) -> max over nsample.
     xyz (B,N,3), new_xyz (B,M,3), idx (B,M,ns) or (G,B,M,ns) i32, rot (B,M,3,3)/(B,M,9) or None,
-    layers = [(w1 (C1,3), b1), (w2_packed, b2, C2), (w3_packed, b3, C3)] -> (B,C3,M) or (B,C3,M,G)."""
+    layers = [(w1 (C1,3), b1), (w2_packed, b2, C2), (w3_packed, b3, C3)] -> (B,C3,M) or (B,C3,M,G)
+    [, the same channels-last (B,M,C3) / (B,M,G,C3) when channels_last]."""
     _chk(xyz, "xyz", torch.float32)
     _chk(new_xyz, "new_xyz", torch.float32)
     _chk(idx, "idx", torch.int32)
@@ -138,12 +139,44 @@ def group_mlp_maxpool(xyz, new_xyz, idx, layers, radius=0.0, rot=None, passes=3)
     if rot is not None:
         _chk(rot, "rot", torch.float32)
     out = torch.empty((b, c3, m, g), dtype=torch.float32, device=xyz.device)
+    out_t = torch.empty((b, m, g, c3), dtype=torch.float32, device=xyz.device) if channels_last else None
     with torch.cuda.device(xyz.device):
         _abi.check(_lib.b200_group_mlp_maxpool(_ptr(xyz), _ptr(new_xyz), _ptr(rot) if rot is not None else None,
                                                _ptr(idx), g, b, n, m, ns, float(radius), _ptr(w1), _ptr(b1),
                                                _ptr(w2p), _ptr(b2), _ptr(w3p), _ptr(b3), c1, c2, c3, int(passes),
-                                               _ptr(out), _stream()), "group_mlp_maxpool")
-    return out.view(b, c3, m) if squeeze else out
+                                               _ptr(out), _ptr(out_t) if channels_last else None, _stream()),
+                   "group_mlp_maxpool")
+    if squeeze:
+        out = out.view(b, c3, m)
+        out_t = out_t.view(b, m, c3) if channels_last else None
+    return (out, out_t) if channels_last else out
+
+
+def group_feat_mlp_maxpool(xyz, new_xyz, feat_t, idx, layers, radius=0.0, passes=3, channels_last=False):
+    """The same with point features: feat_t (B,N,C) CHANNELS-LAST, idx (B,M,ns);
+    layers = [(w1_packed over [features | xyz | pad], b1, C1), (w2_packed, b2, C2), (w3_packed, b3, C3)]
+    -> (B,C3,M) [, (B,M,C3)]."""
+    _chk(xyz, "xyz", torch.float32)
+    _chk(new_xyz, "new_xyz", torch.float32)
+    _chk(feat_t, "feat_t", torch.float32)
+    _chk(idx, "idx", torch.int32)
+    b, n, _ = xyz.shape
+    m, ns = idx.shape[-2], idx.shape[-1]
+    c = feat_t.shape[2]
+    if feat_t.shape[:2] != (b, n):
+        raise RuntimeError("feat_t must be (B,N,C) channels-last")
+    (w1p, b1, c1), (w2p, b2, c2), (w3p, b3, c3) = layers
+    for t, name in ((w1p, "w1"), (b1, "b1"), (w2p, "w2"), (b2, "b2"), (w3p, "w3"), (b3, "b3")):
+        _chk(t, name, torch.float32)
+    out = torch.empty((b, c3, m), dtype=torch.float32, device=xyz.device)
+    out_t = torch.empty((b, m, c3), dtype=torch.float32, device=xyz.device) if channels_last else None
+    with torch.cuda.device(xyz.device):
+        _abi.check(_lib.b200_group_feat_mlp_maxpool(_ptr(xyz), _ptr(new_xyz), _ptr(feat_t), _ptr(idx), b, n, m, ns, c,
+                                                    float(radius), _ptr(w1p), _ptr(b1), _ptr(w2p), _ptr(b2),
+                                                    _ptr(w3p), _ptr(b3), c1, c2, c3, int(passes), _ptr(out),
+                                                    _ptr(out_t) if channels_last else None, _stream()),
+                   "group_feat_mlp_maxpool")
+    return (out, out_t) if channels_last else out
 
 
 def gather_points_grad(grad_out, idx, n):

@@ -86,14 +86,26 @@ int b200_gather_xyz(const float *xyz, const int32_t *idx, int b, int n, int m, f
  *   radius > 0: grouped_xyz /= radius (normalize_xyz); <= 0: left as is
  *   layer 1: w1[C1,3], b1[C1]; layers 2, 3: weights packed by b200_mlp_pack_weights, b2[C2], b3[C3]; BatchNorm is
  *   folded into (w, b) by the caller.  out[B,C3,M,G] (= [B,C3,M] for G = 1; CloudCrop's view(B,-1,num_seed,num_depth)).
+ *   out_t (or NULL): the same features channels-last, [B,M,G,C3] -- the layout b200_group_feat_mlp_maxpool reads.
  *   passes = 3: fp32-grade ("3xTF32" on the tensor cores), passes = 1: TF32 (cuDNN's default for the reference convs).
- * Supported: ns in {16,32,64,128}; C1, C2 multiples of 16, C3 a multiple of 16, all <= 256 (else B200_ECAPACITY). */
+ * Supported: ns in {16,32,64,128}; C1, C2, C3 multiples of 16, all <= 256 (else B200_ECAPACITY). */
 int b200_group_mlp_maxpool(const float *xyz, const float *new_xyz, const float *rot, const int32_t *idx, int g, int b,
                            int n, int m, int ns, float radius, const float *w1, const float *b1,
                            const float *w2_packed, const float *b2, const float *w3_packed, const float *b3, int c1,
-                           int c2, int c3, int passes, float *out, void *stream);
+                           int c2, int c3, int passes, float *out, float *out_t, void *stream);
+/* The same for modules whose grouped input is [xyz | point features] (SA2-SA4: QueryAndGroup with features,
+ * pointnet2_utils.py:352-358 torch.cat([grouped_xyz, grouped_features], dim=1)); all three layers on the tensor cores.
+ *   feat_t[B,N,C]: the features CHANNELS-LAST (a row's C values contiguous: one neighbour = C/4 16-byte loads;
+ *   the reference layout [B,C,N] is transposed by the caller, or taken from out_t of the previous module);
+ *   w1_packed: b200_mlp_pack_weights of the first conv's weight with its input columns reordered to
+ *   [features (C) | x y z | 13 zero columns] (cin = C + 16).  C a multiple of 16, C1 + C2 + C3 <= 512. */
+int b200_group_feat_mlp_maxpool(const float *xyz, const float *new_xyz, const float *feat_t, const int32_t *idx, int b,
+                                int n, int m, int ns, int c, float radius, const float *w1_packed, const float *b1,
+                                const float *w2_packed, const float *b2, const float *w3_packed, const float *b3,
+                                int c1, int c2, int c3, int passes, float *out, float *out_t, void *stream);
 /* w[cout,cin] fp32 (conv weight, BN folded) -> packed[2*cout*cin] in the order the kernel's bulk copies read:
- * K-slabs of 16 input channels, each [hi | lo][k-chunk of 4][cout][4], hi = tf32(w), lo = tf32(w - hi). */
+ * K-slabs of 16 input channels, each [hi | lo][k-chunk of 4][cout][4], hi = tf32(w), lo = tf32(w - hi).
+ * cout a multiple of 16 up to 256, cin a multiple of 16 up to 512. */
 int b200_mlp_pack_weights(const float *w, int cout, int cin, float *packed, void *stream);
 
 /* Replaces ball_query(new_xyz[B,M,3], xyz[B,N,3], radius, nsample) -> [B,M,nsample] i32

@@ -33,16 +33,21 @@ def grouped_xyz(xyz, new_xyz, idx, radius=0.0, rot=None):
     return g
 
 
-def group_mlp_maxpool(xyz, new_xyz, idx, layers, radius=0.0, rot=None):
-    """idx (B,M,ns) or (G,B,M,ns); layers = [(w (Cout,Cin), b (Cout)), ...] already folded
+def group_mlp_maxpool(xyz, new_xyz, idx, layers, radius=0.0, rot=None, features=None):
+    """idx (B,M,ns) or (G,B,M,ns); layers = [(w (Cout,Cin), b (Cout)), ...] already folded; features (B,C,N) or
+    None: the first layer then sees torch.cat([grouped_xyz, grouped_features], dim=1) (pointnet2_utils.py:352-358)
     -> (B,C,M) or (B,C,M,G) float64"""
     squeeze = idx.ndim == 3
     lists = idx[None] if squeeze else idx
+    b = xyz.shape[0]
     outs = []
     for g in range(lists.shape[0]):
         x = grouped_xyz(xyz, new_xyz, lists[g], radius, rot).astype(np.float64)   # (B,M,ns,3)
-        for w, b in layers:
-            x = np.maximum(x @ w.astype(np.float64).T + b.astype(np.float64), 0.0)
+        if features is not None:
+            gf = np.stack([features[i].T[lists[g][i]] for i in range(b)]).astype(np.float64)   # (B,M,ns,C)
+            x = np.concatenate([x, gf], axis=-1)
+        for w, bias in layers:
+            x = np.maximum(x @ w.astype(np.float64).T + bias.astype(np.float64), 0.0)
         outs.append(x.max(axis=2).transpose(0, 2, 1))                           # (B,C,M)
     out = np.stack(outs, axis=-1)
     return out[..., 0] if squeeze else out

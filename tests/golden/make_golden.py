@@ -211,7 +211,9 @@ def make_mlp():
     import synth
     cases = (("a", 5, [3, 64, 64, 128], 1, 600, 10, 64, 0.04, False, 1),      # SA1-like: /radius, no rotation
              ("b", 6, [3, 64, 128, 256], 2, 800, 6, 64, 0.05, True, 4),       # CloudCrop-like: 4 depth lists, rotated
-             ("c", 7, [3, 32, 48, 80], 1, 300, 9, 16, 0.3, True, 2))          # odd widths, 16-row lists
+             ("c", 7, [3, 32, 48, 80], 1, 300, 9, 16, 0.3, True, 2),          # odd widths, 16-row lists
+             ("d", 8, [3 + 32, 48, 64, 96], 2, 400, 11, 32, 0.1, False, 1),   # SA2-like: xyz + 32 point features
+             ("e", 9, [3 + 128, 128, 128, 256], 1, 256, 7, 16, 0.2, False, 1))  # SA3-like widths, 16-row lists
     for name, seed, dims, b, n, m, ns, radius, crop, g in cases:
         xyz = np.stack([synth.tabletop_cloud(n, seed + i) for i in range(b)])
         first = oracle.furthest_point_sampling(xyz, m)
@@ -225,6 +227,8 @@ def make_mlp():
             rot = None
             idx = oracle.ball_query(new_xyz, xyz, radius, ns)[None]
             norm_radius = radius
+        nfeat = dims[0] - 3
+        feat = np.random.default_rng(seed).standard_normal((b, nfeat, n)).astype(np.float32) if nfeat else None
         params = synth.mlp_params(seed, dims)
         mlp = pt_utils.SharedMLP(list(dims), bn=True)
         with torch.no_grad():
@@ -247,13 +251,18 @@ def make_mlp():
                 g_ = grouped.permute(0, 2, 3, 1).contiguous()
                 g_ = torch.matmul(g_, torch.from_numpy(rot).view(b, m, 3, 3))
                 grouped = g_.permute(0, 3, 1, 2).contiguous()
+            if feat is not None:                                                    # pointnet2_utils.py:352-358
+                tf = torch.from_numpy(feat)
+                gfeat = torch.stack([tf[i][:, ti[i]] for i in range(b)])            # (B,C,m,ns) = grouping_operation
+                grouped = torch.cat([grouped, gfeat], dim=1)
             feats.append(grouped)
-        x = torch.stack(feats, dim=3).view(b, 3, m * idx.shape[0], ns)                # modules.py:131-132
+        x = torch.stack(feats, dim=3).view(b, dims[0], m * idx.shape[0], ns)          # modules.py:131-132
         with torch.no_grad():
             y = F.max_pool2d(mlp(x), kernel_size=[1, ns]).view(b, -1, m, idx.shape[0])
         np.savez_compressed(os.path.join(HERE, f"mlp_{name}.npz"), xyz=xyz, new_xyz=new_xyz, idx=idx,
                             rot=np.zeros(0, np.float32) if rot is None else rot, radius=np.float32(norm_radius),
-                            seed=seed, dims=np.array(dims), out=y.numpy())
+                            seed=seed, dims=np.array(dims), out=y.numpy(),
+                            feat=np.zeros(0, np.float32) if feat is None else feat)
         print("mlp", name, dims, tuple(y.shape), float(y.abs().max()))
 
 

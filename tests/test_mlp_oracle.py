@@ -15,7 +15,8 @@ def load_case(path, b200_synth, oracle_mod):
     params = b200_synth.mlp_params(int(z["seed"]), [int(d) for d in z["dims"]])
     layers = [oracle_mod.mlp.fold_bn(*p) for p in params]
     rot = z["rot"] if z["rot"].size else None
-    return z, layers, rot
+    feat = z["feat"] if z["feat"].size else None
+    return z, layers, rot, feat
 
 
 @pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(HERE, "golden", "mlp_*.npz"))))
@@ -24,12 +25,12 @@ def test_oracle_matches_reference_shared_mlp(path, oracle_mod):
     spec = importlib.util.spec_from_file_location("b200_synth", os.path.join(os.path.dirname(HERE), "graspnet-baseline_b200", "synth.py"))
     synth = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(synth)
-    z, layers, rot = load_case(path, synth, oracle_mod)
-    got = oracle_mod.mlp.group_mlp_maxpool(z["xyz"], z["new_xyz"], z["idx"], layers, float(z["radius"]), rot)
+    z, layers, rot, feat = load_case(path, synth, oracle_mod)
+    got = oracle_mod.mlp.group_mlp_maxpool(z["xyz"], z["new_xyz"], z["idx"], layers, float(z["radius"]), rot, feat)
     want = z["out"]
     assert got.shape == want.shape
     assert np.allclose(got, want, rtol=RTOL, atol=RTOL * np.abs(want).max())
 
 
 def test_golden_files_present():
-    assert len(glob.glob(os.path.join(HERE, "golden", "mlp_*.npz"))) == 3
+    assert len(glob.glob(os.path.join(HERE, "golden", "mlp_*.npz"))) == 5
