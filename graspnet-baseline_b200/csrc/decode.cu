@@ -119,6 +119,55 @@ pred_decode_kernel(const float *__restrict__ objectness, const float *__restrict
   }
 }
 
+// ApproachNet's tail (reference models/modules.py:60-73): per seed the best of the V template views (torch.max over
+// the view scores = first maximum), its unit direction and the approach frame built from it with in-plane angle 0.
+// The V directions (generate_grasp_views, utils/loss_utils.py:41-66) and their frames
+// (batch_viewpoint_params_to_matrix(-view, 0), :68-96) depend on V only: the caller computes both tables once and
+// this kernel looks them up -- the reference rebuilds the lattice in a Python loop and expands it to (B,S,V,3)
+// on every forward.  features is conv3's output [b, 2+V, s]; thread = seed, so every view row is read coalesced.
+__global__ void __launch_bounds__(256)
+view_select_kernel(const float *__restrict__ features, const float *__restrict__ views,
+                   const float *__restrict__ frames, int s, int v, long long *__restrict__ top_inds,
+                   float *__restrict__ top_score, float *__restrict__ vp_xyz, float *__restrict__ vp_rot) {
+  const int scene = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= s) return;
+  const float *f = features + ((size_t)scene * (2 + v) + 2) * s + i;
+  int best = 0;
+  float bv = __ldg(f);
+  bool nan = bv != bv;
+  for (int k = 1; k < v && !nan; ++k) {
+    const float x = __ldg(f + (size_t)k * s);
+    if (x > bv || x != x) { bv = x; best = k; nan = x != x; }      // torch.max propagates the first NaN
+  }
+  const size_t o = (size_t)scene * s + i;
+  top_inds[o] = best;
+  top_score[o] = bv;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) vp_xyz[o * 3 + c] = __ldg(views + best * 3 + c);
+#pragma unroll
+  for (int c = 0; c < 9; ++c) vp_rot[o * 9 + c] = __ldg(frames + best * 9 + c);
+}
+
+// PointnetFPModule's interpolation weights (reference pointnet2/pointnet2_modules.py:394-397, after the sqrt of
+// pointnet2_utils.py:140): dist = sqrt(dist2); r = 1 / (dist + 1e-8); weight = r / (r0 + r1 + r2).
+__global__ void __launch_bounds__(256)
+three_nn_weights_kernel(const float *__restrict__ dist2, int n, float *__restrict__ dist, float *__restrict__ weight) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float d[3], r[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    d[k] = __fsqrt_rn(__ldg(dist2 + 3 * (size_t)i + k));
+    r[k] = __fdiv_rn(1.0f, __fadd_rn(d[k], 1e-8f));
+  }
+  const float norm = __fadd_rn(__fadd_rn(r[0], r[1]), r[2]);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    if (dist) dist[3 * (size_t)i + k] = d[k];
+    weight[3 * (size_t)i + k] = __fdiv_rn(r[k], norm);
+  }
+}
+
 }  // namespace
 
 extern "C" int b200_pred_decode(const float *objectness, const float *score, const float *angle_cls,
@@ -133,6 +182,27 @@ extern "C" int b200_pred_decode(const float *objectness, const float *score, con
     return B200_EINVAL;
   pred_decode_kernel<<<b, DT, 0, (cudaStream_t)stream>>>(objectness, score, angle_cls, width, tolerance, xyz, view_xyz,
                                                         ns, num_angle, num_depth, rows, nrows);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200_view_select(const float *features, const float *views, const float *frames, int b, int s, int v,
+                                long long *top_inds, float *top_score, float *vp_xyz, float *vp_rot, void *stream) {
+  if (b < 0 || s < 0 || v < 1) return B200_EINVAL;
+  if (b == 0 || s == 0) return 0;
+  if (!features || !views || !frames || !top_inds || !top_score || !vp_xyz || !vp_rot) return B200_EINVAL;
+  if (b > 65535) return B200_ECAPACITY;
+  view_select_kernel<<<dim3((s + 255) / 256, b), 256, 0, (cudaStream_t)stream>>>(features, views, frames, s, v,
+                                                                                 top_inds, top_score, vp_xyz, vp_rot);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200_three_nn_weights(const float *dist2, int n, float *dist, float *weight, void *stream) {
+  if (n < 0) return B200_EINVAL;
+  if (n == 0) return 0;
+  if (!dist2 || !weight) return B200_EINVAL;
+  three_nn_weights_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(dist2, n, dist, weight);
   B200_LAUNCH_CHECK();
   return 0;
 }

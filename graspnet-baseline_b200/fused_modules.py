@@ -15,6 +15,9 @@ import torch.nn.functional as F
 
 from . import ops, pointnet2_utils
 
+# False = always run the composed path (the reference's own op sequence: group ops + torch layers), also in eval mode
+FUSED = True
+
 
 class _BN(nn.Sequential):
     def __init__(self, channels):
@@ -119,26 +122,34 @@ class PointnetSAModuleVotes(nn.Module):
             inds = pointnet2_utils.furthest_point_sample(xyz, self.npoint)
         else:
             assert inds.shape[1] == self.npoint
-        new_xyz = ops.gather_xyz(xyz, inds, transposed=False)
         self.features_t = None
-        if (not self.training and self.use_xyz and not torch.is_grad_enabled()
-                and fusable(self.mlp_module, self.nsample)):
-            idx = pointnet2_utils.ball_query(self.radius, self.nsample, xyz, new_xyz)
-            radius = self.radius if self.normalize_xyz else 0.0
-            if features is None:
-                new_features, self.features_t = ops.group_mlp_maxpool(
-                    xyz, new_xyz, idx, self._fused.get(), radius=radius, passes=self.passes, channels_last=True)
-            else:
-                if features_t is None:
-                    features_t = features.transpose(1, 2).contiguous()
-                new_features, self.features_t = ops.group_feat_mlp_maxpool(
-                    xyz, new_xyz, features_t, idx, self._fused.get(), radius=radius, passes=self.passes,
-                    channels_last=True)
+        if not self.fused():                             # the reference's own sequence (pointnet2_modules.py:232-272)
+            xyz_flipped = xyz.transpose(1, 2).contiguous()
+            new_xyz = pointnet2_utils.gather_operation(xyz_flipped, inds).transpose(1, 2).contiguous()
+            grouped_features, _ = self.grouper(xyz, new_xyz, features)
+            new_features = self.mlp_module(grouped_features)
+            new_features = F.max_pool2d(new_features, kernel_size=[1, new_features.size(3)]).squeeze(-1)
             return new_xyz, new_features, inds
-        grouped_features, _ = self.grouper(xyz, new_xyz, features)
-        new_features = self.mlp_module(grouped_features)
-        new_features = F.max_pool2d(new_features, kernel_size=[1, new_features.size(3)]).squeeze(-1)
+        new_xyz = ops.gather_xyz(xyz, inds, transposed=False)
+        idx = pointnet2_utils.ball_query(self.radius, self.nsample, xyz, new_xyz)
+        new_features, self.features_t = self.pooled(xyz, new_xyz, idx, features, features_t)
         return new_xyz, new_features, inds
+
+    def fused(self):
+        return (FUSED and not self.training and self.use_xyz and not torch.is_grad_enabled()
+                and fusable(self.mlp_module, self.nsample))
+
+    def pooled(self, xyz, new_xyz, idx, features=None, features_t=None):
+        """the fused kernel on given neighbour lists idx (B,npoint,nsample): -> (new_features (B,C,npoint),
+        the same channels-last (B,npoint,C))"""
+        radius = self.radius if self.normalize_xyz else 0.0
+        if features is None and features_t is None:
+            return ops.group_mlp_maxpool(xyz, new_xyz, idx, self._fused.get(), radius=radius, passes=self.passes,
+                                         channels_last=True)
+        if features_t is None:
+            features_t = features.transpose(1, 2).contiguous()
+        return ops.group_feat_mlp_maxpool(xyz, new_xyz, features_t, idx, self._fused.get(), radius=radius,
+                                          passes=self.passes, channels_last=True)
 
 
 class CloudCrop(nn.Module):
@@ -155,13 +166,16 @@ class CloudCrop(nn.Module):
         self.mlps = SharedMLP([self.in_dim, 64, 128, 256], bn=True)
         self._fused = _FusedMLP(self.mlps)
 
-    def forward(self, seed_xyz, pointcloud, vp_rot):
+    def fused(self):
+        return FUSED and not self.training and not torch.is_grad_enabled() and fusable(self.mlps, self.nsample)
+
+    def forward(self, seed_xyz, pointcloud, vp_rot, grid=None):
         B, num_seed, _, _ = vp_rot.size()
         num_depth = len(self.groupers)
-        if not self.training and not torch.is_grad_enabled() and fusable(self.mlps, self.nsample):
+        if self.fused():
             rot = vp_rot.reshape(B, num_seed, 9).contiguous()
             idx = ops.cylinder_query_multi(seed_xyz, pointcloud, rot, self.cylinder_radius, self.hmin,
-                                           self.hmax_list, self.nsample)
+                                           self.hmax_list, self.nsample, grid=grid)
             return ops.group_mlp_maxpool(pointcloud, seed_xyz, idx, self._fused.get(), rot=rot, passes=self.passes)
         grouped = [g(pointcloud, seed_xyz, vp_rot) for g in self.groupers]
         grouped = torch.stack(grouped, dim=3).view(B, -1, num_seed * num_depth, self.nsample)

@@ -1,0 +1,516 @@
+"""GraspNet inference on the B200 geometry path: the whole forward of the reference network as one CUDA graph
+(whole-forward graph + view-table cache + on-device pred_decode -> collision -> NMS).
+
+Module classes, constructor arguments, forward signatures, end_points keys and state_dict keys follow the reference
+  Pointnet2Backbone   models/backbone.py:20-135        (sa1..sa4, fp1, fp2)
+  PointnetFPModule    pointnet2/pointnet2_modules.py:356-416   (mlp.*)
+  ApproachNet         models/modules.py:22-77           (conv1..3, bn1, bn2)
+  OperationNet        models/modules.py:145-190         (conv1..3, bn1, bn2)
+  ToleranceNet        models/modules.py:193-230         (conv1..3, bn1, bn2)
+  GraspNetStage1/2, GraspNet   models/graspnet.py:26-75 (view_estimator.{backbone,vpmodule},
+                                                         grasp_generator.{crop,operation,tolerance})
+so a reference checkpoint loads with load_state_dict unchanged.  The geometry (FPS, queries, grouping, three_nn,
+interpolation, view selection, decode, collision, NMS) and the grouped shared MLPs are this library's kernels; the
+plain 1x1 convolutions over point columns (FP modules, ApproachNet, heads) are fp32 library GEMMs (cuBLAS through
+torch.addmm) with eval-mode BatchNorm folded into the weights.
+
+In eval mode without autograd every module takes its fast path; with `fused_modules.FUSED = False` (or in training
+mode) it runs the reference's own op sequence on the drop-in ops -- the "composed" path the fast one is tested
+against.  Label generation and the loss (training) stay with the reference's model code (out of scope).
+
+`GraspNetEngine` runs   cloud -> GraspNet -> pred_decode -> voxel down-sample -> collision mask -> NMS   for a batch
+of scenes as ONE graph launch forked over streams by data dependence, with one input and one output buffer.
+"""
+import math
+
+import numpy as np
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import fused_modules as fm
+from . import ops, pointnet2_utils, synth
+from .fused_modules import CloudCrop, PointnetSAModuleVotes, SharedMLP
+
+GRASP_MAX_WIDTH = 0.1            # utils/loss_utils.py:15-16
+GRASP_MAX_TOLERANCE = 0.05
+GRID_CELL = 0.026                # see pipeline.py
+POST = dict(voxel_size=0.01, approach_dist=0.05, collision_thresh=0.01,          # test.py:30-31,95; GraspGroup.nms()
+            translation_thresh=0.03, rotation_thresh=30.0 / 180.0 * math.pi)
+
+
+def _fast(module):
+    return fm.FUSED and not module.training and not torch.is_grad_enabled()
+
+
+def _pointwise(x, w, b, relu=True):
+    """1x1 convolution over point columns: x (B,C,n) -> [relu](w x + b) (B,Cout,n); fp32 GEMM, bias in the epilogue"""
+    if x.shape[0] == 1:
+        y = torch.addmm(b[:, None], w, x[0]).unsqueeze(0)
+    else:
+        y = torch.baddbmm(b[None, :, None], w.unsqueeze(0).expand(x.shape[0], -1, -1), x)
+    return y.relu_() if relu else y
+
+
+class _Folded:
+    """[(w (Cout,Cin), b (Cout))] of a conv(+BatchNorm) stack with the eval-mode statistics folded in; rebuilt when a
+    parameter or buffer changes"""
+
+    def __init__(self, owner, build):
+        self.owner, self.build, self.key, self.layers = owner, build, None, None
+
+    def get(self):
+        tensors = list(self.owner.parameters()) + list(self.owner.buffers())
+        key = tuple((t.data_ptr(), t._version) for t in tensors)
+        if key != self.key:
+            with torch.no_grad():
+                self.layers = [(w.contiguous(), b.contiguous()) for w, b in self.build()]
+            self.key = key
+        return self.layers
+
+
+def _fold1d(conv, bn=None):
+    w = conv.weight.detach()[:, :, 0].float()
+    b = conv.bias.detach().float() if conv.bias is not None else torch.zeros_like(w[:, 0])
+    if bn is not None:
+        scale = bn.weight.detach() / torch.sqrt(bn.running_var + bn.eps)
+        w = w * scale[:, None]
+        b = (b - bn.running_mean) * scale + bn.bias.detach()
+    return w, b
+
+
+def view_frames(towards, angle):
+    """Approach direction (K,3) + in-plane angle (K,) -> (K,3,3) frames [x = towards, y in the horizontal plane,
+    z = x cross y], then rotated about x by `angle` (the construction of utils/loss_utils.py:68-96)."""
+    zero = torch.zeros_like(angle)
+    y = torch.stack([-towards[:, 1], towards[:, 0], zero], dim=-1)
+    degenerate = torch.norm(y, dim=-1) == 0
+    y[degenerate, 1] = 1
+    x = towards / torch.norm(towards, dim=-1, keepdim=True)
+    y = y / torch.norm(y, dim=-1, keepdim=True)
+    z = torch.cross(x, y, dim=-1)
+    frame = torch.stack([x, y, z], dim=-1)
+    s, c, one = torch.sin(angle), torch.cos(angle), torch.ones_like(angle)
+    about_x = torch.stack([one, zero, zero, zero, c, -s, zero, s, c], dim=-1).reshape(-1, 3, 3)
+    return torch.matmul(frame, about_x)
+
+
+class PointnetFPModule(nn.Module):
+    """Feature propagation: inverse-distance interpolation of the three nearest known points, concatenation with the
+    skip features, shared MLP (pointnet2/pointnet2_modules.py:356-416)."""
+
+    def __init__(self, *, mlp, bn=True):
+        super().__init__()
+        self.mlp = SharedMLP(list(mlp), bn=bn)
+        self._folded = _Folded(self.mlp, self.mlp.folded)
+
+    def forward(self, unknown, known, unknow_feats, known_feats, neighbours=None):
+        """unknown (B,n,3), known (B,m,3), unknow_feats (B,C1,n), known_feats (B,C2,m) -> (B,mlp[-1],n).
+        `neighbours` = (idx (B,n,3) i32, weight (B,n,3)) if the caller already ran the search (engine streams)."""
+        if known is None:
+            interpolated = known_feats.expand(*known_feats.size()[0:2], unknown.size(1))
+        elif _fast(self):
+            if neighbours is None:
+                dist2, idx = ops.three_nn(unknown, known)
+                neighbours = (idx, ops.three_nn_weights(dist2))
+            interpolated = ops.three_interpolate(known_feats, *neighbours)
+        else:
+            dist, idx = pointnet2_utils.three_nn(unknown, known)
+            dist_recip = 1.0 / (dist + 1e-8)
+            weight = dist_recip / torch.sum(dist_recip, dim=2, keepdim=True)
+            interpolated = pointnet2_utils.three_interpolate(known_feats, idx, weight)
+        x = torch.cat([interpolated, unknow_feats], dim=1) if unknow_feats is not None else interpolated
+        if _fast(self):
+            for w, b in self._folded.get():
+                x = _pointwise(x, w, b)
+            return x
+        return self.mlp(x.unsqueeze(-1)).squeeze(-1)
+
+
+class Pointnet2Backbone(nn.Module):
+    """Four set-abstraction levels + two feature-propagation levels (models/backbone.py:20-135)."""
+
+    def __init__(self, input_feature_dim=0, passes=3):
+        super().__init__()
+        sa = dict(use_xyz=True, normalize_xyz=True, passes=passes)
+        self.sa1 = PointnetSAModuleVotes(npoint=2048, radius=0.04, nsample=64, mlp=[input_feature_dim, 64, 64, 128], **sa)
+        self.sa2 = PointnetSAModuleVotes(npoint=1024, radius=0.1, nsample=32, mlp=[128, 128, 128, 256], **sa)
+        self.sa3 = PointnetSAModuleVotes(npoint=512, radius=0.2, nsample=16, mlp=[256, 128, 128, 256], **sa)
+        self.sa4 = PointnetSAModuleVotes(npoint=256, radius=0.3, nsample=16, mlp=[256, 128, 128, 256], **sa)
+        self.fp1 = PointnetFPModule(mlp=[256 + 256, 256, 256])
+        self.fp2 = PointnetFPModule(mlp=[256 + 256, 256, 256])
+
+    @staticmethod
+    def _break_up_pc(pc):
+        xyz = pc[..., 0:3].contiguous()
+        features = pc[..., 3:].transpose(1, 2).contiguous() if pc.size(-1) > 3 else None
+        return xyz, features
+
+    def forward(self, pointcloud, end_points=None):
+        """pointcloud (B,N,3+C) -> (fp2_features (B,256,1024), fp2_xyz (B,1024,3), end_points)"""
+        if not end_points:
+            end_points = {}
+        xyz, features = self._break_up_pc(pointcloud)
+        end_points['input_xyz'] = xyz
+        end_points['input_features'] = features
+        feats_t = None
+        for name, sa in (("sa1", self.sa1), ("sa2", self.sa2), ("sa3", self.sa3), ("sa4", self.sa4)):
+            xyz, features, inds = sa(xyz, features, features_t=feats_t)
+            feats_t = sa.features_t
+            if name in ("sa1", "sa2"):
+                end_points[name + '_inds'] = inds
+            end_points[name + '_xyz'] = xyz
+            end_points[name + '_features'] = features
+        features = self.fp1(end_points['sa3_xyz'], end_points['sa4_xyz'], end_points['sa3_features'],
+                            end_points['sa4_features'])
+        features = self.fp2(end_points['sa2_xyz'], end_points['sa3_xyz'], end_points['sa2_features'], features)
+        end_points['fp2_features'] = features
+        end_points['fp2_xyz'] = end_points['sa2_xyz']
+        num_seed = end_points['fp2_xyz'].shape[1]
+        end_points['fp2_inds'] = end_points['sa1_inds'][:, 0:num_seed]
+        return features, end_points['fp2_xyz'], end_points
+
+
+class ApproachNet(nn.Module):
+    """Objectness + approach-view scores per seed, best view and its frame (models/modules.py:22-77)."""
+
+    def __init__(self, num_view, seed_feature_dim):
+        super().__init__()
+        self.num_view, self.in_dim = num_view, seed_feature_dim
+        self.conv1 = nn.Conv1d(self.in_dim, self.in_dim, 1)
+        self.conv2 = nn.Conv1d(self.in_dim, 2 + self.num_view, 1)
+        self.conv3 = nn.Conv1d(2 + self.num_view, 2 + self.num_view, 1)
+        self.bn1 = nn.BatchNorm1d(self.in_dim)
+        self.bn2 = nn.BatchNorm1d(2 + self.num_view)
+        self._folded = _Folded(self, lambda: [_fold1d(self.conv1, self.bn1), _fold1d(self.conv2, self.bn2),
+                                              _fold1d(self.conv3)])
+        self._tables = {}
+
+    def tables(self, device):
+        """(views (V,3), frames (V,3,3)) on `device`: the Fibonacci-lattice template views (generate_grasp_views,
+        utils/loss_utils.py:41-66) and the approach frame of each (-view, angle 0); they depend on V only, so they are
+        built once instead of on every forward (models/modules.py:66-71)."""
+        key = str(device)
+        if key not in self._tables:
+            views = torch.from_numpy(synth.fibonacci_views(self.num_view).astype(np.float32)).to(device)
+            frames = view_frames(-views, torch.zeros(self.num_view, dtype=views.dtype, device=device))
+            self._tables[key] = (views.contiguous(), frames.contiguous())
+        return self._tables[key]
+
+    def forward(self, seed_xyz, seed_features, end_points):
+        B, num_seed, _ = seed_xyz.size()
+        views, frames = self.tables(seed_features.device)
+        if _fast(self):
+            (w1, b1), (w2, b2), (w3, b3) = self._folded.get()
+            features = _pointwise(_pointwise(_pointwise(seed_features, w1, b1), w2, b2), w3, b3, relu=False)
+            top_view_inds, top_view_scores, vp_xyz, vp_rot = ops.view_select(features, views, frames)
+            view_score = features[:, 2:2 + self.num_view, :].transpose(1, 2)       # a view; the loss wants it contiguous
+        else:
+            features = F.relu(self.bn1(self.conv1(seed_features)), inplace=True)
+            features = F.relu(self.bn2(self.conv2(features)), inplace=True)
+            features = self.conv3(features)
+            view_score = features[:, 2:2 + self.num_view, :].transpose(1, 2).contiguous()
+            top_view_scores, top_view_inds = torch.max(view_score, dim=2)
+            vp_xyz = views[top_view_inds]
+            angle = torch.zeros(B * num_seed, dtype=vp_xyz.dtype, device=vp_xyz.device)
+            vp_rot = view_frames(-vp_xyz.view(-1, 3), angle).view(B, num_seed, 3, 3)
+        end_points['objectness_score'] = features[:, :2, :]
+        end_points['view_score'] = view_score
+        end_points['grasp_top_view_inds'] = top_view_inds
+        end_points['grasp_top_view_score'] = top_view_scores
+        end_points['grasp_top_view_xyz'] = vp_xyz
+        end_points['grasp_top_view_rot'] = vp_rot
+        return end_points
+
+
+class _Head(nn.Module):
+    """256 -> 128 -> 128 -> out per (seed, depth) column"""
+
+    def __init__(self, out_channels):
+        super().__init__()
+        self.conv1 = nn.Conv1d(256, 128, 1)
+        self.conv2 = nn.Conv1d(128, 128, 1)
+        self.conv3 = nn.Conv1d(128, out_channels, 1)
+        self.bn1 = nn.BatchNorm1d(128)
+        self.bn2 = nn.BatchNorm1d(128)
+        self._folded = _Folded(self, lambda: [_fold1d(self.conv1, self.bn1), _fold1d(self.conv2, self.bn2),
+                                              _fold1d(self.conv3)])
+
+    def scores(self, vp_features):
+        B, _, num_seed, num_depth = vp_features.size()
+        x = vp_features.view(B, -1, num_seed * num_depth)
+        if _fast(self):
+            (w1, b1), (w2, b2), (w3, b3) = self._folded.get()
+            x = _pointwise(_pointwise(_pointwise(x, w1, b1), w2, b2), w3, b3, relu=False)
+        else:
+            x = F.relu(self.bn1(self.conv1(x)), inplace=True)
+            x = F.relu(self.bn2(self.conv2(x)), inplace=True)
+            x = self.conv3(x)
+        return x.view(B, -1, num_seed, num_depth)
+
+
+class OperationNet(_Head):
+    """Grasp score / in-plane angle class / width per angle class and depth (models/modules.py:145-190)."""
+
+    def __init__(self, num_angle, num_depth):
+        super().__init__(3 * num_angle)
+        self.num_angle, self.num_depth = num_angle, num_depth
+
+    def forward(self, vp_features, end_points):
+        x = self.scores(vp_features)
+        end_points['grasp_score_pred'] = x[:, 0:self.num_angle]
+        end_points['grasp_angle_cls_pred'] = x[:, self.num_angle:2 * self.num_angle]
+        end_points['grasp_width_pred'] = x[:, 2 * self.num_angle:3 * self.num_angle]
+        return end_points
+
+
+class ToleranceNet(_Head):
+    """Grasp tolerance per angle class and depth (models/modules.py:193-230)."""
+
+    def __init__(self, num_angle, num_depth):
+        super().__init__(num_angle)
+
+    def forward(self, vp_features, end_points):
+        end_points['grasp_tolerance_pred'] = self.scores(vp_features)
+        return end_points
+
+
+class GraspNetStage1(nn.Module):
+    def __init__(self, input_feature_dim=0, num_view=300, passes=3):
+        super().__init__()
+        self.backbone = Pointnet2Backbone(input_feature_dim, passes=passes)
+        self.vpmodule = ApproachNet(num_view, 256)
+
+    def forward(self, end_points):
+        seed_features, seed_xyz, end_points = self.backbone(end_points['point_clouds'], end_points)
+        return self.vpmodule(seed_xyz, seed_features, end_points)
+
+
+class GraspNetStage2(nn.Module):
+    def __init__(self, num_angle=12, num_depth=4, cylinder_radius=0.05, hmin=-0.02, hmax_list=(0.01, 0.02, 0.03, 0.04),
+                 is_training=True, passes=3):
+        super().__init__()
+        self.num_angle, self.num_depth, self.is_training = num_angle, num_depth, is_training
+        self.crop = CloudCrop(64, 3, cylinder_radius, hmin, hmax_list, passes=passes)
+        self.operation = OperationNet(num_angle, num_depth)
+        self.tolerance = ToleranceNet(num_angle, num_depth)
+
+    def forward(self, end_points, grid=None):
+        if self.is_training:
+            raise NotImplementedError("b200grasp: label matching for training (utils/label_generation.py) stays with "
+                                      "the reference's model code; build the network with is_training=False")
+        vp_features = self.crop(end_points['fp2_xyz'], end_points['input_xyz'], end_points['grasp_top_view_rot'],
+                                grid=grid)
+        end_points = self.operation(vp_features, end_points)
+        return self.tolerance(vp_features, end_points)
+
+
+class GraspNet(nn.Module):
+    """forward(end_points with 'point_clouds' (B,N,3[+C]) f32 cuda) -> end_points, as models/graspnet.py:63-75.
+    `passes`: 3 = 3xTF32 in the fused grouped MLPs (fp32-grade, 1e-5 parity with the reference's fp32 layers), 1 = plain
+    TF32 (what the reference's convolutions use when torch.backends.cudnn.allow_tf32 is left at its default)."""
+
+    def __init__(self, input_feature_dim=0, num_view=300, num_angle=12, num_depth=4, cylinder_radius=0.05, hmin=-0.02,
+                 hmax_list=(0.01, 0.02, 0.03, 0.04), is_training=True, passes=3):
+        super().__init__()
+        self.is_training = is_training
+        self.view_estimator = GraspNetStage1(input_feature_dim, num_view, passes=passes)
+        self.grasp_generator = GraspNetStage2(num_angle, num_depth, cylinder_radius, hmin, hmax_list, is_training,
+                                              passes=passes)
+
+    def forward(self, end_points):
+        end_points = self.view_estimator(end_points)
+        return self.grasp_generator(end_points)
+
+
+def pred_decode(end_points):
+    from .decode import pred_decode as _pd
+    return _pd(end_points)
+
+
+class GraspNetEngine:
+    """cloud -> grasps, for `batch` scenes of `num_point` points, as one CUDA graph.
+
+    io_in  = cloud (B,N,3) f32
+    io_out = per scene: decoded row count i32 | collision mask (S) u8 | kept rows (S,17) f32 | kept count i32
+    (segments 256-byte aligned).  `infer(host_cloud)` = one H2D copy, one graph launch, one D2H copy.
+
+    Streams inside the graph: the SA1 sampling chain runs on the main stream while the grid binning and the voxel
+    down-sample of the cloud run beside it; once SA1's samples exist, the samples / neighbour lists / three-nearest
+    searches of SA2..SA4 and FP1..FP2 (coordinates only) run on a side stream under SA1's grouped MLP."""
+
+    def __init__(self, net, batch=1, num_point=20000, device="cuda", post=None):
+        self.net, self.B, self.N = net.eval(), batch, num_point
+        self.dev = torch.device(device)
+        self.post = dict(POST, **(post or {}))
+        bb = net.view_estimator.backbone
+        self.S = bb.sa2.npoint
+        B, S = batch, self.S
+        self._in_layout = [("cloud", np.float32, (B, num_point, 3))]
+        self._out_layout = []
+        for s in range(B):
+            self._out_layout += [("nrows%d" % s, np.int32, (1,)), ("mask%d" % s, np.uint8, (S,)),
+                                 ("kept%d" % s, np.float32, (S, 17)), ("nkept%d" % s, np.int32, (1,))]
+        self.io_in = torch.zeros(self._bytes(self._in_layout), dtype=torch.uint8, device=self.dev)
+        self.io_out = torch.zeros(self._bytes(self._out_layout), dtype=torch.uint8, device=self.dev)
+        self.cloud = self.views(self.io_in, "in")["cloud"]
+        self._out = self.views(self.io_out, "out")
+        self.host_in = torch.zeros(self.io_in.numel(), dtype=torch.uint8).pin_memory()
+        self.host_out = torch.zeros(self.io_out.numel(), dtype=torch.uint8).pin_memory()
+        self._graph = None
+        self._streams = None
+        self.launches = 0
+        self.end_points = None
+
+    @staticmethod
+    def _bytes(layout):
+        return sum((int(np.prod(shape)) * np.dtype(dt).itemsize + 255) // 256 * 256 for _, dt, shape in layout)
+
+    def views(self, buf, which):
+        """name -> typed view of a uint8 buffer (device or host) in the io_in / io_out layout"""
+        layout = self._in_layout if which == "in" else self._out_layout
+        tdt = {np.float32: torch.float32, np.int32: torch.int32, np.uint8: torch.uint8}
+        out, off = {}, 0
+        for name, dt, shape in layout:
+            nb = int(np.prod(shape)) * np.dtype(dt).itemsize
+            out[name] = buf[off: off + nb].view(tdt[dt]).view(shape)
+            off += (nb + 255) // 256 * 256
+        return out
+
+    # ---- the forward, forked over streams
+    def forward_streams(self):
+        net, B, dev = self.net, self.B, self.dev
+        bb, vp = net.view_estimator.backbone, net.view_estimator.vpmodule
+        gen = net.grasp_generator
+        sas = [bb.sa1, bb.sa2, bb.sa3, bb.sa4]
+        if not all(sa.fused() for sa in sas) or not gen.crop.fused():
+            raise RuntimeError("b200grasp: GraspNetEngine needs the fused eval path (net.eval(), torch.no_grad(), "
+                               "fused_modules.FUSED)")
+        main = torch.cuda.current_stream()
+        if self._streams is None:
+            self._streams = [torch.cuda.Stream(device=dev) for _ in range(6 + min(B, 16))]
+        s_grid, s_vox, s_q = self._streams[0:3]
+        s_chk = self._streams[3:6]
+        s_post = self._streams[6:]
+        hold = []
+        ep = {'point_clouds': self.cloud, 'input_xyz': self.cloud, 'input_features': None}
+        cloud = self.cloud
+        P = self.post
+        s_grid.wait_stream(main)
+        with torch.cuda.stream(s_grid):
+            grid = ops.query_grid_build(cloud, GRID_CELL) if cloud.shape[1] >= ops.GRID_QUERY_MIN_N else None
+        s_vox.wait_stream(main)
+        with torch.cuda.stream(s_vox):
+            voxels = [ops.voxel_down_sample(cloud[s].double(), P["voxel_size"]) for s in range(B)]
+        npts = [sa.npoint for sa in sas]
+        # SA1 sampling: the serial chain
+        inds1 = ops.furthest_point_sampling(cloud, npts[0])
+        xyz1 = ops.gather_xyz(cloud, inds1, transposed=False)
+        xyzs, inds = [xyz1], [inds1]
+        nested = all(npts[l + 1] <= npts[l] for l in range(3))
+        verdicts = []
+        if nested:
+            for l in range(1, 4):
+                s_chk[l - 1].wait_stream(main)
+                with torch.cuda.stream(s_chk[l - 1]):
+                    verdicts.append(ops.fps_prefix_check(xyz1, npts[l - 1], npts[l]))
+        s_q.wait_stream(main)
+        with torch.cuda.stream(s_q):                   # coordinates-only work of the deeper levels
+            for c in (s_chk if nested else []):
+                s_q.wait_stream(c)
+            for l in range(1, 4):
+                ind = (ops.furthest_point_sampling_spec(xyzs[-1], npts[l], verdicts[:l]) if nested
+                       else ops.furthest_point_sampling(xyzs[-1], npts[l]))
+                inds.append(ind)
+                xyzs.append(ops.gather_xyz(xyzs[-1], ind, transposed=False))
+            balls = [None] + [ops.ball_query(xyzs[l], xyzs[l - 1], sas[l].radius, sas[l].nsample) for l in range(1, 4)]
+            nn = []
+            for unknown, known in ((xyzs[2], xyzs[3]), (xyzs[1], xyzs[2])):
+                dist2, idx3 = ops.three_nn(unknown, known)
+                nn.append((idx3, ops.three_nn_weights(dist2)))
+                hold.append(dist2)
+        main.wait_stream(s_grid)
+        balls[0] = ops.ball_query(xyz1, cloud, sas[0].radius, sas[0].nsample, grid=grid)
+        feats, feats_t = [None] * 4, [None] * 4
+        feats[0], feats_t[0] = sas[0].pooled(cloud, xyz1, balls[0])
+        main.wait_stream(s_q)
+        for l in range(1, 4):
+            feats[l], feats_t[l] = sas[l].pooled(xyzs[l - 1], xyzs[l], balls[l], features_t=feats_t[l - 1])
+        for l in range(4):
+            ep['sa%d_xyz' % (l + 1)], ep['sa%d_features' % (l + 1)] = xyzs[l], feats[l]
+        ep['sa1_inds'], ep['sa2_inds'] = inds[0], inds[1]
+        f = bb.fp1(xyzs[2], xyzs[3], feats[2], feats[3], neighbours=nn[0])
+        f = bb.fp2(xyzs[1], xyzs[2], feats[1], f, neighbours=nn[1])
+        ep['fp2_features'], ep['fp2_xyz'] = f, xyzs[1]
+        ep['fp2_inds'] = inds[0][:, 0:xyzs[1].shape[1]]
+        ep = vp(xyzs[1], f, ep)
+        ep = gen(ep, grid=grid)
+        rows, nrows = ops.pred_decode(*[ep[k].float().contiguous() for k in
+                                        ("objectness_score", "grasp_score_pred", "grasp_angle_cls_pred",
+                                         "grasp_width_pred", "grasp_tolerance_pred", "fp2_xyz", "grasp_top_view_xyz")])
+        ep['grasp_rows'], ep['grasp_nrows'] = rows, nrows
+        main.wait_stream(s_vox)
+        kept = []
+        for sp in s_post[:B]:
+            sp.wait_stream(main)
+        for s in range(B):
+            sp = s_post[s % len(s_post)]
+            with torch.cuda.stream(sp):
+                n_s = nrows[s:s + 1]
+                mask = ops.collision_mask_device(voxels[s][0], voxels[s][1], rows[s], n_s, P["voxel_size"],
+                                                 P["approach_dist"], P["collision_thresh"])
+                free, nfree = ops.compact_rows(rows[s], mask, n_s)
+                k, nk = ops.grasp_nms_device(free, nfree, P["translation_thresh"], math.cos(P["rotation_thresh"]))
+                o = self._out
+                o["nrows%d" % s].copy_(n_s)
+                o["mask%d" % s].copy_(mask)
+                o["kept%d" % s].copy_(k)
+                o["nkept%d" % s].copy_(nk)
+                kept.append((k, nk, mask))
+                hold += [free, nfree]
+        for sp in s_post[:B]:
+            main.wait_stream(sp)
+        for c in (s_chk if nested else []):
+            main.wait_stream(c)
+        ep['kept'] = kept
+        hold += [grid, voxels, verdicts, balls, nn, feats_t, inds, xyzs]
+        ep['_hold'] = hold
+        return ep
+
+    def run_graph(self):
+        """one graph launch over the static input buffer; returns the (static) end_points of the captured pass"""
+        if self._graph is None:
+            from . import _abi
+            with torch.no_grad():
+                side = torch.cuda.Stream(device=self.dev)
+                side.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(side):                   # lazy one-time setup (weight packing, cuBLAS handles,
+                    self.forward_streams()                      # view tables) must not be captured
+                    self.forward_streams()
+                torch.cuda.current_stream().wait_stream(side)
+                torch.cuda.synchronize()
+                n0 = _abi.lib.b200_launch_count()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    ep = self.forward_streams()
+                self.launches = int(_abi.lib.b200_launch_count() - n0)
+            self._graph, self.end_points = g, ep
+        self._graph.replay()
+        return self.end_points
+
+    def infer(self, clouds=None):
+        """clouds: (B,N,3) float32 numpy / CPU tensor (None = whatever host_in already holds) -> per scene
+        dict(nrows, mask, kept (K,17)) as numpy; one H2D copy, one graph launch, one D2H copy"""
+        if clouds is not None:
+            self.views(self.host_in, "in")["cloud"].copy_(torch.as_tensor(clouds))
+        self.io_in.copy_(self.host_in, non_blocking=True)
+        self.run_graph()
+        self.host_out.copy_(self.io_out, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        v = self.views(self.host_out, "out")
+        res = []
+        for s in range(self.B):
+            k = int(v["nkept%d" % s][0])
+            n = int(v["nrows%d" % s][0])
+            res.append(dict(nrows=n, mask=v["mask%d" % s][:n].numpy().astype(bool), kept=v["kept%d" % s][:k].numpy()))
+        return res

@@ -333,6 +333,38 @@ def three_nn(unknowns, knows):
     return dist2, idx
 
 
+def three_nn_weights(dist2):
+    """dist2 (B,n,3) from three_nn -> inverse-distance weights (B,n,3) = (1/(sqrt(dist2)+1e-8)) / sum
+    [pointnet2_modules.py:394-397 after the sqrt of pointnet2_utils.py:140], one launch"""
+    _chk(dist2, "dist2", torch.float32)
+    weight = torch.empty_like(dist2)
+    with torch.cuda.device(dist2.device):
+        _abi.check(_lib.b200_three_nn_weights(_ptr(dist2), dist2.numel() // 3, None, _ptr(weight), _stream()),
+                   "three_nn_weights")
+    return weight
+
+
+def view_select(features, views, frames):
+    """features (B,2+V,S) f32 (ApproachNet conv3 output), views (V,3), frames (V,9) ->
+    (top_view_inds (B,S) i64, top_view_score (B,S), vp_xyz (B,S,3), vp_rot (B,S,3,3))   [models/modules.py:60-73]"""
+    _chk(features, "features", torch.float32)
+    _chk(views, "views", torch.float32)
+    _chk(frames, "frames", torch.float32)
+    b, c, s = features.shape
+    v = c - 2
+    if tuple(views.shape) != (v, 3) or frames.numel() != v * 9:
+        raise ValueError("b200grasp: view tables do not match the %d view scores" % v)
+    dev = features.device
+    inds = torch.empty((b, s), dtype=torch.int64, device=dev)
+    score = torch.empty((b, s), dtype=torch.float32, device=dev)
+    xyz = torch.empty((b, s, 3), dtype=torch.float32, device=dev)
+    rot = torch.empty((b, s, 3, 3), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _abi.check(_lib.b200_view_select(_ptr(features), _ptr(views), _ptr(frames), b, s, v, _ptr(inds), _ptr(score),
+                                         _ptr(xyz), _ptr(rot), _stream()), "view_select")
+    return inds, score, xyz, rot
+
+
 def three_interpolate(points, idx, weight):
     """points (B,c,m), idx (B,n,3) i32, weight (B,n,3) -> (B,c,n)   [interpolate.cpp:47-75]"""
     _chk(points, "points", torch.float32)

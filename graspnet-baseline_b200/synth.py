@@ -111,3 +111,28 @@ def mlp_params(seed, dims):
                     (0.3 * rng.standard_normal(cout)).astype(np.float32),
                     rng.uniform(0.5, 2.0, cout).astype(np.float32)))
     return out
+
+
+def fill_state_dict(module, seed):
+    """Deterministic parameters and BatchNorm statistics for a torch module, keyed by TENSOR NAME (so two
+    implementations with the same state_dict keys -- the reference GraspNet and this package's -- get the same
+    values whatever their construction order): conv weights N(0, 2/fan_in), biases and running means N(0, 0.1),
+    BatchNorm scales and running variances U(0.5, 1.5)."""
+    import zlib
+    import torch
+    sd = module.state_dict()
+    with torch.no_grad():
+        for name in sorted(sd):
+            t = sd[name]
+            if name.endswith("num_batches_tracked"):
+                continue
+            rng = np.random.default_rng([seed, zlib.crc32(name.encode())])
+            shape = tuple(t.shape)
+            if name.endswith("running_var") or (t.dim() == 1 and name.endswith("weight")):
+                v = rng.uniform(0.5, 1.5, shape)
+            elif name.endswith("running_mean") or name.endswith("bias"):
+                v = rng.normal(0.0, 0.1, shape)
+            else:
+                v = rng.normal(0.0, np.sqrt(2.0 / max(int(np.prod(shape[1:])), 1)), shape)
+            t.copy_(torch.from_numpy(v.astype(np.float32)).to(t.device))
+    return module

@@ -139,6 +139,18 @@ int b200_pred_decode(const float *objectness, const float *score, const float *a
                      const float *tolerance, const float *xyz, const float *view_xyz, int b, int ns,
                      int num_angle, int num_depth, float *rows, int32_t *nrows, void *stream);
 
+/* ApproachNet's tail (models/modules.py:60-73): features [b,2+v,s] fp32 (conv3's output) -> per seed the first
+ * maximum over the v view scores: top_inds [b,s] i64, top_score [b,s], vp_xyz [b,s,3] = views[top], vp_rot [b,s,9] =
+ * frames[top].  views [v,3] = generate_grasp_views(v) (utils/loss_utils.py:41-66) and frames [v,9] =
+ * batch_viewpoint_params_to_matrix(-views, 0) (:68-96) are caller-provided device tables (computed once). */
+int b200_view_select(const float *features, const float *views, const float *frames, int b, int s, int v,
+                     long long *top_inds, float *top_score, float *vp_xyz, float *vp_rot, void *stream);
+
+/* PointnetFPModule's interpolation weights (pointnet2/pointnet2_modules.py:394-397 after pointnet2_utils.py:140):
+ * dist2 [n,3] squared distances from b200_three_nn -> dist [n,3] = sqrt (may be NULL), weight [n,3] =
+ * (1/(dist+1e-8)) / sum over the three. */
+int b200_three_nn_weights(const float *dist2, int n, float *dist, float *weight, void *stream);
+
 /* Device-resident post-processing: pred_decode's rows -> collision mask -> surviving rows -> NMS -> kept rows, with
  * every row count read from / written to device memory (no host synchronisation between the stages).
  *  b200_collision_mask_device: ModelFreeCollisionDetector.detect's default return (collision_detector.py:37-112) for

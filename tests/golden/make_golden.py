@@ -23,7 +23,15 @@ neither exists on the GPU box, which only reads the committed .npz files.
                     equivalent torch indexing), then F.max_pool2d over nsample and CloudCrop's view
                     (models/modules.py:138-141).  Stores the geometry inputs, the seed of the parameters
                     (tests regenerate them with synth.mlp_params) and the pooled features.
-No pointnet2 fixture can be produced here: every pointnet2 op of the reference is
+  graspnet_*.npz  : the reference's WHOLE network -- models/graspnet.py::GraspNet(is_training=False).eval() and
+                    pred_decode, imported and run unmodified on the CPU in fp32 -- on a seeded cloud with seeded
+                    parameters (synth.fill_state_dict, keyed by state_dict name).  The reference's pointnet2 ops are
+                    CUDA-only, so the module object `pointnet2_utils._ext` (the compiled extension, imported from
+                    oracle/_ref) is replaced by a shim that answers the same ten functions with the C oracle
+                    (oracle/geom_oracle.c, itself pinned to the legacy CUDA kernels on the GPU box); every line of
+                    Python between those ops -- groupers, SharedMLP, FP modules, ApproachNet, CloudCrop, heads,
+                    decode -- is the reference's.  Stores the cloud, the parameter seed and (sub-sampled) outputs.
+No single-op pointnet2 fixture can be produced here: every pointnet2 op of the reference is
 CUDA-only and this container has no GPU -- those are pinned on the GPU box against
 oracle/_ref directly (tests/test_gpu_vs_legacy.py).
 """
@@ -266,8 +274,89 @@ def make_mlp():
         print("mlp", name, dims, tuple(y.shape), float(y.abs().max()))
 
 
+class _OracleExt:
+    """the ten functions of pointnet2._ext (bindings.cpp:13-26) on CPU tensors, answered by the C oracle"""
+
+    def __init__(self, oracle, torch):
+        self.o, self.t = oracle, torch
+
+    def _np(self, *ts):
+        return [np.ascontiguousarray(t.detach().cpu().numpy()) for t in ts]
+
+    def furthest_point_sampling(self, xyz, npoint):
+        return self.t.from_numpy(self.o.furthest_point_sampling(*self._np(xyz), npoint))
+
+    def gather_points(self, features, idx):
+        return self.t.from_numpy(self.o.gather_points(*self._np(features, idx)))
+
+    def ball_query(self, new_xyz, xyz, radius, nsample):
+        return self.t.from_numpy(self.o.ball_query(*self._np(new_xyz, xyz), radius, nsample))
+
+    def cylinder_query(self, new_xyz, xyz, rot, radius, hmin, hmax, nsample):
+        return self.t.from_numpy(self.o.cylinder_query(*self._np(new_xyz, xyz, rot), radius, hmin, hmax, nsample))
+
+    def group_points(self, features, idx):
+        return self.t.from_numpy(self.o.group_points(*self._np(features, idx)))
+
+    def three_nn(self, unknown, known):
+        d2, idx = self.o.three_nn(*self._np(unknown, known))
+        return self.t.from_numpy(d2), self.t.from_numpy(idx)
+
+    def three_interpolate(self, features, idx, weight):
+        return self.t.from_numpy(self.o.three_interpolate(*self._np(features, idx, weight)))
+
+
+def make_graspnet():
+    import torch
+    sys.path.insert(0, ROOT)
+    import oracle
+    oracle.cpu.build()
+    sys.path.insert(0, os.path.join(ROOT, "graspnet-baseline_b200"))
+    import synth
+    for d in ("models", "pointnet2", "utils", "knn"):
+        sys.path.insert(0, os.path.join(REF, d))
+    sys.path.insert(0, os.path.join(ROOT, "oracle", "_ref"))       # pointnet2._ext, knn_pytorch (import-time only)
+    import pointnet2_utils as ref_pu
+    ref_pu._ext = _OracleExt(oracle, torch)
+    import graspnet as ref_graspnet                                  # models/graspnet.py
+    torch.set_num_threads(os.cpu_count() or 1)
+    for name, seed, b, n in (("a", 63, 1, 5000), ("b", 84, 2, 3000)):
+        net = ref_graspnet.GraspNet(input_feature_dim=0, num_view=300, num_angle=12, num_depth=4,
+                                    cylinder_radius=0.05, hmin=-0.02, hmax_list=[0.01, 0.02, 0.03, 0.04],
+                                    is_training=False)
+        synth.fill_state_dict(net, seed)
+        net.eval()
+        cloud = np.stack([synth.tabletop_cloud(n, seed + i) for i in range(b)])
+        with torch.no_grad():
+            ep = net({"point_clouds": torch.from_numpy(cloud)})
+            rows = ref_graspnet.pred_decode(ep)
+        sd = net.state_dict()
+        save = {"cloud": cloud, "seed": seed, "state_keys": np.array(sorted(sd)),
+                "state_shapes": np.array([",".join(map(str, sd[k].shape)) for k in sorted(sd)]),
+                "sa1_inds": ep["sa1_inds"].numpy(), "fp2_inds": ep["fp2_inds"].numpy(),
+                "sa1_features": ep["sa1_features"].numpy()[:, :, ::16],
+                "sa4_features": ep["sa4_features"].numpy()[:, :, ::4],
+                "fp2_features": ep["fp2_features"].numpy()[:, :, ::8],
+                "objectness_score": ep["objectness_score"].numpy(),
+                "grasp_top_view_inds": ep["grasp_top_view_inds"].numpy(),
+                "grasp_top_view_score": ep["grasp_top_view_score"].numpy(),
+                "view_score": ep["view_score"].numpy()[:, ::8],
+                "grasp_top_view_xyz": ep["grasp_top_view_xyz"].numpy(),
+                "grasp_top_view_rot": ep["grasp_top_view_rot"].numpy()}
+        for k in ("grasp_score_pred", "grasp_angle_cls_pred", "grasp_width_pred", "grasp_tolerance_pred"):
+            save[k] = ep[k].numpy()[:, :, ::4]
+        for i, r in enumerate(rows):
+            save["rows_%d" % i] = r.numpy()
+        np.savez_compressed(os.path.join(HERE, f"graspnet_{name}.npz"), **save)
+        print("graspnet", name, cloud.shape, [tuple(r.shape) for r in rows],
+              "fp2 |max|", float(ep["fp2_features"].abs().max()))
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["collision", "knn", "decode", "mlp"]
+    which = sys.argv[1:] or ["collision", "knn", "decode", "mlp", "graspnet"]
+    if "graspnet" in which:
+        make_graspnet()
+        sys.exit(0) if which == ["graspnet"] else None
     if "mlp" in which:
         make_mlp()
     if "collision" in which:

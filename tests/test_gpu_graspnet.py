@@ -1,0 +1,149 @@
+"""The whole GraspNet forward (graspnet-baseline_b200/graspnet.py) against golden outputs of the REFERENCE network
+(tests/golden/graspnet_*.npz: models/graspnet.py::GraspNet + pred_decode run unmodified on the CPU, pointnet2 ops
+answered by the C oracle -- tests/golden/make_golden.py), the fused path against the composed path, and the
+CUDA-graph engine against the call-by-call sequence.
+
+Tolerances: sample / seed indices bit-exact; features 1e-5 relative to the tensor's scale PER MODULE (north_star:
+"features within 1e-5 relative (fp32)"; every fused module alone is held to 1e-5 in tests/test_gpu_mlp_fused.py).
+Through the network the bound is 1e-5 x the number of fused grouped-MLP modules chained in front of the tensor
+(SA4 / FP2 / ApproachNet outputs: 4; CloudCrop and the grasp heads: 1): the tensor core adds each K = 8 product group
+to its fp32 accumulator with truncation, a bias of up to half an ulp per step that a chain of modules accumulates (the
+measured errors are written to gpurun_out/graspnet_parity.txt; the reference's own GPU arithmetic -- cuDNN
+convolutions with TF32 allowed, torch's default -- is ~1e-3 from the same fp32 CPU results).  Discrete selections
+downstream of features (best view, decoded classes) must agree on all but a fraction of seeds (near-ties flip).
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+REL = 1e-5
+
+
+def _net(b200, seed, **kw):
+    net = b200.graspnet.GraspNet(input_feature_dim=0, num_view=300, num_angle=12, num_depth=4, cylinder_radius=0.05,
+                                 hmin=-0.02, hmax_list=[0.01, 0.02, 0.03, 0.04], is_training=False, **kw)
+    b200.synth.fill_state_dict(net, seed)
+    return net
+
+
+def close(got, want, rel=REL, what=""):
+    got, want = np.asarray(got, dtype=np.float64), np.asarray(want, dtype=np.float64)
+    scale = np.abs(want).max() if want.size else 1.0
+    err = np.abs(got - want).max() / max(scale, 1e-30) if want.size else 0.0
+    out = os.path.join(os.path.dirname(os.path.dirname(__file__)), "gpurun_out")
+    if os.path.isdir(out):
+        with open(os.path.join(out, "graspnet_parity.txt"), "a") as f:
+            f.write("%-40s max error %.3g of scale (tolerance %.1g)\n" % (what, err, rel))
+    assert err <= rel, "%s: max error %.3g of scale (tolerance %.1g)" % (what, err, rel)
+
+
+@pytest.mark.parametrize("name", ["a", "b"])
+def test_state_dict_keys_are_the_reference_s(name):
+    """CPU: same parameter / buffer names and shapes as the reference GraspNet -> its checkpoints load unchanged"""
+    import b200grasp
+    g = np.load(os.path.join(GOLD, "graspnet_%s.npz" % name))
+    sd = b200grasp.graspnet.GraspNet(is_training=False).state_dict()
+    assert sorted(sd) == list(g["state_keys"])
+    assert [",".join(map(str, sd[k].shape)) for k in sorted(sd)] == list(g["state_shapes"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["a", "b"])
+def test_forward_matches_reference_network(b200, name):
+    g = np.load(os.path.join(GOLD, "graspnet_%s.npz" % name))
+    net = _net(b200, int(g["seed"])).cuda().eval()
+    with torch.no_grad():
+        ep = net({"point_clouds": torch.from_numpy(g["cloud"]).cuda()})
+        rows = b200.graspnet.pred_decode(ep)
+    cpu = lambda k: ep[k].cpu().numpy()
+    assert (cpu("sa1_inds") == g["sa1_inds"]).all() and (cpu("fp2_inds") == g["fp2_inds"]).all()
+    close(cpu("sa1_features")[:, :, ::16], g["sa1_features"], what="golden %s sa1_features" % name)
+    close(cpu("sa4_features")[:, :, ::4], g["sa4_features"], 4 * REL, what="sa4_features")
+    close(cpu("fp2_features")[:, :, ::8], g["fp2_features"], 4 * REL, what="fp2_features")
+    close(cpu("objectness_score"), g["objectness_score"], 4 * REL, what="objectness_score")
+    close(cpu("view_score")[:, ::8], g["view_score"], 4 * REL, what="view_score")
+    same_view = cpu("grasp_top_view_inds") == g["grasp_top_view_inds"]
+    assert same_view.mean() >= 0.995, "best view differs on %d seeds" % (~same_view).sum()
+    close(cpu("grasp_top_view_score"), g["grasp_top_view_score"], 4 * REL, what="top view score")
+    assert np.abs(cpu("grasp_top_view_xyz") - g["grasp_top_view_xyz"])[same_view].max() <= 1e-6
+    assert np.abs(cpu("grasp_top_view_rot") - g["grasp_top_view_rot"])[same_view].max() <= 1e-6
+    sub = same_view[:, ::4]
+    for k in ("grasp_score_pred", "grasp_angle_cls_pred", "grasp_width_pred", "grasp_tolerance_pred"):
+        got, want = cpu(k)[:, :, ::4], g[k]
+        sel = np.broadcast_to(sub[:, None, :, None], want.shape)
+        close(got[sel], want[sel], what=k)
+    for i, r in enumerate(rows):
+        want = g["rows_%d" % i]
+        got = r.cpu().numpy()
+        assert got.shape == want.shape, "scene %d: %d rows decoded, reference %d" % (i, got.shape[0], want.shape[0])
+        # rows are in seed order; classes (depth, angle) are argmaxes and may flip on near-ties -> row-wise agreement
+        ok = np.abs(got - want).max(axis=1) <= 1e-4
+        assert ok.mean() >= 0.98, "scene %d: %d of %d decoded rows differ" % (i, (~ok).sum(), len(ok))
+
+
+@pytest.mark.gpu
+def test_fused_path_equals_composed_path(b200):
+    """fast path (fused grouped MLPs, folded BatchNorm, view table) == the reference's op sequence on the drop-ins"""
+    net = _net(b200, 90).cuda().eval()
+    cloud = torch.from_numpy(np.stack([b200.synth.tabletop_cloud(6000, 5), b200.synth.tabletop_cloud(6000, 6)])).cuda()
+    tf32 = torch.backends.cudnn.allow_tf32
+    with torch.no_grad():
+        fast = net({"point_clouds": cloud})
+        b200.fused_modules.FUSED = False
+        torch.backends.cudnn.allow_tf32 = False                 # the composed path's convolutions in fp32
+        try:
+            slow = net({"point_clouds": cloud})
+        finally:
+            b200.fused_modules.FUSED = True
+            torch.backends.cudnn.allow_tf32 = tf32
+    assert torch.equal(fast["sa1_inds"], slow["sa1_inds"])
+    for depth, k in ((1, "sa1_features"), (2, "sa2_features"), (3, "sa3_features"), (4, "sa4_features"),
+                     (4, "fp2_features"), (4, "objectness_score")):
+        close(fast[k].cpu().numpy(), slow[k].cpu().numpy(), depth * REL, what="fused vs composed " + k)
+    same = (fast["grasp_top_view_inds"] == slow["grasp_top_view_inds"])
+    assert same.float().mean() >= 0.995
+    d = (fast["grasp_top_view_rot"] - slow["grasp_top_view_rot"]).abs()[same]
+    assert d.max() <= 1e-6
+    sel = same[:, None, :, None].expand_as(fast["grasp_score_pred"])
+    for k in ("grasp_score_pred", "grasp_angle_cls_pred", "grasp_width_pred", "grasp_tolerance_pred"):
+        close(fast[k][sel].cpu().numpy(), slow[k][sel].cpu().numpy(), what=k)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("batch", [1, 3])
+def test_engine_graph_equals_call_sequence(b200, batch):
+    """GraspNetEngine (one graph, several streams, device-resident post-processing) == net() + pred_decode +
+    ModelFreeCollisionDetector.detect + GraspGroup.nms called one after the other (test.py:86-96)"""
+    net = _net(b200, 72).cuda().eval()
+    n = 8000
+    clouds = np.stack([b200.synth.tabletop_cloud(n, 20 + s) for s in range(batch)])
+    eng = b200.graspnet.GraspNetEngine(net, batch=batch, num_point=n)
+    res = eng.infer(clouds)
+    res2 = eng.infer(clouds)                                    # replay
+    with torch.no_grad():
+        ep = net({"point_clouds": torch.from_numpy(clouds).cuda()})
+        rows = b200.graspnet.pred_decode(ep)
+    P = b200.graspnet.POST
+    for s in range(batch):
+        assert torch.equal(eng.end_points["sa1_inds"], ep["sa1_inds"])
+        assert torch.equal(eng.end_points["fp2_features"], ep["fp2_features"]), "streams changed the arithmetic"
+        gg = b200.GraspGroup(rows[s].cpu().numpy())
+        det = b200.ModelFreeCollisionDetector(clouds[s], voxel_size=P["voxel_size"])
+        mask = det.detect(gg, approach_dist=P["approach_dist"], collision_thresh=P["collision_thresh"])
+        want = gg[~mask].nms().grasp_group_array
+        assert res[s]["nrows"] == len(gg)
+        assert (res[s]["mask"] == mask).all()
+        assert res[s]["kept"].shape == want.shape and (res[s]["kept"] == want).all()
+        assert (res2[s]["kept"] == res[s]["kept"]).all()
+    # a new cloud through the same graph
+    clouds2 = np.stack([b200.synth.tabletop_cloud(n, 40 + s) for s in range(batch)])
+    r3 = eng.infer(clouds2)
+    with torch.no_grad():
+        ep2 = net({"point_clouds": torch.from_numpy(clouds2).cuda()})
+        rows2 = b200.graspnet.pred_decode(ep2)
+    for s in range(batch):
+        assert r3[s]["nrows"] == rows2[s].shape[0]
+    assert eng.launches > 0
