@@ -1,13 +1,16 @@
 #!/usr/bin/env python
-"""bench.py -- scenes/sec of the GraspNet-baseline geometry hot path on B200.
+"""bench.py -- scenes/sec of GraspNet-baseline inference (geometry hot path + post-processing) on B200.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-A "step" = one scene (BASELINE.json configs[1]: batch 1, 20000 points -> 2048/1024/512/256 SA
-points, 1024 seeds x 4 cylinder depths, 1024 grasps collision-checked + NMS) through every
-geometry op of the path in model order (graspnet-baseline_b200/pipeline.py).  Rank r of N
-processes its own scenes, no collective on the data path (scaling = weak).
+A "step" = one scene of BASELINE.json configs[1]: GraspNet inference (seeded random weights, batch 1,
+20000 points -> 2048/1024/512/256 SA points -> 1024 seeds, 300 views / 12 angles / 4 depths),
+pred_decode, voxel down-sample of the cloud, collision detection of the decoded grasps and NMS --
+graspnet-baseline_b200/graspnet.py::GraspNetEngine, one CUDA graph per scene.  Rank r of N
+processes its own scenes, no collective on the data path (scaling = weak).  The geometry ops alone
+(graspnet-baseline_b200/pipeline.py, stand-in features instead of the MLPs: the previous headline)
+are reported beside it under "geometry_path", with the per-kernel roofline table.
 
 Prints ONE JSON line on rank 0 (see the round contract): value = scenes/s with inputs
 resident in HBM; e2e = scenes/s through the reference-facing API with HOST buffers (H2D of
@@ -34,8 +37,10 @@ if ROOT not in sys.path:
 
 METRIC = "scenes/sec (20k pts, 1024 seeds, collision+NMS)"
 UNIT = "scenes/s"
-WORKLOAD = ("cfg2: GraspNet inference geometry path, batch 1, 20000 pts -> SA 2048/1024/512/256, "
-            "1024 seeds x 4 cylinder depths, collision 1024 grasps x voxel(0.01) cloud + NMS")
+WORKLOAD = ("cfg2: GraspNet inference (seeded random weights, eval), batch 1, 20000 pts -> SA 2048/1024/512/256 -> "
+            "1024 seeds, 300 views / 12 angles / 4 depths, pred_decode, collision (voxel 0.01, approach 0.05, "
+            "thresh 0.01) of the decoded grasps + NMS")
+WEIGHT_SEED = 12          # synth.fill_state_dict seed: every seed passes the objectness test -> 1024 grasps per scene
 SA_CFG = [(2048, 0.04, 64, 0), (1024, 0.1, 32, 128), (512, 0.2, 16, 256), (256, 0.3, 16, 256)]
 HMAX = [0.01, 0.02, 0.03, 0.04]
 
@@ -122,69 +127,91 @@ def fused_mlp_report(sc, timed, dev):
 
 # ---------------------------------------------------------------- CPU port of one step (oracle)
 
-def cpu_step(oracle, host, s=0):
-    """The same op sequence as pipeline.GeometryScene.run() for scene s, on the host."""
-    xyz = host["cloud"][s:s + 1]
-    cloud = xyz
-    lv = []
-    for lvl, (npoint, radius, nsample, cin) in enumerate(SA_CFG):
-        xyz_t = np.ascontiguousarray(xyz.transpose(0, 2, 1))
-        inds = oracle.furthest_point_sampling(xyz, npoint)
-        new_xyz = np.ascontiguousarray(oracle.gather_points(xyz_t, inds).transpose(0, 2, 1))
-        idx = oracle.ball_query(new_xyz, xyz, radius, nsample)
-        oracle.group_points(xyz_t, idx)
-        if cin:
-            oracle.group_points(host["feat"]["sa%d_in" % (lvl + 1)][s:s + 1], idx)
-        lv.append(new_xyz)
-        xyz = new_xyz
-    for name, u, k in (("fp1", lv[2], lv[3]), ("fp2", lv[1], lv[2])):
-        d2, i3 = oracle.three_nn(u, k)
-        oracle.three_interpolate(host["feat"][name + "_known"][s:s + 1], i3, np.full_like(d2, 1.0 / 3.0))
-    rot9 = host["rot"][s:s + 1].reshape(1, -1, 9)
-    cloud_t = np.ascontiguousarray(cloud.transpose(0, 2, 1))
-    for h in HMAX:
-        ci = oracle.cylinder_query(lv[1], cloud, rot9, 0.05, -0.02, h, 64)
-        oracle.group_points(cloud_t, ci)
-    # post-processing as test.py:94-96 + GraspGroup.nms(): voxel down-sample, collision mask, NMS of the survivors
-    scene = oracle.voxel_down_sample(host["cloud"][s].astype(np.float64), 0.01)
-    mask = oracle.collision_detect(scene, host["grasps"][s], 0.01, 0.05, 0.01)
-    keep = oracle.grasp_nms(host["grasps"][s][~mask])
-    return mask, keep
+class OracleOps:
+    """The functions of pointnet2._ext (bindings.cpp:13-26) on CPU tensors, answered by the C oracle
+    (oracle/geom_oracle.c, OpenMP): stands in for b200grasp.ops under the network's composed path, i.e. the reference's
+    own op sequence with its CUDA-only ops replaced by their CPU restatement."""
+
+    def __init__(self, oracle, torch):
+        self.o, self.t = oracle, torch
+
+    def _np(self, *ts):
+        return [np.ascontiguousarray(t.detach().numpy()) for t in ts]
+
+    def furthest_point_sampling(self, xyz, npoint):
+        return self.t.from_numpy(self.o.furthest_point_sampling(*self._np(xyz), npoint))
+
+    def gather_points(self, features, idx):
+        return self.t.from_numpy(self.o.gather_points(*self._np(features, idx)))
+
+    def ball_query(self, new_xyz, xyz, radius, nsample):
+        return self.t.from_numpy(self.o.ball_query(*self._np(new_xyz, xyz), radius, nsample))
+
+    def cylinder_query(self, new_xyz, xyz, rot, radius, hmin, hmax, nsample):
+        return self.t.from_numpy(self.o.cylinder_query(*self._np(new_xyz, xyz, rot), radius, hmin, hmax, nsample))
+
+    def group_points(self, features, idx):
+        return self.t.from_numpy(self.o.group_points(*self._np(features, idx)))
+
+    def three_nn(self, unknown, known):
+        d2, idx = self.o.three_nn(*self._np(unknown, known))
+        return self.t.from_numpy(d2), self.t.from_numpy(idx)
+
+    def three_interpolate(self, features, idx, weight):
+        return self.t.from_numpy(self.o.three_interpolate(*self._np(features, idx, weight)))
 
 
-def host_inputs(batch, seed=1234):
-    """Host copies of everything a step consumes (same generator as GeometryScene)."""
+def make_net(device="cpu", passes=3):
+    """GraspNet with the configuration of test.py:52-53 and seeded random parameters / BatchNorm statistics"""
     import b200grasp
+    net = b200grasp.graspnet.GraspNet(input_feature_dim=0, num_view=300, num_angle=12, num_depth=4, cylinder_radius=0.05,
+                                      hmin=-0.02, hmax_list=HMAX, is_training=False, passes=passes)
+    b200grasp.synth.fill_state_dict(net, WEIGHT_SEED)
+    return net.to(device).eval()
+
+
+def scene_cloud(seed):
     from b200grasp import synth
-    import torch
-    h = {"cloud": np.stack([synth.tabletop_cloud(20000, seed + s) for s in range(batch)])}
-    h["rot"] = np.stack([synth.seed_rotations(1024, seed + s) for s in range(batch)])
-    h["grasps"] = [synth.synthetic_grasps(h["cloud"][s], 1024, seed + s) for s in range(batch)]
-    g = torch.Generator(device="cpu").manual_seed(seed)
-    npts = [c[0] for c in SA_CFG]
-    feat = {}
-    for lvl, (_, _, _, cin) in enumerate(SA_CFG):
-        if cin:
-            feat["sa%d_in" % (lvl + 1)] = torch.randn(batch, cin, npts[lvl - 1], generator=g).numpy()
-    feat["fp1_known"] = torch.randn(batch, 256, npts[3], generator=g).numpy()
-    feat["fp2_known"] = torch.randn(batch, 256, npts[2], generator=g).numpy()
-    h["feat"] = feat
-    return h
+    return synth.tabletop_cloud(20000, seed)
+
+
+def cpu_inference(net, oracle, torch, cloud):
+    """One scene on the host: network forward (composed path: reference op sequence, oracle ops + torch CPU layers),
+    pred_decode, voxel down-sample, collision mask, NMS -- the step GraspNetEngine runs on the GPU."""
+    with torch.no_grad():
+        ep = net({"point_clouds": torch.from_numpy(cloud[None])})
+    rows = oracle.post.pred_decode(*[ep[k][0].numpy() for k in
+                                     ("objectness_score", "grasp_score_pred", "grasp_angle_cls_pred", "grasp_width_pred",
+                                      "grasp_tolerance_pred", "fp2_xyz", "grasp_top_view_xyz")])
+    scene = oracle.voxel_down_sample(cloud.astype(np.float64), 0.01)
+    mask = oracle.collision_detect(scene, rows, 0.01, 0.05, 0.01)
+    free = rows[~mask]
+    return rows, mask, free[oracle.grasp_nms(free)]
 
 
 def time_cpu(steps, warmup):
     # the C port is OpenMP-parallel; torchrun exports OMP_NUM_THREADS=1, which would make this a 1-thread run
     os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
+    import torch
     import oracle
+    import b200grasp
+    from b200grasp import fused_modules, pointnet2_utils
     oracle.cpu.build()
-    host = host_inputs(1)
-    for _ in range(max(warmup, 1)):
-        cpu_step(oracle, host)
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        cpu_step(oracle, host)
-    dt = time.perf_counter() - t0
-    return steps / dt, dt / steps
+    torch.set_num_threads(os.cpu_count() or 1)
+    net = make_net("cpu")
+    cloud = scene_cloud(1234)
+    fused, ext = fused_modules.FUSED, pointnet2_utils._ext
+    fused_modules.FUSED, pointnet2_utils._ext = False, OracleOps(oracle, torch)
+    try:
+        for _ in range(max(warmup, 1)):
+            cpu_inference(net, oracle, torch, cloud)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            out = cpu_inference(net, oracle, torch, cloud)
+        dt = time.perf_counter() - t0
+    finally:
+        fused_modules.FUSED, pointnet2_utils._ext = fused, ext
+    return steps / dt, dt / steps, out
 
 
 # ---------------------------------------------------------------- clocks sampler
@@ -324,6 +351,62 @@ def load_legacy():
         return None
 
 
+def inference_op_times(torch, b200grasp, net, cloud, flush, reps=7):
+    """Per-op CUDA-event times of one whole scene run call by call on one stream (network forward, decode, device
+    post-processing): every public function of b200grasp.ops is wrapped for the duration of the pass; what is left of
+    the total is the torch side (fp32 GEMMs of the FP modules / ApproachNet / heads, concatenations, copies)."""
+    import inspect
+    from b200grasp import ops, graspnet, postprocess
+    rec = []
+
+    def wrap(name, fn):
+        def w(*a, **k):
+            st = torch.cuda.current_stream()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(st)
+            r = fn(*a, **k)
+            e1.record(st)
+            rec.append((name, e0, e1))
+            return r
+        return w
+
+    orig = {n: f for n, f in vars(ops).items() if inspect.isfunction(f) and not n.startswith("_")
+            and f.__module__ == ops.__name__}
+    per, totals = {}, []
+    try:
+        for n, f in orig.items():
+            setattr(ops, n, wrap(n, f))
+        for _ in range(reps + 2):
+            flush.zero_()
+            del rec[:]
+            t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0.record()
+            with torch.no_grad():
+                ep = net({"point_clouds": cloud})
+                rows, nrows = b200grasp.pred_decode_device(ep)
+                postprocess.grasp_postprocess_device(cloud[0], rows[0], nrows[0:1])
+            t1.record()
+            torch.cuda.synchronize()
+            seen = {}
+            for name, e0, e1 in rec:
+                k = seen.get(name, 0)
+                seen[name] = k + 1
+                per.setdefault("%s#%d" % (name, k), []).append(e0.elapsed_time(e1))
+            totals.append(t0.elapsed_time(t1))
+    finally:
+        for n, f in orig.items():
+            setattr(ops, n, f)
+    rows = [{"op": k, "ms": round(float(np.median(v[2:])), 5)} for k, v in per.items()]
+    total = float(np.median(totals[2:]))
+    ours = sum(r["ms"] for r in rows)
+    rows.sort(key=lambda r: -r["ms"])
+    return {"what": "one scene call by call on one stream, eager, L2 flushed first; ops = this library's C-ABI calls in "
+                    "call order (#k = k-th call: furthest_point_sampling/gather_xyz/ball_query #0-3 = SA1-SA4, "
+                    "group_mlp_maxpool #0 = SA1, #1 = CloudCrop, group_feat_mlp_maxpool #0-2 = SA2-SA4)",
+            "total_ms": round(total, 4), "library_ops_ms": round(ours, 4),
+            "torch_layers_and_launch_gaps_ms": round(total - ours, 4), "ops": rows}
+
+
 # ---------------------------------------------------------------- our arm
 
 def run_ours(args, rank, world, local_rank):
@@ -360,7 +443,14 @@ def run_ours(args, rank, world, local_rank):
         # whole job: MAX of the elapsed device time over ranks (each rank ran `steps` scenes of its own shard)
         return b200grasp.sharding.whole_job_throughput(steps, ms, device=dev)[1]
 
-    sc.run_graph()                                          # capture (untimed, once)
+    from b200grasp import graspnet, synth
+    net = make_net(dev)
+    eng = graspnet.GraspNetEngine(net, batch=1, num_point=20000, device=dev)
+    cloud_host = scene_cloud(1234 + 1000 * rank)
+    eng.views(eng.host_in, "in")["cloud"].copy_(torch.from_numpy(cloud_host)[None])
+    eng.io_in.copy_(eng.host_in)
+    eng.run_graph()                                         # capture (untimed, once)
+    sc.run_graph()
     torch.cuda.synchronize()
     try:
         uuid = torch.cuda.get_device_properties(dev).uuid
@@ -368,22 +458,49 @@ def run_ours(args, rank, world, local_rank):
         uuid = None
     clocks = Clocks(local_rank, uuid)
     for _ in range(args.warmup):
-        sc.run_graph()
+        eng.run_graph()
     clocks.start()                                          # samples only while the timed region below runs
-    total_ms = timed(sc.run_graph, args.steps, args.warmup)
+    total_ms = timed(eng.run_graph, args.steps, args.warmup)
     clk = clocks.summary()
-    launches = sc.launches                                  # our kernels per step (library counter at capture)
+    launches = eng.launches                                 # our kernels per step (library counter at capture)
+
+    def call_sequence():
+        """the same scene as the reference's scripts run it (test.py:86-96): net(), pred_decode, detector, nms called
+        one after the other through the drop-ins, one stream, eager"""
+        with torch.no_grad():
+            ep = net({"point_clouds": eng.cloud})
+            rows = graspnet.pred_decode(ep)[0]
+        gg = b200grasp.GraspGroup(rows.cpu().numpy())
+        det = b200grasp.ModelFreeCollisionDetector(cloud_host, voxel_size=0.01, device=dev)
+        mask = det.detect(gg, approach_dist=0.05, collision_thresh=0.01)
+        return gg, mask, gg[~mask].nms(device=dev)
+
+    seq_ms = timed(call_sequence, args.steps, args.warmup)
+    # ---- e2e: host cloud in, host results out, every step, through the engine's public call
+    h2d, d2h = eng.host_in.numel(), eng.host_out.numel()
+    e2e_ms = timed(lambda: eng.infer(None), args.steps, args.warmup)
+    got = eng.infer(None)[0]
+    gg, mask, kept = call_sequence()
+    if not (got["nrows"] == len(gg) and np.array_equal(got["mask"], mask)
+            and np.array_equal(got["kept"], kept.grasp_group_array)):
+        raise SystemExit("bench: the engine graph and the drop-in call sequence disagree")
+    infer_counts = {"decoded_grasps": int(got["nrows"]), "colliding": int(got["mask"].sum()),
+                    "kept_after_nms": int(got["kept"].shape[0])}
+
+    # ================= geometry ops alone (pipeline.GeometryScene: stand-in features instead of the MLPs)
+    geo_total_ms = timed(sc.run_graph, args.steps, args.warmup)
+    geo_launches = sc.launches
     serial_ms = timed(sc.run, args.steps, args.warmup)      # same ops, one stream, eager launches
     sc.glue = 0
     sc.run()
     glue = sc.glue
 
-    # ---- e2e: host buffers in, host results out, every step
+    # ---- geometry e2e: host buffers in, host results out, every step
     host = sc.host
     pin_in = sc.host_io_in(pinned=True)                     # cloud | seed rotations | grasp rows | row count
     pin_out = torch.zeros(sc.io_out.numel(), dtype=torch.uint8).pin_memory()
     res = sc.io_views(pin_out, "out")                       # seed indices | collision mask | kept rows | kept count
-    h2d, d2h = pin_in.numel(), pin_out.numel()
+    geo_h2d, geo_d2h = pin_in.numel(), pin_out.numel()
 
     def e2e_step():
         # one pinned host buffer -> the graph's static inputs -> ONE graph launch (geometry + voxel down-sample +
@@ -394,7 +511,7 @@ def run_ours(args, rank, world, local_rank):
         torch.cuda.current_stream().synchronize()           # the caller reads the results now
         return res["kept0"][: int(res["nkept0"][0])], res["mask0"]
 
-    e2e_ms = timed(e2e_step, args.steps, args.warmup)
+    geo_e2e_ms = timed(e2e_step, args.steps, args.warmup)
 
     # the same scene through the numpy-in / numpy-out drop-ins, called one after the other as test.py:94-96 does
     # (detector rebuilt per scene), on a second stream beside the geometry graph: reported for comparison
@@ -433,6 +550,32 @@ def run_ours(args, rank, world, local_rank):
                           "FPS, gather, ball query, grouping, three_nn, three_interpolate, 4x cylinder query of one cfg2 scene",
                   "legacy_geometry_ms_per_scene": round(leg_ms, 4), "ours_geometry_ms_per_scene": round(geo_ms, 4),
                   "speedup": round(leg_ms / geo_ms, 2) if geo_ms > 0 else None}
+        # the whole network forward as the reference runs it: its own op sequence (composed path), its own CUDA
+        # extension for the pointnet2 ops, torch / cuDNN layers (TF32 allowed, torch's default), eager launches
+        from b200grasp import fused_modules, pointnet2_utils
+        fused, pext = fused_modules.FUSED, pointnet2_utils._ext
+        fused_modules.FUSED, pointnet2_utils._ext = False, ext
+
+        def legacy_forward():
+            with torch.no_grad():
+                return net({"point_clouds": eng.cloud})
+
+        try:
+            legf_ms = timed(legacy_forward, lsteps, 3) / lsteps
+        finally:
+            fused_modules.FUSED, pointnet2_utils._ext = fused, pext
+
+        def our_forward():
+            with torch.no_grad():
+                return net({"point_clouds": eng.cloud})
+
+        ourf_ms = timed(our_forward, args.steps, args.warmup) / args.steps
+        legacy.update({"forward_what": "GraspNet forward (no decode / collision / NMS): reference op sequence with its "
+                                       "own pointnet2._ext + torch/cuDNN layers, eager  vs  this package's forward "
+                                       "(eager, one stream) and the engine graph (whole step incl. post-processing)",
+                       "legacy_forward_ms": round(legf_ms, 4), "ours_forward_eager_ms": round(ourf_ms, 4),
+                       "ours_whole_step_graph_ms": round(total_ms / args.steps, 4),
+                       "forward_speedup_vs_graph_step": round(legf_ms / (total_ms / args.steps), 2)})
     # ---- config 3 shape: 64 scenes per graph launch on this GPU (throughput mode; extra, not the headline)
     batch64 = None
     if world == 1 and not args.no_batch64:
@@ -464,8 +607,18 @@ def run_ours(args, rank, world, local_rank):
         batch64["kernels"] = rows[:12]
         batch64["peak_gbs"] = peaks()[0]
         del sc64
+        eng64 = graspnet.GraspNetEngine(net, batch=64, num_point=20000, device=dev)
+        eng64.cloud.copy_(torch.from_numpy(np.stack([scene_cloud(4321 + s) for s in range(64)])))
+        eng64.run_graph()
+        torch.cuda.synchronize()
+        i_ms = timed(eng64.run_graph, b_steps, 3) / b_steps
+        batch64["inference"] = {"workload": "cfg3: 64 scenes of whole GraspNet inference + post-processing in one graph "
+                                            "launch on one GPU", "ms_per_64_scenes": round(i_ms, 4),
+                                "scenes_per_s": round(64.0 / (i_ms * 1e-3), 1), "gpu_launches_per_step": eng64.launches}
+        del eng64
     # ---- SURVEY.md 8(f) f1 (extra, not part of the step): group -> shared MLP -> max-pool fused on the tensor cores
     fused_mlp = fused_mlp_report(sc, timed, dev) if world == 1 else None
+    infer_ops = inference_op_times(torch, b200grasp, net, eng.cloud, flush)
     # ---- per-kernel pass (rank 0): CUDA events around every launch, L2 flushed before each pass
     per = {}
     reps = 9
@@ -507,18 +660,32 @@ def run_ours(args, rank, world, local_rank):
             "scaling": "weak", "vs_baseline": None, "dtype": "f32 (fp64 collision/NMS, int32 indices)",
             "data": "synthetic",
             "config": {"workload": WORKLOAD, "scenes_per_step_per_gpu": 1, "l2": "flushed between timed iterations "
-                       "(512 MiB write)", "glue_torch_launches_per_step": glue,
-                       "execution": "one CUDA graph per scene, ops forked over 5 streams by data dependence",
-                       "single_stream_eager_ms_per_step": round(serial_ms / args.steps, 4)},
+                       "(512 MiB write)", "weights": "synth.fill_state_dict(seed %d), eval-mode BatchNorm" % WEIGHT_SEED,
+                       "grouped_mlp_arithmetic": "3xTF32 on tcgen05 (fp32-grade); other layers fp32 cuBLAS GEMMs",
+                       "execution": "one CUDA graph per scene (GraspNetEngine), forked over streams by data dependence",
+                       "scene": infer_counts},
             "clocks": clk, "gpu_launches": launches * args.steps,
             "e2e": {"value": round(e2e, 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": round(e2e_ms / args.steps, 4),
-                    "api": "GeometryScene.run_graph(): one pinned host buffer (cloud | rotations | grasp rows) copied "
-                           "into the graph's static inputs, one graph launch (geometry + voxel + collision + NMS on "
-                           "the device), one copy of the results (seeds | mask | kept rows) to pinned host memory, "
-                           "stream synchronised",
-                    "dropin_calls_ms_per_step": round(dropin_ms / args.steps, 4)},
+                    "api": "GraspNetEngine.infer(): the cloud in pinned host memory copied into the graph's static "
+                           "input, one graph launch (network + pred_decode + voxel + collision + NMS on the device), "
+                           "one copy of the results (decoded count | mask | kept rows | kept count) to pinned host "
+                           "memory, stream synchronised, numpy views returned",
+                    "call_sequence_ms_per_step": round(seq_ms / args.steps, 4),
+                    "call_sequence": "net(end_points), pred_decode, GraspGroup, ModelFreeCollisionDetector(...).detect, "
+                                     ".nms() through the drop-ins, one after the other as test.py:86-96 (eager, "
+                                     "numpy round trips); results equal the engine's (checked in this run)"},
             "roofline": roof, "legacy_cuda": legacy, "batch64": batch64, "fused_mlp": fused_mlp,
+            "inference_ops": infer_ops,
+            "geometry_path": {"what": "the geometry ops + post-processing alone (pipeline.GeometryScene: stand-in "
+                                      "features instead of the MLPs, 1024 synthetic grasps), one graph per scene",
+                              "scenes_per_s": round(world * args.steps / (geo_total_ms * 1e-3), 2),
+                              "ms_per_step": round(geo_total_ms / args.steps, 4),
+                              "gpu_launches_per_step": geo_launches, "glue_torch_launches_per_step": glue,
+                              "single_stream_eager_ms_per_step": round(serial_ms / args.steps, 4),
+                              "e2e_scenes_per_s": round(world * args.steps / (geo_e2e_ms * 1e-3), 2),
+                              "e2e_h2d_bytes": int(geo_h2d), "e2e_d2h_bytes": int(geo_d2h),
+                              "dropin_calls_ms_per_step": round(dropin_ms / args.steps, 4)},
             "kernels": kern}
     return line
 
@@ -540,13 +707,15 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return 0
-        sps, sec = time_cpu(args.steps, args.warmup)
+        sps, sec, _ = time_cpu(args.steps, args.warmup)
         cores = os.cpu_count()
         cb = {"value": round(sps, 4), "unit": UNIT, "cores": cores, "kind": "port",
-              "sample": "%d whole scenes of the cfg2 workload (oracle/geom_oracle.c, OpenMP over centres/grasps)" % args.steps}
+              "sample": "%d whole scenes of the cfg2 workload: the network's reference op sequence with the pointnet2 ops "
+                        "answered by oracle/geom_oracle.c (OpenMP) and the layers by torch CPU (all threads), then "
+                        "pred_decode / voxel / collision / NMS restated in oracle/post.py" % args.steps}
         print(json.dumps({"metric": METRIC, "value": round(sps, 4), "unit": UNIT, "n_gpus": world, "steps": args.steps,
                           "warmup": args.warmup, "ms_per_step": round(sec * 1e3, 3), "higher_is_better": True,
-                          "scaling": "weak", "vs_baseline": None, "dtype": "f32 (fp64 collision/NMS)", "data": "synthetic",
+                          "scaling": "weak", "vs_baseline": None, "dtype": "f32 (fp64 collision/NMS, int32 indices)", "data": "synthetic",
                           "config": {"workload": WORKLOAD}, "impl": "reference", "cpu_baseline": cb,
                           "e2e": {"value": round(sps, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
         return 0
@@ -555,9 +724,11 @@ def main():
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             n = 8
-            sps, sec = time_cpu(n, 1)
+            sps, sec, cpu_out = time_cpu(n, 1)
             line["cpu_baseline"] = {"value": round(sps, 4), "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
-                                    "sample": "%d whole scenes of the same workload, oracle C port with OpenMP" % n}
+                                    "sample": "%d whole scenes of the same workload (network forward: oracle C ops with "
+                                              "OpenMP + torch CPU layers; decode / voxel / collision / NMS: oracle)" % n,
+                                    "decoded_grasps": int(cpu_out[0].shape[0]), "kept_after_nms": int(cpu_out[2].shape[0])}
         print(json.dumps(line))
     if world > 1:
         import torch.distributed as dist
