@@ -27,7 +27,7 @@ __global__ void __launch_bounds__(DT)
 pred_decode_kernel(const float *__restrict__ objectness, const float *__restrict__ score,
                    const float *__restrict__ angle_cls, const float *__restrict__ width,
                    const float *__restrict__ tol, const float *__restrict__ xyz, const float *__restrict__ view,
-                   int ns, int na, int nd, float *__restrict__ rows, int32_t *__restrict__ nrows) {
+                   int ns, int na, int nd, int vec4, float *__restrict__ rows, int32_t *__restrict__ nrows) {
   __shared__ int warp_sum[DT / 32];
   __shared__ int s_base;
   __shared__ Frame first3[3];
@@ -46,24 +46,53 @@ pred_decode_kernel(const float *__restrict__ objectness, const float *__restrict
     if (i < ns) {
       keep = __ldg(obj + ns + i) > __ldg(obj + i);                 // argmax over 2 == 1 (first maximum wins a tie)
       float best = 0.f;
-      for (int d = 0; d < nd; ++d) {
-        // angle class of this depth: first maximum over the A class scores
-        int a_best = 0;
-        float c_best = __ldg(cl + ((size_t)0 * ns + i) * nd + d);
+      int a_of[MAXD];
+      if (vec4) {
+        // D = 4: the four depths of (angle class a, seed i) are one aligned float4; the A loads are independent
+        const float4 *c4 = reinterpret_cast<const float4 *>(cl) + i;
+        float4 cb = __ldg(c4);
+        a_of[0] = a_of[1] = a_of[2] = a_of[3] = 0;
+#pragma unroll 4
         for (int a = 1; a < na; ++a) {
-          const float c = __ldg(cl + ((size_t)a * ns + i) * nd + d);
-          if (c > c_best) { c_best = c; a_best = a; }
+          const float4 c = __ldg(c4 + (size_t)a * ns);
+          if (c.x > cb.x) { cb.x = c.x; a_of[0] = a; }
+          if (c.y > cb.y) { cb.y = c.y; a_of[1] = a; }
+          if (c.z > cb.z) { cb.z = c.z; a_of[2] = a; }
+          if (c.w > cb.w) { cb.w = c.w; a_of[3] = a; }
         }
-        const size_t at = ((size_t)a_best * ns + i) * nd + d;
-        const float s = __ldg(sc + at);
-        if (d == 0 || s > best) {                                   // depth class: first maximum of the gathered scores
-          best = s;
-          const float w = __fmul_rn(1.2f, __ldg(wd + at));
-          g_width = fminf(fmaxf(w, 0.f), 0.1f);
-          g_score = __fdiv_rn(__fmul_rn(s, __ldg(tl + at)), 0.05f);
-          g_depth = __fmul_rn((float)(d + 1), 0.01f);
-          g_angle = __fmul_rn(__fdiv_rn((float)a_best, 12.f), 3.14159265358979323846f);
+      } else {
+        for (int d = 0; d < nd; ++d) {
+          // angle class of this depth: first maximum over the A class scores
+          int a_best = 0;
+          float c_best = __ldg(cl + ((size_t)0 * ns + i) * nd + d);
+          for (int a = 1; a < na; ++a) {
+            const float c = __ldg(cl + ((size_t)a * ns + i) * nd + d);
+            if (c > c_best) { c_best = c; a_best = a; }
+          }
+          a_of[d] = a_best;
         }
+      }
+      float s_of[MAXD];
+#pragma unroll
+      for (int d = 0; d < MAXD; ++d)
+        if (d < nd) s_of[d] = __ldg(sc + ((size_t)a_of[d] * ns + i) * nd + d);
+      int d_best = 0;
+#pragma unroll
+      for (int d = 1; d < MAXD; ++d)
+        if (d < nd && s_of[d] > s_of[d_best]) d_best = d;     // depth class: first maximum of the gathered scores
+      {
+        // (static indexing keeps a_of / s_of in registers)
+        int a_best = a_of[0];
+        best = s_of[0];
+#pragma unroll
+        for (int d = 1; d < MAXD; ++d)
+          if (d == d_best) { a_best = a_of[d]; best = s_of[d]; }
+        const size_t at = ((size_t)a_best * ns + i) * nd + d_best;
+        const float w = __fmul_rn(1.2f, __ldg(wd + at));
+        g_width = fminf(fmaxf(w, 0.f), 0.1f);
+        g_score = __fdiv_rn(__fmul_rn(best, __ldg(tl + at)), 0.05f);
+        g_depth = __fmul_rn((float)(d_best + 1), 0.01f);
+        g_angle = __fmul_rn(__fdiv_rn((float)a_best, 12.f), 3.14159265358979323846f);
       }
     }
     // order-preserving compaction: block exclusive scan of the keep flags
@@ -124,28 +153,56 @@ pred_decode_kernel(const float *__restrict__ objectness, const float *__restrict
 // The V directions (generate_grasp_views, utils/loss_utils.py:41-66) and their frames
 // (batch_viewpoint_params_to_matrix(-view, 0), :68-96) depend on V only: the caller computes both tables once and
 // this kernel looks them up -- the reference rebuilds the lattice in a Python loop and expands it to (B,S,V,3)
-// on every forward.  features is conv3's output [b, 2+V, s]; thread = seed, so every view row is read coalesced.
+// on every forward.  features is conv3's output [b, 2+V, s]; lanes = consecutive seeds, so every view row is read
+// coalesced.
+// A CTA is 32 seeds x 8 view slices: slice g scans the views g, g+8, ... (strict `>`, so the first maximum of its
+// own ascending sub-sequence), then the 8 candidates of a seed meet in shared memory (larger value, then lower index).
+// NaN is treated as the largest value and the first NaN wins (torch.max propagates it).
+__device__ __forceinline__ bool view_better(float v, int k, float bv, int bk) {
+  const bool vn = v != v, bn = bv != bv;
+  if (vn != bn) return vn;
+  if (!vn && v != bv) return v > bv;
+  return k < bk;
+}
+
 __global__ void __launch_bounds__(256)
 view_select_kernel(const float *__restrict__ features, const float *__restrict__ views,
                    const float *__restrict__ frames, int s, int v, long long *__restrict__ top_inds,
                    float *__restrict__ top_score, float *__restrict__ vp_xyz, float *__restrict__ vp_rot) {
-  const int scene = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= s) return;
-  const float *f = features + ((size_t)scene * (2 + v) + 2) * s + i;
-  int best = 0;
-  float bv = __ldg(f);
-  bool nan = bv != bv;
-  for (int k = 1; k < v && !nan; ++k) {
+  __shared__ float s_val[8][32];
+  __shared__ int s_idx[8][32];
+  const int scene = blockIdx.y, sx = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int i = blockIdx.x * 32 + sx;
+  const float *f = features + ((size_t)scene * (2 + v) + 2) * s + min(i, s - 1);
+  int best = g < v ? g : 0;
+  float bv = __ldg(f + (size_t)best * s);
+#pragma unroll 4
+  for (int k = g + 8; k < v; k += 8) {
     const float x = __ldg(f + (size_t)k * s);
-    if (x > bv || x != x) { bv = x; best = k; nan = x != x; }      // torch.max propagates the first NaN
+    if (view_better(x, k, bv, best)) { bv = x; best = k; }
   }
-  const size_t o = (size_t)scene * s + i;
-  top_inds[o] = best;
-  top_score[o] = bv;
+  s_val[g][sx] = bv;
+  s_idx[g][sx] = best;
+  __syncthreads();
+  if (g == 0 && i < s) {
 #pragma unroll
-  for (int c = 0; c < 3; ++c) vp_xyz[o * 3 + c] = __ldg(views + best * 3 + c);
-#pragma unroll
-  for (int c = 0; c < 9; ++c) vp_rot[o * 9 + c] = __ldg(frames + best * 9 + c);
+    for (int q = 1; q < 8; ++q)
+      if (view_better(s_val[q][sx], s_idx[q][sx], bv, best)) { bv = s_val[q][sx]; best = s_idx[q][sx]; }
+    s_idx[0][sx] = best;
+    const size_t o = (size_t)scene * s + i;
+    top_inds[o] = best;
+    top_score[o] = bv;
+  }
+  __syncthreads();
+  // the 12 table floats of each seed, written by all 256 threads
+  for (int e = threadIdx.x; e < 32 * 12; e += 256) {
+    const int q = e / 12, c = e % 12, ii = blockIdx.x * 32 + q;
+    if (ii >= s) break;
+    const int k = s_idx[0][q];
+    const size_t o = (size_t)scene * s + ii;
+    if (c < 3) vp_xyz[o * 3 + c] = __ldg(views + k * 3 + c);
+    else vp_rot[o * 9 + (c - 3)] = __ldg(frames + k * 9 + (c - 3));
+  }
 }
 
 // PointnetFPModule's interpolation weights (reference pointnet2/pointnet2_modules.py:394-397, after the sqrt of
@@ -180,8 +237,9 @@ extern "C" int b200_pred_decode(const float *objectness, const float *score, con
   if (!nrows) return B200_EINVAL;
   if (ns > 0 && (!objectness || !score || !angle_cls || !width || !tolerance || !xyz || !view_xyz || !rows))
     return B200_EINVAL;
+  const int vec4 = num_depth == 4 && (reinterpret_cast<uintptr_t>(angle_cls) & 15u) == 0;
   pred_decode_kernel<<<b, DT, 0, (cudaStream_t)stream>>>(objectness, score, angle_cls, width, tolerance, xyz, view_xyz,
-                                                        ns, num_angle, num_depth, rows, nrows);
+                                                        ns, num_angle, num_depth, vec4, rows, nrows);
   B200_LAUNCH_CHECK();
   return 0;
 }
@@ -192,7 +250,7 @@ extern "C" int b200_view_select(const float *features, const float *views, const
   if (b == 0 || s == 0) return 0;
   if (!features || !views || !frames || !top_inds || !top_score || !vp_xyz || !vp_rot) return B200_EINVAL;
   if (b > 65535) return B200_ECAPACITY;
-  view_select_kernel<<<dim3((s + 255) / 256, b), 256, 0, (cudaStream_t)stream>>>(features, views, frames, s, v,
+  view_select_kernel<<<dim3((s + 31) / 32, b), 256, 0, (cudaStream_t)stream>>>(features, views, frames, s, v,
                                                                                  top_inds, top_score, vp_xyz, vp_rot);
   B200_LAUNCH_CHECK();
   return 0;

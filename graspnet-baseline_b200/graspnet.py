@@ -10,9 +10,9 @@ Module classes, constructor arguments, forward signatures, end_points keys and s
   GraspNetStage1/2, GraspNet   models/graspnet.py:26-75 (view_estimator.{backbone,vpmodule},
                                                          grasp_generator.{crop,operation,tolerance})
 so a reference checkpoint loads with load_state_dict unchanged.  The geometry (FPS, queries, grouping, three_nn,
-interpolation, view selection, decode, collision, NMS) and the grouped shared MLPs are this library's kernels; the
-plain 1x1 convolutions over point columns (FP modules, ApproachNet, heads) are fp32 library GEMMs (cuBLAS through
-torch.addmm) with eval-mode BatchNorm folded into the weights.
+interpolation, view selection, decode, collision, NMS), the grouped shared MLPs (tcgen05) and the 1x1 convolutions
+over point columns (FP modules, ApproachNet, heads: csrc/pointwise.cu, eval-mode BatchNorm folded into the weights,
+bias + ReLU in the epilogue) are this library's kernels; torch only holds the memory.
 
 In eval mode without autograd every module takes its fast path; with `fused_modules.FUSED = False` (or in training
 mode) it runs the reference's own op sequence on the drop-in ops -- the "composed" path the fast one is tested
@@ -43,13 +43,10 @@ def _fast(module):
     return fm.FUSED and not module.training and not torch.is_grad_enabled()
 
 
-def _pointwise(x, w, b, relu=True):
-    """1x1 convolution over point columns: x (B,C,n) -> [relu](w x + b) (B,Cout,n); fp32 GEMM, bias in the epilogue"""
-    if x.shape[0] == 1:
-        y = torch.addmm(b[:, None], w, x[0]).unsqueeze(0)
-    else:
-        y = torch.baddbmm(b[None, :, None], w.unsqueeze(0).expand(x.shape[0], -1, -1), x)
-    return y.relu_() if relu else y
+def _pointwise(x, w, b, relu=True, x2=None):
+    """1x1 convolution over point columns: x (B,C,n) [| x2 along channels] -> [relu](w x + b) (B,Cout,n), one launch
+    (csrc/pointwise.cu: exact fp32 FMAs, bias and ReLU in the epilogue)"""
+    return ops.pointwise_conv(x.contiguous(), w, b, relu=relu, x2=None if x2 is None else x2.contiguous())
 
 
 class _Folded:
@@ -119,11 +116,12 @@ class PointnetFPModule(nn.Module):
             dist_recip = 1.0 / (dist + 1e-8)
             weight = dist_recip / torch.sum(dist_recip, dim=2, keepdim=True)
             interpolated = pointnet2_utils.three_interpolate(known_feats, idx, weight)
-        x = torch.cat([interpolated, unknow_feats], dim=1) if unknow_feats is not None else interpolated
         if _fast(self):
+            x, skip = interpolated, unknow_feats             # the concatenation happens inside the first layer
             for w, b in self._folded.get():
-                x = _pointwise(x, w, b)
+                x, skip = _pointwise(x, w, b, x2=skip), None
             return x
+        x = torch.cat([interpolated, unknow_feats], dim=1) if unknow_feats is not None else interpolated
         return self.mlp(x.unsqueeze(-1)).squeeze(-1)
 
 

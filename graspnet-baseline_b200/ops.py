@@ -333,6 +333,29 @@ def three_nn(unknowns, knows):
     return dist2, idx
 
 
+def pointwise_conv(x, w, b, relu=True, x2=None):
+    """1x1 convolution over point columns: x (B,C1,n) [concatenated with x2 (B,C2,n) along channels], w (Cout,C1+C2),
+    b (Cout) -> [relu](w x + b) (B,Cout,n); bias / folded BatchNorm and ReLU in the kernel's epilogue, one launch"""
+    _chk(x, "x", torch.float32)
+    _chk(w, "w", torch.float32)
+    _chk(b, "b", torch.float32)
+    bsz, c1, n = x.shape
+    c2 = 0
+    if x2 is not None:
+        _chk(x2, "x2", torch.float32)
+        if x2.shape[0] != bsz or x2.shape[2] != n:
+            raise ValueError("b200grasp: x and x2 must agree in batch and columns")
+        c2 = x2.shape[1]
+    cout = w.shape[0]
+    if w.shape[1] != c1 + c2 or b.numel() != cout:
+        raise ValueError("b200grasp: weight (%d,%d) does not match %d input channels" % (cout, w.shape[1], c1 + c2))
+    y = torch.empty((bsz, cout, n), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _abi.check(_lib.b200_pointwise_conv(_ptr(w), _ptr(b), _ptr(x), c1, _ptr(x2) if x2 is not None else None, c2,
+                                            bsz, n, cout, 1 if relu else 0, _ptr(y), _stream()), "pointwise_conv")
+    return y
+
+
 def three_nn_weights(dist2):
     """dist2 (B,n,3) from three_nn -> inverse-distance weights (B,n,3) = (1/(sqrt(dist2)+1e-8)) / sum
     [pointnet2_modules.py:394-397 after the sqrt of pointnet2_utils.py:140], one launch"""

@@ -139,6 +139,14 @@ int b200_pred_decode(const float *objectness, const float *score, const float *a
                      const float *tolerance, const float *xyz, const float *view_xyz, int b, int ns,
                      int num_angle, int num_depth, float *rows, int32_t *nrows, void *stream);
 
+/* 1x1 convolution over point columns with the bias (eval-mode BatchNorm folded in) and optional ReLU in the epilogue:
+ *   y[b,co,j] = act(bias[co] + sum_ci w[co,ci] * x[b,ci,j]),  x = the channel concatenation [x1 (c1 rows) | x2 (c2 rows)]
+ * (x2 may be NULL with c2 = 0).  One launch per layer of PointnetFPModule's SharedMLP (pointnet2_modules.py:403-414,
+ * pytorch_utils.py:11-36), ApproachNet (models/modules.py:52-57), OperationNet / ToleranceNet (:170-177, :215-222).
+ * w [cout, c1+c2], bias [cout], x1 [b,c1,n], x2 [b,c2,n], y [b,cout,n]; all fp32, exact fp32 FMAs. */
+int b200_pointwise_conv(const float *w, const float *bias, const float *x1, int c1, const float *x2, int c2, int b,
+                        int n, int cout, int relu, float *y, void *stream);
+
 /* ApproachNet's tail (models/modules.py:60-73): features [b,2+v,s] fp32 (conv3's output) -> per seed the first
  * maximum over the v view scores: top_inds [b,s] i64, top_score [b,s], vp_xyz [b,s,3] = views[top], vp_rot [b,s,9] =
  * frames[top].  views [v,3] = generate_grasp_views(v) (utils/loss_utils.py:41-66) and frames [v,9] =

@@ -147,3 +147,48 @@ def test_engine_graph_equals_call_sequence(b200, batch):
     for s in range(batch):
         assert r3[s]["nrows"] == rows2[s].shape[0]
     assert eng.launches > 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("b,c1,c2,n,cout,relu", [(1, 256, 256, 512, 256, True), (2, 256, 0, 1024, 302, True),
+                                                  (1, 302, 0, 1024, 302, False), (3, 128, 0, 4096, 36, False),
+                                                  (1, 7, 5, 33, 3, True), (2, 16, 0, 5, 70, False)])
+def test_pointwise_conv_matches_fp64_statement(b200, b, c1, c2, n, cout, relu):
+    """csrc/pointwise.cu: y = [relu](w [x1 | x2] + bias) against the same product in fp64 (1e-6 of the scale)"""
+    g = torch.Generator().manual_seed(b * 1000 + cout)
+    x1 = torch.randn(b, c1, n, generator=g)
+    x2 = torch.randn(b, c2, n, generator=g) if c2 else None
+    w = torch.randn(cout, c1 + c2, generator=g) / (c1 + c2) ** 0.5
+    bias = torch.randn(cout, generator=g)
+    x = torch.cat([x1, x2], 1) if c2 else x1
+    want = torch.matmul(w.double(), x.double()) + bias.double()[None, :, None]
+    if relu:
+        want = want.clamp_min(0)
+    got = b200.ops.pointwise_conv(x1.cuda(), w.cuda(), bias.cuda(), relu=relu, x2=None if x2 is None else x2.cuda())
+    assert got.shape == (b, cout, n)
+    close(got.cpu().numpy(), want.numpy(), 1e-6, what="pointwise_conv %s" % ((b, c1, c2, n, cout),))
+
+
+@pytest.mark.gpu
+def test_view_select_is_torch_max_plus_the_reference_frames(b200):
+    """first maximum over the view scores (ties, NaN) + table lookup == torch.max + the reference construction"""
+    g = torch.Generator().manual_seed(5)
+    B, S, V = 2, 1000, 300
+    f = torch.randn(B, 2 + V, S, generator=g)
+    f[:, 2:, ::7] = torch.round(f[:, 2:, ::7])              # exact ties between views
+    f[0, 40, 3] = float("nan")
+    f[0, 90, 3] = float("nan")
+    f[1, 2:, 11] = 0.5                                       # every view equal
+    vp = b200.graspnet.ApproachNet(V, 256)
+    views, frames = vp.tables(torch.device("cuda"))
+    inds, score, xyz, rot = b200.ops.view_select(f.cuda(), views, frames)
+    want_score, want_inds = torch.max(f[:, 2:].transpose(1, 2).contiguous().cuda(), dim=2)
+    nan = torch.isnan(want_score)
+    assert torch.equal(inds[~nan], want_inds[~nan]) and torch.equal(score[~nan], want_score[~nan])
+    assert int(inds[0, 3]) == 38 and torch.isnan(score[0, 3])           # the FIRST NaN (view 40 - 2)
+    assert int(inds[1, 11]) == 0
+    want_xyz = views[inds]
+    angle = torch.zeros(B * S, device="cuda")
+    want_rot = b200.graspnet.view_frames(-want_xyz.view(-1, 3), angle).view(B, S, 3, 3)
+    assert torch.equal(xyz, want_xyz)
+    assert (rot - want_rot).abs().max() <= 1e-6
