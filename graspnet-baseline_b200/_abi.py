@@ -48,7 +48,7 @@ SIGNATURES = {
     "b200_mlp_pack_weights": [_vp, _i, _i, _vp, _vp],
     "b200_gather_xyz": [_vp, _vp, _i, _i, _i, _vp, _vp, _vp],
     "b200_pred_decode": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp],
-    "b200_pointwise_conv": [_vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _vp, _vp],
+    "b200_pointwise_conv": [_vp, _i, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _vp, _vp],
     "b200_view_select": [_vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp],
     "b200_three_nn_weights": [_vp, _i, _vp, _vp, _vp],
     "b200_ball_query_grid": [_vp, _vp, _i, _i, _i, _f, _i, _vp, _vp, _sz, _vp],

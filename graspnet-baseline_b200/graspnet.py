@@ -61,7 +61,7 @@ class _Folded:
         key = tuple((t.data_ptr(), t._version) for t in tensors)
         if key != self.key:
             with torch.no_grad():
-                self.layers = [(w.contiguous(), b.contiguous()) for w, b in self.build()]
+                self.layers = [(ops.pad_weight(w), b.contiguous()) for w, b in self.build()]
             self.key = key
         return self.layers
 
@@ -335,7 +335,8 @@ class GraspNetEngine:
 
     Streams inside the graph: the SA1 sampling chain runs on the main stream while the grid binning and the voxel
     down-sample of the cloud run beside it; once SA1's samples exist, the samples / neighbour lists / three-nearest
-    searches of SA2..SA4 and FP1..FP2 (coordinates only) run on a side stream under SA1's grouped MLP."""
+    searches of SA2..SA4 and FP1..FP2 (coordinates only) run on a side stream under SA1's grouped MLP; the two
+    grasp heads run side by side."""
 
     def __init__(self, net, batch=1, num_point=20000, device="cuda", post=None):
         self.net, self.B, self.N = net.eval(), batch, num_point
@@ -386,10 +387,11 @@ class GraspNetEngine:
                                "fused_modules.FUSED)")
         main = torch.cuda.current_stream()
         if self._streams is None:
-            self._streams = [torch.cuda.Stream(device=dev) for _ in range(6 + min(B, 16))]
+            self._streams = [torch.cuda.Stream(device=dev) for _ in range(7 + min(B, 16))]
         s_grid, s_vox, s_q = self._streams[0:3]
         s_chk = self._streams[3:6]
-        s_post = self._streams[6:]
+        s_head = self._streams[6]
+        s_post = self._streams[7:]
         hold = []
         ep = {'point_clouds': self.cloud, 'input_xyz': self.cloud, 'input_features': None}
         cloud = self.cloud
@@ -442,7 +444,13 @@ class GraspNetEngine:
         ep['fp2_features'], ep['fp2_xyz'] = f, xyzs[1]
         ep['fp2_inds'] = inds[0][:, 0:xyzs[1].shape[1]]
         ep = vp(xyzs[1], f, ep)
-        ep = gen(ep, grid=grid)
+        vp_features = gen.crop(xyzs[1], cloud, ep['grasp_top_view_rot'], grid=grid)
+        s_head.wait_stream(main)
+        with torch.cuda.stream(s_head):                # the two heads read the same crop features
+            ep = gen.tolerance(vp_features, ep)
+        ep = gen.operation(vp_features, ep)
+        main.wait_stream(s_head)
+        hold.append(vp_features)
         rows, nrows = ops.pred_decode(*[ep[k].float().contiguous() for k in
                                         ("objectness_score", "grasp_score_pred", "grasp_angle_cls_pred",
                                          "grasp_width_pred", "grasp_tolerance_pred", "fp2_xyz", "grasp_top_view_xyz")])

@@ -334,8 +334,9 @@ def three_nn(unknowns, knows):
 
 
 def pointwise_conv(x, w, b, relu=True, x2=None):
-    """1x1 convolution over point columns: x (B,C1,n) [concatenated with x2 (B,C2,n) along channels], w (Cout,C1+C2),
-    b (Cout) -> [relu](w x + b) (B,Cout,n); bias / folded BatchNorm and ReLU in the kernel's epilogue, one launch"""
+    """1x1 convolution over point columns: x (B,C1,n) [concatenated with x2 (B,C2,n) along channels], w (Cout,C1+C2)
+    -- or (Cout, C1+C2 rounded up to a multiple of 4) with ZERO padding columns, which takes the 16-byte copy path
+    (pad_weight) --, b (Cout) -> [relu](w x + b) (B,Cout,n); bias / folded BatchNorm and ReLU in the epilogue"""
     _chk(x, "x", torch.float32)
     _chk(w, "w", torch.float32)
     _chk(b, "b", torch.float32)
@@ -346,14 +347,20 @@ def pointwise_conv(x, w, b, relu=True, x2=None):
         if x2.shape[0] != bsz or x2.shape[2] != n:
             raise ValueError("b200grasp: x and x2 must agree in batch and columns")
         c2 = x2.shape[1]
-    cout = w.shape[0]
-    if w.shape[1] != c1 + c2 or b.numel() != cout:
-        raise ValueError("b200grasp: weight (%d,%d) does not match %d input channels" % (cout, w.shape[1], c1 + c2))
+    cout, ldw = w.shape
+    if not c1 + c2 <= ldw < c1 + c2 + 4 or b.numel() != cout:
+        raise ValueError("b200grasp: weight (%d,%d) does not match %d input channels" % (cout, ldw, c1 + c2))
     y = torch.empty((bsz, cout, n), dtype=torch.float32, device=x.device)
     with torch.cuda.device(x.device):
-        _abi.check(_lib.b200_pointwise_conv(_ptr(w), _ptr(b), _ptr(x), c1, _ptr(x2) if x2 is not None else None, c2,
+        _abi.check(_lib.b200_pointwise_conv(_ptr(w), ldw, _ptr(b), _ptr(x), c1, _ptr(x2) if x2 is not None else None, c2,
                                             bsz, n, cout, 1 if relu else 0, _ptr(y), _stream()), "pointwise_conv")
     return y
+
+
+def pad_weight(w):
+    """(Cout,Cin) -> (Cout, Cin rounded up to a multiple of 4), zero-padded, contiguous (see pointwise_conv)"""
+    pad = (-w.shape[1]) % 4
+    return torch.nn.functional.pad(w, (0, pad)).contiguous() if pad else w.contiguous()
 
 
 def three_nn_weights(dist2):

@@ -143,9 +143,10 @@ int b200_pred_decode(const float *objectness, const float *score, const float *a
  *   y[b,co,j] = act(bias[co] + sum_ci w[co,ci] * x[b,ci,j]),  x = the channel concatenation [x1 (c1 rows) | x2 (c2 rows)]
  * (x2 may be NULL with c2 = 0).  One launch per layer of PointnetFPModule's SharedMLP (pointnet2_modules.py:403-414,
  * pytorch_utils.py:11-36), ApproachNet (models/modules.py:52-57), OperationNet / ToleranceNet (:170-177, :215-222).
- * w [cout, c1+c2], bias [cout], x1 [b,c1,n], x2 [b,c2,n], y [b,cout,n]; all fp32, exact fp32 FMAs. */
-int b200_pointwise_conv(const float *w, const float *bias, const float *x1, int c1, const float *x2, int c2, int b,
-                        int n, int cout, int relu, float *y, void *stream);
+ * w [cout, ldw] with ldw >= c1+c2 the row stride (columns c1+c2..ldw-1 must be ZERO: rows padded to a multiple of 4
+ * floats take the 16-byte cp.async path), bias [cout], x1 [b,c1,n], x2 [b,c2,n], y [b,cout,n]; fp32, exact FMAs. */
+int b200_pointwise_conv(const float *w, int ldw, const float *bias, const float *x1, int c1, const float *x2, int c2,
+                        int b, int n, int cout, int relu, float *y, void *stream);
 
 /* ApproachNet's tail (models/modules.py:60-73): features [b,2+v,s] fp32 (conv3's output) -> per seed the first
  * maximum over the v view scores: top_inds [b,s] i64, top_score [b,s], vp_xyz [b,s,3] = views[top], vp_rot [b,s,9] =
