@@ -40,6 +40,8 @@ UNIT = "scenes/s"
 WORKLOAD = ("cfg2: GraspNet inference (seeded random weights, eval), batch 1, 20000 pts -> SA 2048/1024/512/256 -> "
             "1024 seeds, 300 views / 12 angles / 4 depths, pred_decode, collision (voxel 0.01, approach 0.05, "
             "thresh 0.01) of the decoded grasps + NMS")
+PIPE_DEPTH = 8            # scenes in flight (tools/pipe_probe.py: 1 -> 1075, 2 -> 1689, 4 -> 2232, 8 -> 2631 scenes/s)
+POOL = 640                # different clouds the timed stream rotates through (640 x 240 kB = 154 MB > L2)
 WEIGHT_SEED = 12          # synth.fill_state_dict seed: every seed passes the objectness test -> 1024 grasps per scene
 SA_CFG = [(2048, 0.04, 64, 0), (1024, 0.1, 32, 128), (512, 0.2, 16, 256), (256, 0.3, 16, 256)]
 HMAX = [0.01, 0.02, 0.03, 0.04]
@@ -457,12 +459,39 @@ def run_ours(args, rank, world, local_rank):
     except Exception:
         uuid = None
     clocks = Clocks(local_rank, uuid)
-    for _ in range(args.warmup):
-        eng.run_graph()
+    # ---- the headline: a stream of scenes through GraspNetPipeline (PIPE_DEPTH scenes in flight, each its own
+    # batch-1 graph on its own stream).  Inputs rotate through a pool of POOL different clouds = 154 MB > 126 MB L2,
+    # resident in HBM; the timed region is ONE pair of events around exactly `steps` scenes.
+    pipe = graspnet.GraspNetPipeline(net, depth=PIPE_DEPTH, num_point=20000, device=dev)
+    pool_host = [scene_cloud(100000 * (rank + 1) + i) for i in range(POOL)]
+    pool_host[0] = cloud_host
+    pool = torch.from_numpy(np.stack(pool_host)).to(dev)
+
+    def timed_stream(run, steps, warmup):
+        run(warmup, 0)
+        barrier()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record(stream)
+        run(steps, warmup)
+        pipe.join()
+        t1.record(stream)
+        barrier()
+        return b200grasp.sharding.whole_job_throughput(steps, t0.elapsed_time(t1), device=dev)[1]
+
+    def resident_stream(count, first):
+        for i in range(first, first + count):
+            pipe.submit(device_cloud=pool[i % POOL], readback=False)
+
+    def host_stream(count, first):                          # e2e: host cloud in, host results out, every scene
+        return pipe.run(pool_host[i % POOL] for i in range(first, first + count))
+
     clocks.start()                                          # samples only while the timed region below runs
-    total_ms = timed(eng.run_graph, args.steps, args.warmup)
+    total_ms = timed_stream(resident_stream, args.steps, max(args.warmup, PIPE_DEPTH))
     clk = clocks.summary()
-    launches = eng.launches                                 # our kernels per step (library counter at capture)
+    launches = pipe.launches                                # our kernels per scene (library counter at capture)
+    e2e_ms = timed_stream(host_stream, args.steps, max(args.warmup, PIPE_DEPTH))
+    lat_ms = timed(eng.run_graph, min(args.steps, 50), args.warmup) / min(args.steps, 50)   # one scene alone, L2 flushed
+    lat_e2e_ms = timed(lambda: eng.infer(None), min(args.steps, 50), args.warmup) / min(args.steps, 50)
 
     def call_sequence():
         """the same scene as the reference's scripts run it (test.py:86-96): net(), pred_decode, detector, nms called
@@ -475,11 +504,10 @@ def run_ours(args, rank, world, local_rank):
         mask = det.detect(gg, approach_dist=0.05, collision_thresh=0.01)
         return gg, mask, gg[~mask].nms(device=dev)
 
-    seq_ms = timed(call_sequence, args.steps, args.warmup)
-    # ---- e2e: host cloud in, host results out, every step, through the engine's public call
+    seq_steps = min(args.steps, 20)
+    seq_ms = timed(call_sequence, seq_steps, args.warmup) / seq_steps
     h2d, d2h = eng.host_in.numel(), eng.host_out.numel()
-    e2e_ms = timed(lambda: eng.infer(None), args.steps, args.warmup)
-    got = eng.infer(None)[0]
+    got = host_stream(1, 0)[0]                              # pool_host[0] is the engine's cloud
     gg, mask, kept = call_sequence()
     if not (got["nrows"] == len(gg) and np.array_equal(got["mask"], mask)
             and np.array_equal(got["kept"], kept.grasp_group_array)):
@@ -488,9 +516,10 @@ def run_ours(args, rank, world, local_rank):
                     "kept_after_nms": int(got["kept"].shape[0])}
 
     # ================= geometry ops alone (pipeline.GeometryScene: stand-in features instead of the MLPs)
-    geo_total_ms = timed(sc.run_graph, args.steps, args.warmup)
+    gsteps = min(args.steps, 20)
+    geo_total_ms = timed(sc.run_graph, gsteps, args.warmup)
     geo_launches = sc.launches
-    serial_ms = timed(sc.run, args.steps, args.warmup)      # same ops, one stream, eager launches
+    serial_ms = timed(sc.run, gsteps, args.warmup)          # same ops, one stream, eager launches
     sc.glue = 0
     sc.run()
     glue = sc.glue
@@ -511,7 +540,7 @@ def run_ours(args, rank, world, local_rank):
         torch.cuda.current_stream().synchronize()           # the caller reads the results now
         return res["kept0"][: int(res["nkept0"][0])], res["mask0"]
 
-    geo_e2e_ms = timed(e2e_step, args.steps, args.warmup)
+    geo_e2e_ms = timed(e2e_step, gsteps, args.warmup)
 
     # the same scene through the numpy-in / numpy-out drop-ins, called one after the other as test.py:94-96 does
     # (detector rebuilt per scene), on a second stream beside the geometry graph: reported for comparison
@@ -531,7 +560,7 @@ def run_ours(args, rank, world, local_rank):
         out["sa2_inds"].cpu()
         return kept, mask
 
-    dropin_ms = timed(dropin_step, args.steps, args.warmup)
+    dropin_ms = timed(dropin_step, gsteps, args.warmup)
     got_k, got_m = e2e_step()
     ref_k, ref_m = dropin_step()
     if not (np.array_equal(got_m.numpy().astype(bool), ref_m) and np.array_equal(got_k.numpy(), ref_k.grasp_group_array)):
@@ -545,7 +574,7 @@ def run_ours(args, rank, world, local_rank):
     if ext is not None:
         lsteps = max(3, min(args.steps, 10))
         leg_ms = timed(lambda: legacy_step(ext, sc, torch), lsteps, 3) / lsteps
-        geo_ms = timed(lambda: sc.run_graph(post=False), args.steps, args.warmup) / args.steps
+        geo_ms = timed(lambda: sc.run_graph(post=False), gsteps, args.warmup) / gsteps
         legacy = {"what": "reference pointnet2._ext (votenet-derived kernels, built unmodified for sm_100) on the same B200: "
                           "FPS, gather, ball query, grouping, three_nn, three_interpolate, 4x cylinder query of one cfg2 scene",
                   "legacy_geometry_ms_per_scene": round(leg_ms, 4), "ours_geometry_ms_per_scene": round(geo_ms, 4),
@@ -569,13 +598,14 @@ def run_ours(args, rank, world, local_rank):
             with torch.no_grad():
                 return net({"point_clouds": eng.cloud})
 
-        ourf_ms = timed(our_forward, args.steps, args.warmup) / args.steps
+        ourf_ms = timed(our_forward, gsteps, args.warmup) / gsteps
         legacy.update({"forward_what": "GraspNet forward (no decode / collision / NMS): reference op sequence with its "
                                        "own pointnet2._ext + torch/cuDNN layers, eager  vs  this package's forward "
                                        "(eager, one stream) and the engine graph (whole step incl. post-processing)",
                        "legacy_forward_ms": round(legf_ms, 4), "ours_forward_eager_ms": round(ourf_ms, 4),
-                       "ours_whole_step_graph_ms": round(total_ms / args.steps, 4),
-                       "forward_speedup_vs_graph_step": round(legf_ms / (total_ms / args.steps), 2)})
+                       "ours_whole_step_graph_latency_ms": round(lat_ms, 4),
+                       "ours_whole_step_stream_ms_per_scene": round(total_ms / args.steps, 4),
+                       "forward_speedup_vs_graph_latency": round(legf_ms / lat_ms, 2)})
     # ---- config 3 shape: 64 scenes per graph launch on this GPU (throughput mode; extra, not the headline)
     batch64 = None
     if world == 1 and not args.no_batch64:
@@ -659,19 +689,25 @@ def run_ours(args, rank, world, local_rank):
             "warmup": args.warmup, "ms_per_step": round(total_ms / args.steps, 4), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32 (fp64 collision/NMS, int32 indices)",
             "data": "synthetic",
-            "config": {"workload": WORKLOAD, "scenes_per_step_per_gpu": 1, "l2": "flushed between timed iterations "
-                       "(512 MiB write)", "weights": "synth.fill_state_dict(seed %d), eval-mode BatchNorm" % WEIGHT_SEED,
-                       "grouped_mlp_arithmetic": "3xTF32 on tcgen05 (fp32-grade); other layers fp32 cuBLAS GEMMs",
-                       "execution": "one CUDA graph per scene (GraspNetEngine), forked over streams by data dependence",
+            "config": {"workload": WORKLOAD, "scenes_per_step_per_gpu": 1, "weights": "synth.fill_state_dict(seed %d), eval-mode BatchNorm" % WEIGHT_SEED,
+                       "grouped_mlp_arithmetic": "3xTF32 on tcgen05 (fp32-grade); the other layers exact fp32 FMAs (csrc/pointwise.cu)",
+                       "execution": "GraspNetPipeline: %d scenes in flight, each a batch-1 CUDA graph (GraspNetEngine, "
+                                    "forked over streams by data dependence) on its own stream" % PIPE_DEPTH,
+                       "l2": "inputs rotate through a pool of %d different clouds (%d MB > 126 MB L2) resident in HBM; "
+                             "the latency / per-kernel legs flush L2 (512 MiB write) between iterations" %
+                             (POOL, POOL * 240000 // 1000000),
+                       "single_scene_latency_ms": round(lat_ms, 4),
+                       "single_scene_latency_e2e_ms": round(lat_e2e_ms, 4),
                        "scene": infer_counts},
             "clocks": clk, "gpu_launches": launches * args.steps,
             "e2e": {"value": round(e2e, 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": round(e2e_ms / args.steps, 4),
-                    "api": "GraspNetEngine.infer(): the cloud in pinned host memory copied into the graph's static "
-                           "input, one graph launch (network + pred_decode + voxel + collision + NMS on the device), "
-                           "one copy of the results (decoded count | mask | kept rows | kept count) to pinned host "
-                           "memory, stream synchronised, numpy views returned",
-                    "call_sequence_ms_per_step": round(seq_ms / args.steps, 4),
+                    "api": "GraspNetPipeline.run(clouds): per scene the host cloud is copied into a pinned buffer and from "
+                           "there into the slot's static input, one graph launch (network + pred_decode + voxel + "
+                           "collision + NMS on the device), one copy of the results (decoded count | mask | kept rows | "
+                           "kept count) to pinned host memory, numpy results returned in order; %d scenes in flight" %
+                           PIPE_DEPTH,
+                    "call_sequence_ms_per_step": round(seq_ms, 4),
                     "call_sequence": "net(end_points), pred_decode, GraspGroup, ModelFreeCollisionDetector(...).detect, "
                                      ".nms() through the drop-ins, one after the other as test.py:86-96 (eager, "
                                      "numpy round trips); results equal the engine's (checked in this run)"},
@@ -679,13 +715,13 @@ def run_ours(args, rank, world, local_rank):
             "inference_ops": infer_ops,
             "geometry_path": {"what": "the geometry ops + post-processing alone (pipeline.GeometryScene: stand-in "
                                       "features instead of the MLPs, 1024 synthetic grasps), one graph per scene",
-                              "scenes_per_s": round(world * args.steps / (geo_total_ms * 1e-3), 2),
-                              "ms_per_step": round(geo_total_ms / args.steps, 4),
+                              "scenes_per_s": round(world * gsteps / (geo_total_ms * 1e-3), 2),
+                              "ms_per_step": round(geo_total_ms / gsteps, 4),
                               "gpu_launches_per_step": geo_launches, "glue_torch_launches_per_step": glue,
-                              "single_stream_eager_ms_per_step": round(serial_ms / args.steps, 4),
-                              "e2e_scenes_per_s": round(world * args.steps / (geo_e2e_ms * 1e-3), 2),
+                              "single_stream_eager_ms_per_step": round(serial_ms / gsteps, 4),
+                              "e2e_scenes_per_s": round(world * gsteps / (geo_e2e_ms * 1e-3), 2),
                               "e2e_h2d_bytes": int(geo_h2d), "e2e_d2h_bytes": int(geo_d2h),
-                              "dropin_calls_ms_per_step": round(dropin_ms / args.steps, 4)},
+                              "dropin_calls_ms_per_step": round(dropin_ms / gsteps, 4)},
             "kernels": kern}
     return line
 
@@ -693,8 +729,8 @@ def run_ours(args, rank, world, local_rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=400)
+    ap.add_argument("--warmup", type=int, default=16)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-batch64", action="store_true")
@@ -707,7 +743,8 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return 0
-        sps, sec, _ = time_cpu(args.steps, args.warmup)
+        args.steps = min(args.steps, 40)                    # bounded sample: a scene takes ~0.3-1 s on the host cores
+        sps, sec, _ = time_cpu(args.steps, min(args.warmup, 2))
         cores = os.cpu_count()
         cb = {"value": round(sps, 4), "unit": UNIT, "cores": cores, "kind": "port",
               "sample": "%d whole scenes of the cfg2 workload: the network's reference op sequence with the pointnet2 ops "

@@ -518,5 +518,79 @@ class GraspNetEngine:
         for s in range(self.B):
             k = int(v["nkept%d" % s][0])
             n = int(v["nrows%d" % s][0])
-            res.append(dict(nrows=n, mask=v["mask%d" % s][:n].numpy().astype(bool), kept=v["kept%d" % s][:k].numpy()))
+            res.append(dict(nrows=n, mask=v["mask%d" % s][:n].numpy().astype(bool),
+                            kept=v["kept%d" % s][:k].numpy().copy()))       # copies: host_out is reused by the next call
         return res
+
+
+class GraspNetPipeline:
+    """A stream of single scenes through `depth` engines (each with its own static buffers and graph), fed
+    round-robin on their own CUDA streams.  One scene cannot fill the GPU -- its SA1 sampling chain is a serial chain on
+    one cluster (16 of 148 SMs) and is 40 % of the scene's latency -- so scene i+1's chain runs under scene i's
+    grouped MLPs, heads and post-processing.  Results are the engine's, scene by scene (each scene is still a
+    batch-1 forward; nothing is shared between scenes but the weights).
+
+        slot = pipe.submit(cloud)      # (N,3) float32 numpy / CPU tensor; returns at once
+        ...                            # up to `depth` scenes in flight
+        res = pipe.collect(slot)       # dict(nrows, mask, kept) of that scene (waits for it)
+    """
+
+    def __init__(self, net, depth=2, num_point=20000, device="cuda", post=None):
+        self.dev = torch.device(device)
+        self.engines = [GraspNetEngine(net, batch=1, num_point=num_point, device=device, post=post)
+                        for _ in range(depth)]
+        for eng in self.engines:
+            eng.run_graph()                             # capture now (capturing synchronises)
+        torch.cuda.synchronize(self.dev)
+        self.streams = [torch.cuda.Stream(device=self.dev) for _ in range(depth)]
+        self.done = [None] * depth
+        self.k = 0
+
+    @property
+    def launches(self):
+        return self.engines[0].launches
+
+    def submit(self, cloud=None, device_cloud=None, readback=True):
+        """queue one scene on the next slot (whose previous scene must have been collected): `cloud` from the host
+        (copied through the slot's pinned buffer), or `device_cloud` (N,3) already in HBM"""
+        k = self.k % len(self.engines)
+        self.k += 1
+        eng, st = self.engines[k], self.streams[k]
+        if cloud is not None:
+            eng.views(eng.host_in, "in")["cloud"][0].copy_(torch.as_tensor(cloud))
+        st.wait_stream(torch.cuda.current_stream(self.dev))
+        with torch.cuda.stream(st):
+            if device_cloud is not None:
+                eng.cloud[0].copy_(device_cloud, non_blocking=True)
+            else:
+                eng.io_in.copy_(eng.host_in, non_blocking=True)
+            eng.run_graph()
+            if readback:
+                eng.host_out.copy_(eng.io_out, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(st)
+        self.done[k] = ev
+        return k
+
+    def collect(self, k):
+        self.done[k].synchronize()
+        eng = self.engines[k]
+        v = eng.views(eng.host_out, "out")
+        n, kk = int(v["nrows0"][0]), int(v["nkept0"][0])
+        return dict(nrows=n, mask=v["mask0"][:n].numpy().astype(bool), kept=v["kept0"][:kk].numpy().copy())
+
+    def join(self):
+        """the caller's stream waits for everything submitted so far"""
+        cur = torch.cuda.current_stream(self.dev)
+        for st in self.streams:
+            cur.wait_stream(st)
+
+    def run(self, clouds):
+        """clouds: iterable of (N,3) arrays -> list of result dicts, in order"""
+        out, pending = [], []
+        for c in clouds:
+            if len(pending) == len(self.engines):
+                out.append(self.collect(pending.pop(0)))
+            pending.append(self.submit(c))
+        out += [self.collect(k) for k in pending]
+        return out

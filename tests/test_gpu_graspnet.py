@@ -192,3 +192,21 @@ def test_view_select_is_torch_max_plus_the_reference_frames(b200):
     want_rot = b200.graspnet.view_frames(-want_xyz.view(-1, 3), angle).view(B, S, 3, 3)
     assert torch.equal(xyz, want_xyz)
     assert (rot - want_rot).abs().max() <= 1e-6
+
+
+@pytest.mark.gpu
+def test_pipeline_of_scenes_equals_one_scene_at_a_time(b200):
+    """GraspNetPipeline (several scenes in flight on their own streams / graphs) returns, scene by scene, exactly
+    what a single engine returns for that scene alone"""
+    net = _net(b200, 72).cuda().eval()
+    n = 6000
+    clouds = [b200.synth.tabletop_cloud(n, 60 + s) for s in range(7)]
+    eng = b200.graspnet.GraspNetEngine(net, batch=1, num_point=n)
+    want = [eng.infer(c[None])[0] for c in clouds]
+    pipe = b200.graspnet.GraspNetPipeline(net, depth=3, num_point=n)
+    for _ in range(2):
+        got = pipe.run(clouds)
+        assert len(got) == len(want)
+        for g, w in zip(got, want):
+            assert g["nrows"] == w["nrows"] and (g["mask"] == w["mask"]).all()
+            assert g["kept"].shape == w["kept"].shape and (g["kept"] == w["kept"]).all()
