@@ -489,6 +489,14 @@ def run_ours(args, rank, world, local_rank):
     total_ms = timed_stream(resident_stream, args.steps, max(args.warmup, PIPE_DEPTH))
     clk = clocks.summary()
     launches = pipe.launches                                # our kernels per scene (library counter at capture)
+    # the resident stream really processed the pool's clouds: a slot fed from HBM returns what the same cloud fed
+    # from the host returns
+    chk = [pipe.collect(pipe.submit(device_cloud=pool[i], readback=True)) for i in (1, 2, 3)]
+    ref = host_stream(3, 1)
+    for a, b in zip(chk, ref):
+        if not (a["nrows"] == b["nrows"] and a["nrows"] > 0 and np.array_equal(a["mask"], b["mask"])
+                and np.array_equal(a["kept"], b["kept"])):
+            raise SystemExit("bench: device-fed and host-fed scenes of the stream disagree")
     e2e_ms = timed_stream(host_stream, args.steps, max(args.warmup, PIPE_DEPTH))
     lat_ms = timed(eng.run_graph, min(args.steps, 50), args.warmup) / min(args.steps, 50)   # one scene alone, L2 flushed
     lat_e2e_ms = timed(lambda: eng.infer(None), min(args.steps, 50), args.warmup) / min(args.steps, 50)
@@ -570,7 +578,7 @@ def run_ours(args, rank, world, local_rank):
         return None
     # ---- the reference's legacy CUDA ops on this same GPU (geometry ops only; rank 0)
     legacy = None
-    ext = load_legacy() if world == 1 else None
+    ext = load_legacy() if world == 1 and not args.lean else None
     if ext is not None:
         lsteps = max(3, min(args.steps, 10))
         leg_ms = timed(lambda: legacy_step(ext, sc, torch), lsteps, 3) / lsteps
@@ -608,7 +616,7 @@ def run_ours(args, rank, world, local_rank):
                        "forward_speedup_vs_graph_latency": round(legf_ms / lat_ms, 2)})
     # ---- config 3 shape: 64 scenes per graph launch on this GPU (throughput mode; extra, not the headline)
     batch64 = None
-    if world == 1 and not args.no_batch64:
+    if world == 1 and not args.no_batch64 and not args.lean:
         sc64 = GeometryScene(batch=64, num_point=20000, num_grasp=1024, seed=4321, device=dev)
         sc64.run_graph()
         torch.cuda.synchronize()
@@ -647,8 +655,8 @@ def run_ours(args, rank, world, local_rank):
                                 "scenes_per_s": round(64.0 / (i_ms * 1e-3), 1), "gpu_launches_per_step": eng64.launches}
         del eng64
     # ---- SURVEY.md 8(f) f1 (extra, not part of the step): group -> shared MLP -> max-pool fused on the tensor cores
-    fused_mlp = fused_mlp_report(sc, timed, dev) if world == 1 else None
-    infer_ops = inference_op_times(torch, b200grasp, net, eng.cloud, flush)
+    fused_mlp = fused_mlp_report(sc, timed, dev) if world == 1 and not args.lean else None
+    infer_ops = inference_op_times(torch, b200grasp, net, eng.cloud, flush) if not args.lean else None
     # ---- per-kernel pass (rank 0): CUDA events around every launch, L2 flushed before each pass
     per = {}
     reps = 9
@@ -734,6 +742,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-batch64", action="store_true")
+    ap.add_argument("--lean", action="store_true", help="headline, e2e and latency legs only (the command ncu lists "
+                                                        "the launches of): no legacy / batch-64 / fused-MLP / per-op legs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -759,7 +769,7 @@ def main():
 
     line = run_ours(args, rank, world, local_rank)
     if rank == 0:
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1 and not args.no_cpu_baseline and not args.lean:
             n = 8
             sps, sec, cpu_out = time_cpu(n, 1)
             line["cpu_baseline"] = {"value": round(sps, 4), "unit": UNIT, "cores": os.cpu_count(), "kind": "port",

@@ -210,3 +210,40 @@ def test_pipeline_of_scenes_equals_one_scene_at_a_time(b200):
         for g, w in zip(got, want):
             assert g["nrows"] == w["nrows"] and (g["mask"] == w["mask"]).all()
             assert g["kept"].shape == w["kept"].shape and (g["kept"] == w["kept"]).all()
+
+
+@pytest.mark.gpu
+def test_backbone_training_step_gradients_match_legacy_ops(b200, legacy):
+    """cfg5's per-replica step on the backbone: training mode (batch statistics, autograd through grouping_operation /
+    three_interpolate backward) with this library's ops vs the SAME modules on the reference's own CUDA extension
+    (oracle/_ref): loss equal, every parameter gradient within 1e-4 of its scale (both sides accumulate with atomics)."""
+    if legacy is None:
+        pytest.skip("oracle/_ref (legacy extension) not built")
+    from b200grasp import pointnet2_utils
+    cloud = torch.from_numpy(np.stack([b200.synth.tabletop_cloud(6000, 30 + s) for s in range(2)])).cuda()
+    target = torch.randn(2, 256, 1024, generator=torch.Generator().manual_seed(1)).cuda()
+    tf32 = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    grads, losses = [], []
+    try:
+        for ext in (None, legacy["ext"]):
+            bb = b200.graspnet.Pointnet2Backbone()
+            b200.synth.fill_state_dict(bb, 7)
+            bb = bb.cuda().train()
+            saved = pointnet2_utils._ext
+            if ext is not None:
+                pointnet2_utils._ext = ext
+            try:
+                feats, _, _ = bb(cloud)
+                loss = ((feats - target) ** 2).mean()
+                loss.backward()
+            finally:
+                pointnet2_utils._ext = saved
+            losses.append(float(loss))
+            grads.append({k: p.grad.detach().clone() for k, p in bb.named_parameters()})
+    finally:
+        torch.backends.cudnn.allow_tf32 = tf32
+    assert abs(losses[0] - losses[1]) <= 1e-5 * abs(losses[1])
+    assert all(g.abs().max() > 0 for k, g in grads[0].items() if "sa" in k and "weight" in k and "bn" not in k)
+    for k in grads[0]:
+        close(grads[0][k].cpu().numpy(), grads[1][k].cpu().numpy(), 1e-4, what="grad " + k)
