@@ -277,7 +277,9 @@ class Clocks(threading.Thread):
 
 
 # per-launch DRAM bytes from the committed ncu --set full capture (profiles/r01_top_kernels_full.txt)
-NCU_TRAFFIC = {"fps_sa1": 257536}
+NCU_TRAFFIC = {"fps_sa1": 257536,
+               # the CloudCrop launch of group_mlp_maxpool_kernel in profiles/r01_infer_kernels_full.txt (read + write)
+               "group_mlp_maxpool_cloudcrop": 1720320}
 
 # ---------------------------------------------------------------- algorithmic bytes
 
@@ -444,6 +446,20 @@ def run_ours(args, rank, world, local_rank):
         ms = sum(a.elapsed_time(b) for a, b in evs)
         # whole job: MAX of the elapsed device time over ranks (each rank ran `steps` scenes of its own shard)
         return b200grasp.sharding.whole_job_throughput(steps, ms, device=dev)[1]
+
+    def timed_local(fn, steps, warmup):
+        """this rank only (no barrier, no reduction): per-kernel legs that rank 0 runs alone"""
+        for _ in range(warmup):
+            flush.zero_(); fn()
+        torch.cuda.synchronize()
+        evs = []
+        for _ in range(steps):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream); fn(); e1.record(stream)
+            evs.append((e0, e1))
+        torch.cuda.synchronize()
+        return sum(a.elapsed_time(b) for a, b in evs)
 
     from b200grasp import graspnet, synth
     net = make_net(dev)
@@ -678,19 +694,49 @@ def run_ours(args, rank, world, local_rank):
                      "gbs": round(ab / (ms * 1e-3) / 1e9, 3) if ms > 0 else None})
     kern.sort(key=lambda k: -k["ms"])
     top = kern[0]
-    roof = {"bound": "hbm", "kernel": top["kernel"], "achieved": top["gbs"], "peak": peak, "unit": "GB/s",
-            "frac": round(top["gbs"] / peak, 6),
-            # dram__bytes_read.sum + dram__bytes_write.sum of the fps_sa1 launch in the committed ncu --set full
-            # capture (profiles/r01_top_kernels_full.txt): the cloud is read once, nothing else touches DRAM
-            "traffic": NCU_TRAFFIC.get(top["kernel"]), "peak_source": which,
-            "note": "FPS is a serial sample chain (latency-bound, state in registers); see DESIGN.md"}
+    fps_roof = {"bound": "hbm", "kernel": top["kernel"], "achieved": top["gbs"], "peak": peak, "unit": "GB/s",
+                "frac": round(top["gbs"] / peak, 6),
+                # dram__bytes_read.sum + dram__bytes_write.sum of the fps_sa1 launch in the committed ncu --set full
+                # capture: the cloud is read once, nothing else touches DRAM
+                "traffic": NCU_TRAFFIC.get(top["kernel"]), "peak_source": which,
+                "note": "largest kernel of a scene's latency chain; a serial sample chain on one cluster (latency-bound, "
+                        "state in registers), see DESIGN.md 4.1"}
     fps_steps = sum(c[0] - 1 for c in SA_CFG)
     fps_ms = sum(k["ms"] for k in kern if k["kernel"].startswith("fps_"))
-    roof["latency_model"] = {"fps_steps_per_scene": fps_steps, "fps_ms_per_scene": round(fps_ms, 4),
-                             "ns_per_step_sa1": round(1e6 * next(k["ms"] for k in kern if k["kernel"] == "fps_sa1") / (SA_CFG[0][0] - 1), 1)}
+    fps_roof["latency_model"] = {"fps_steps_per_scene": fps_steps, "fps_ms_per_scene": round(fps_ms, 4),
+                                 "ns_per_step_sa1": round(1e6 * next(k["ms"] for k in kern if k["kernel"] == "fps_sa1") / (SA_CFG[0][0] - 1), 1)}
     bw = max((k for k in kern if k["gbs"]), key=lambda k: k["gbs"])
-    roof["best_bandwidth_kernel"] = {"kernel": bw["kernel"], "achieved": bw["gbs"], "frac": round(bw["gbs"] / peak, 4),
-                                     "note": "single launch timed with L2 flushed; B=1 sizes are launch/latency-bound, see DESIGN.md"}
+    # ---- the dominant kernel of the headline (a stream of scenes is bound by SM-time, not by the chain): CloudCrop's
+    # fused group -> MLP -> max-pool, 129 us on all 148 SMs per scene (FPS: 365 us on 16 SMs).  Timed live, alone,
+    # with CUDA events on the launching stream, L2 flushed between iterations.
+    with torch.no_grad():
+        ep = eng.run_graph()
+        crop = net.grasp_generator.crop
+        seeds, rot9 = ep["fp2_xyz"], ep["grasp_top_view_rot"].reshape(1, -1, 9).contiguous()
+        cidx = b200grasp.ops.cylinder_query_multi(seeds, eng.cloud, rot9, crop.cylinder_radius, crop.hmin, crop.hmax_list,
+                                                 crop.nsample)
+        layers = crop._fused.get()
+        n_it = 20
+        crop_ms = timed_local(lambda: b200grasp.ops.group_mlp_maxpool(eng.cloud, seeds, cidx, layers, rot=rot9,
+                                                                      passes=crop.passes), n_it, 3) / n_it
+    crop_rows = cidx.shape[0] * cidx.shape[2] * cidx.shape[3]
+    mma_flops = 2.0 * crop_rows * (64 * 128 + 128 * 256) * crop.passes      # tf32 tensor-core flops actually issued
+    tpeak, twhich = tensor_peak()
+    tf = mma_flops / (crop_ms * 1e-3) / 1e12
+    roof = {"bound": "tensor", "kernel": "group_mlp_maxpool (CloudCrop: 262144 rows x 3->64->128->256, 3xTF32)",
+            "achieved": round(tf, 1), "peak": round(tpeak / 2, 1), "unit": "TFLOP/s", "frac": round(tf / (tpeak / 2), 4),
+            "traffic": NCU_TRAFFIC["group_mlp_maxpool_cloudcrop"], "ms": round(crop_ms, 4),
+            "peak_source": twhich + " bf16 / 2 (tf32 runs at half the bf16 rate)",
+            "algorithmic": "flops = 2 x rows x (64x128 + 128x256) x 3 passes of tcgen05.mma kind::tf32 per launch "
+                           "(the K=3 first layer runs on the CUDA cores and is not counted); fp32-equivalent useful "
+                           "rate = a third of achieved",
+            "note": "dominant kernel of the headline stream by SM-time; the largest kernel of a single scene's latency "
+                    "is fps_sa1 (latency_kernel)",
+            "latency_kernel": fps_roof,
+            "best_bandwidth_kernel": {"kernel": bw["kernel"], "achieved": bw["gbs"], "frac": round(bw["gbs"] / peak, 4),
+                                      "peak": peak, "unit": "GB/s",
+                                      "note": "single launch timed with L2 flushed; B=1 sizes are launch/latency-bound, "
+                                              "see DESIGN.md"}}
     value = world * args.steps / (total_ms * 1e-3)
     e2e = world * args.steps / (e2e_ms * 1e-3)
     line = {"metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,

@@ -239,7 +239,7 @@ def test_backbone_training_step_gradients_match_legacy_ops(b200, legacy):
                 loss.backward()
             finally:
                 pointnet2_utils._ext = saved
-            losses.append(float(loss))
+            losses.append(loss.item())
             grads.append({k: p.grad.detach().clone() for k, p in bb.named_parameters()})
     finally:
         torch.backends.cudnn.allow_tf32 = tf32
