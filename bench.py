@@ -791,6 +791,14 @@ def main():
     ap.add_argument("--lean", action="store_true", help="headline, e2e and latency legs only (the command ncu lists "
                                                         "the launches of): no legacy / batch-64 / fused-MLP / per-op legs")
     args = ap.parse_args()
+    # stdout carries ONE JSON line: anything a library prints there (e.g. NCCL's version banner) goes to stderr instead
+    sys.stdout.flush()
+    out_fd = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(obj):
+        os.write(out_fd, (json.dumps(obj) + "\n").encode())
+
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -807,11 +815,11 @@ def main():
               "sample": "%d whole scenes of the cfg2 workload: the network's reference op sequence with the pointnet2 ops "
                         "answered by oracle/geom_oracle.c (OpenMP) and the layers by torch CPU (all threads), then "
                         "pred_decode / voxel / collision / NMS restated in oracle/post.py" % args.steps}
-        print(json.dumps({"metric": METRIC, "value": round(sps, 4), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        emit({"metric": METRIC, "value": round(sps, 4), "unit": UNIT, "n_gpus": world, "steps": args.steps,
                           "warmup": args.warmup, "ms_per_step": round(sec * 1e3, 3), "higher_is_better": True,
                           "scaling": "weak", "vs_baseline": None, "dtype": "f32 (fp64 collision/NMS, int32 indices)", "data": "synthetic",
                           "config": {"workload": WORKLOAD}, "impl": "reference", "cpu_baseline": cb,
-                          "e2e": {"value": round(sps, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+                          "e2e": {"value": round(sps, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
         return 0
 
     line = run_ours(args, rank, world, local_rank)
@@ -823,7 +831,7 @@ def main():
                                     "sample": "%d whole scenes of the same workload (network forward: oracle C ops with "
                                               "OpenMP + torch CPU layers; decode / voxel / collision / NMS: oracle)" % n,
                                     "decoded_grasps": int(cpu_out[0].shape[0]), "kept_after_nms": int(cpu_out[2].shape[0])}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         import torch.distributed as dist
         dist.destroy_process_group()

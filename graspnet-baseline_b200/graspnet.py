@@ -466,15 +466,13 @@ class GraspNetEngine:
             sp = s_post[s % len(s_post)]
             with torch.cuda.stream(sp):
                 n_s = nrows[s:s + 1]
+                o = self._out                          # results go straight into the one output buffer
                 mask = ops.collision_mask_device(voxels[s][0], voxels[s][1], rows[s], n_s, P["voxel_size"],
-                                                 P["approach_dist"], P["collision_thresh"])
+                                                 P["approach_dist"], P["collision_thresh"], out=o["mask%d" % s])
                 free, nfree = ops.compact_rows(rows[s], mask, n_s)
-                k, nk = ops.grasp_nms_device(free, nfree, P["translation_thresh"], math.cos(P["rotation_thresh"]))
-                o = self._out
+                k, nk = ops.grasp_nms_device(free, nfree, P["translation_thresh"], math.cos(P["rotation_thresh"]),
+                                             out=o["kept%d" % s], out_count=o["nkept%d" % s])
                 o["nrows%d" % s].copy_(n_s)
-                o["mask%d" % s].copy_(mask)
-                o["kept%d" % s].copy_(k)
-                o["nkept%d" % s].copy_(nk)
                 kept.append((k, nk, mask))
                 hold += [free, nfree]
         for sp in s_post[:B]:

@@ -490,16 +490,23 @@ def pred_decode(objectness, score, angle_cls, width, tolerance, xyz, view_xyz):
     return rows, nrows
 
 
-def collision_mask_device(scene, n_dev, grasps, m_dev, voxel_size, approach_dist, collision_thresh):
+def collision_mask_device(scene, n_dev, grasps, m_dev, voxel_size, approach_dist, collision_thresh, out=None):
     """scene (N,3) f64 (+ n_dev (1,) i32 or None), grasps (Mmax,17) f32 of which m_dev (1,) i32 rows are valid ->
-    mask (Mmax,) u8 on the device, 1 = collides   [collision_detector.py:37-112, default return]"""
+    mask (Mmax,) u8 on the device, 1 = collides   [collision_detector.py:37-112, default return].
+    `out`: a (Mmax,) u8 buffer to write into (only the first m_dev entries are written)."""
     _chk(scene, "scene", torch.float64)
     _chk(grasps, "grasps", torch.float32)
     _chk(m_dev, "m_dev", torch.int32)
     if n_dev is not None:
         _chk(n_dev, "n_dev", torch.int32)
     m = grasps.shape[0]
-    mask = torch.zeros((m,), dtype=torch.uint8, device=grasps.device)
+    if out is None:
+        mask = torch.zeros((m,), dtype=torch.uint8, device=grasps.device)
+    else:
+        _chk(out, "out", torch.uint8)
+        if out.numel() != m:
+            raise ValueError("b200grasp: out must hold one byte per grasp row")
+        mask = out
     nbytes = _lib.b200_collision_mask_workspace(m)
     ws = torch.empty((nbytes,), dtype=torch.uint8, device=grasps.device)
     with torch.cuda.device(grasps.device):
@@ -524,14 +531,24 @@ def compact_rows(rows, drop, m_dev):
     return out, nout
 
 
-def grasp_nms_device(grasps, m_dev, translation_thresh, cos_rotation_thresh):
-    """grasps (Mmax,17) f32 with m_dev (1,) i32 valid rows -> (kept rows (Mmax,17) in score order, nkeep (1,) i32)"""
+def grasp_nms_device(grasps, m_dev, translation_thresh, cos_rotation_thresh, out=None, out_count=None):
+    """grasps (Mmax,17) f32 with m_dev (1,) i32 valid rows -> (kept rows (Mmax,17) in score order, nkeep (1,) i32);
+    `out` / `out_count`: buffers of those shapes to write into"""
     _chk(grasps, "grasps", torch.float32)
     _chk(m_dev, "m_dev", torch.int32)
     m = grasps.shape[0]
     keep = torch.empty((max(m, 1),), dtype=torch.int32, device=grasps.device)
-    nkeep = torch.empty((1,), dtype=torch.int32, device=grasps.device)
-    out = torch.empty_like(grasps)
+    if out_count is None:
+        nkeep = torch.empty((1,), dtype=torch.int32, device=grasps.device)
+    else:
+        _chk(out_count, "out_count", torch.int32)
+        nkeep = out_count
+    if out is None:
+        out = torch.empty_like(grasps)
+    else:
+        _chk(out, "out", torch.float32)
+        if tuple(out.shape) != tuple(grasps.shape):
+            raise ValueError("b200grasp: out must have the shape of the grasp rows")
     nbytes = _lib.b200_grasp_nms_workspace(m)
     ws = torch.empty((nbytes,), dtype=torch.uint8, device=grasps.device)
     with torch.cuda.device(grasps.device):
