@@ -18,6 +18,15 @@ lib = ctypes.CDLL(LIB_PATH)
 
 _vp, _i, _f, _d, _sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_double, ctypes.c_size_t
 
+
+class MlpLayer(ctypes.Structure):
+    """b200_mlp_layer (include/b200grasp.h): one tensor-core layer of the fp16x3 kernels"""
+    _fields_ = [("w_packed", _vp), ("bias", _vp), ("k_pad", _i), ("n_pad", _i), ("cout", _i), ("relu", _i),
+                ("w_exp", _i), ("w_norm1", _f), ("b_max", _f), ("y", _vp), ("y_batch_stride", ctypes.c_longlong)]
+
+
+_lp = ctypes.POINTER(MlpLayer)
+
 # name -> argtypes, in the order of include/b200grasp.h
 SIGNATURES = {
     "b200_furthest_point_sampling": [_vp, _i, _i, _i, _vp, _vp],
@@ -55,6 +64,10 @@ SIGNATURES = {
     "b200_cylinder_query_multi_grid": [_vp, _vp, _vp, _i, _i, _i, _f, _f, ctypes.POINTER(_f), _i, _i, _vp, _vp, _sz, _vp],
     "b200_query_grid_build": [_vp, _i, _i, _f, _vp, _sz, _vp],
     "b200_ball_query_prebuilt": [_vp, _vp, _i, _i, _i, _f, _i, _vp, _vp, _sz, _vp],
+    "b200_mlp_f16_pack": [_vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp],
+    "b200_group_mlp_maxpool_f16": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp, _vp, _i, _f, _f, _lp, _vp, _vp, _vp],
+    "b200_group_feat_mlp_maxpool_f16": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _lp, _vp, _vp, _vp],
+    "b200_pointwise_stack_f16": [_vp, _i, _vp, _i, _i, _i, _lp, _i, _i, _vp],
     "b200_cylinder_query_multi_prebuilt": [_vp, _vp, _vp, _i, _i, _i, _f, _f, ctypes.POINTER(_f), _i, _i, _vp, _vp, _sz, _vp],
 }
 for _name, _args in SIGNATURES.items():
@@ -67,6 +80,8 @@ lib.b200_voxel_down_sample_workspace.argtypes = [_i]
 lib.b200_voxel_down_sample_workspace.restype = _sz
 lib.b200_collision_mask_workspace.argtypes = [_i]
 lib.b200_collision_mask_workspace.restype = _sz
+lib.b200_mlp_f16_packed_bytes.argtypes = [_i, _i]
+lib.b200_mlp_f16_packed_bytes.restype = _sz
 lib.b200_query_grid_workspace.argtypes = [_i, _i]
 lib.b200_query_grid_workspace.restype = _sz
 lib.b200_error_string.argtypes = [_i]
@@ -84,7 +99,7 @@ lib.b200_fps_set_multi.restype = None
 lib.b200_fps_set_speculation.argtypes = [_i]
 lib.b200_fps_set_speculation.restype = None
 
-EXPORTS = sorted(list(SIGNATURES) + ["b200_grasp_nms_workspace", "b200_voxel_down_sample_workspace", "b200_query_grid_workspace", "b200_collision_mask_workspace", "b200_error_string", "b200_version", "b200_launch_count"])
+EXPORTS = sorted(list(SIGNATURES) + ["b200_grasp_nms_workspace", "b200_voxel_down_sample_workspace", "b200_query_grid_workspace", "b200_collision_mask_workspace", "b200_mlp_f16_packed_bytes", "b200_error_string", "b200_version", "b200_launch_count"])
 
 
 def check(code, what):

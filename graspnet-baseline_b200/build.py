@@ -65,8 +65,22 @@ def build_fps_profile():
     return out
 
 
+def build_mlp_profile():
+    """Instrumented fused-MLP library (clock64 timeline of CTA 0) for tools/mlp_prof.py; not shipped."""
+    out = os.path.join(HERE, "lib", "libb200mlp_prof.so")
+    cmd = [NVCC, "-shared", "-o", out, os.path.join(CSRC, "mlp_fused.cu"), os.path.join(CSRC, "mlp_f16.cu"),
+           os.path.join(CSRC, "common.cu"), "-DMLP_PROFILE"] + FLAGS
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode:
+        sys.stderr.write(r.stdout + r.stderr)
+        raise RuntimeError("nvcc failed (mlp profile build)")
+    return out
+
+
 if __name__ == "__main__":
-    if "--fps-profile" in sys.argv:
+    if "--mlp-profile" in sys.argv:
+        print(build_mlp_profile())
+    elif "--fps-profile" in sys.argv:
         print(build_fps_profile())
     else:
         print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))

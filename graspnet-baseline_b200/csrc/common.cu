@@ -1,24 +1,36 @@
 // common.cu -- process-wide helpers and the error-string / version entry points.
 #include "common.cuh"
 
+int b200_device() {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return -1;
+  }
+  return dev;
+}
+
 int b200_sm_count() {
-  static int cached = 0;
-  if (cached > 0) return cached;
-  int dev = 0, sms = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess ||
-      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) {
+  static std::atomic<int> cached[64];
+  const int dev = b200_device();
+  if (dev >= 0 && dev < 64) {
+    const int c = cached[dev].load(std::memory_order_relaxed);
+    if (c > 0) return c;
+  }
+  int sms = 0;
+  if (dev < 0 || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) {
     (void)cudaGetLastError();
     return 148;  // B200
   }
-  cached = sms;
+  if (dev < 64) cached[dev].store(sms, std::memory_order_relaxed);
   return sms;
 }
 
-unsigned long long g_b200_launches = 0;
+std::atomic<unsigned long long> g_b200_launches{0};
 
-extern "C" unsigned long long b200_launch_count(void) { return g_b200_launches; }
+extern "C" unsigned long long b200_launch_count(void) { return g_b200_launches.load(); }
 
-extern "C" int b200_version(void) { return 100; }
+extern "C" int b200_version(void) { return 200; }
 
 extern "C" const char *b200_error_string(int code) {
   switch (code) {

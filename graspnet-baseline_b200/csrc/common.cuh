@@ -3,10 +3,12 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+
 #include "../../include/b200grasp.h"
 
 // number of kernels this library has launched in this process (bench.py's gpu_launches)
-extern unsigned long long g_b200_launches;
+extern std::atomic<unsigned long long> g_b200_launches;
 
 #define B200_LAUNCH_CHECK()                         \
   do {                                              \
@@ -24,8 +26,21 @@ extern unsigned long long g_b200_launches;
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 static inline long long ceil_div_ll(long long a, long long b) { return (a + b - 1) / b; }
 
-// SM count of the current device (cached per process; B200 = 148).
+// SM count of the current device (cached per device; B200 = 148).
 int b200_sm_count();
+
+// ordinal of the current device (-1 if the runtime cannot tell)
+int b200_device();
+
+// Per-device one-time setup of a kernel (cudaFuncSetAttribute is a per-device setting): one static instance per
+// kernel instantiation; devices beyond 63 are simply configured on every launch.
+struct B200DeviceOnce {
+  std::atomic<unsigned long long> bits{0};
+  bool need(int dev) const { return dev < 0 || dev >= 64 || !((bits.load(std::memory_order_acquire) >> dev) & 1ull); }
+  void mark(int dev) {
+    if (dev >= 0 && dev < 64) bits.fetch_or(1ull << dev, std::memory_order_release);
+  }
+};
 
 // Squared norm / distance with the association the legacy pointnet2 kernels
 // compile to (nvcc --fmad=true on `a*a + b*b + c*c`): fma(c,c, fma(a,a, b*b)).

@@ -367,12 +367,13 @@ template <int PP, int NT, int ET>
 int launch(const float *xyz, int b, int n, int m, int C, int bits, FpsVerdicts spec, int32_t *idx, cudaStream_t st) {
   constexpr int tab_bytes = (2 * PP * NT * 16 <= TAB_LIMIT) ? 2 * PP * NT * 16 : 0;
   auto kern = fps_kernel<PP, NT, ET>;
-  static bool configured = false;                  // per instantiation
-  if (!configured) {
+  static B200DeviceOnce configured;                // per instantiation, per device
+  const int dev = b200_device();
+  if (configured.need(dev)) {
     if (tab_bytes > 32 * 1024)
       B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tab_bytes));
     if (ET > 0) B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-    configured = true;
+    configured.mark(dev);
   }
   if (ET == 0) {
     kern<<<b, NT, tab_bytes, st>>>(xyz, n, m, 1, bits, spec, idx);
@@ -533,10 +534,11 @@ int g_force_cluster = 0, g_force_threads = 0, g_spec_enabled = 1, g_multi_enable
 // non-portable opt-in and a GPC with 16 free SMs; fall back to the portable 8).
 template <int NT>
 int max_cluster() {
-  static int cached = 0;
-  if (cached) return cached;
+  static std::atomic<int> per_device[64];
+  const int dev = b200_device();
+  if (dev >= 0 && dev < 64 && per_device[dev].load(std::memory_order_relaxed)) return per_device[dev].load(std::memory_order_relaxed);
   auto kern = fps_kernel<(NT == 128 ? 2 : 1), NT, 2>;
-  cached = 8;
+  int cached = 8;
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(MAXC, 1, 1);
@@ -552,6 +554,7 @@ int max_cluster() {
     if (cudaOccupancyMaxActiveClusters(&nclusters, kern, &cfg) == cudaSuccess && nclusters >= 1) cached = MAXC;
   }
   (void)cudaGetLastError();
+  if (dev >= 0 && dev < 64) per_device[dev].store(cached, std::memory_order_relaxed);
   return cached;
 }
 

@@ -279,12 +279,13 @@ template <int PP, int NT, int EL>
 int launch_multi(const float *xyz, int b, int n, int m, int C, int bits, FpsVerdicts spec, int32_t *idx, cudaStream_t st) {
   constexpr int tab_bytes = 2 * PP * NT * 16;
   auto kern = fps_multi_kernel<PP, NT, EL>;
-  static bool configured = false;                  // per instantiation
-  if (!configured) {
+  static B200DeviceOnce configured;                // per instantiation, per device
+  const int dev = b200_device();
+  if (configured.need(dev)) {
     if (tab_bytes > 32 * 1024)
       B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tab_bytes));
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-    configured = true;
+    configured.mark(dev);
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(b * C), 1, 1);

@@ -89,6 +89,18 @@ struct Smem {
   static constexpr int total = holder + 16;
 };
 
+#ifdef MLP_PROFILE
+// timeline of CTA 0 (tools/mlp_prof.py): clock64 stamps [role][tile iteration][event]
+constexpr int PROF_TILES = 16, PROF_EV = 8;
+__device__ unsigned long long g_mlp_prof[3][PROF_TILES][PROF_EV];
+#define PROF(role, it, ev)                                                                   \
+  do {                                                                                       \
+    if (blockIdx.x == 0 && (it) < PROF_TILES) g_mlp_prof[role][it][ev] = (unsigned long long)clock64(); \
+  } while (0)
+#else
+#define PROF(role, it, ev) do {} while (0)
+#endif
+
 __device__ __forceinline__ float relu_keep_nan(float v) { return (v <= 0.f) ? 0.f : v; }
 
 __device__ __forceinline__ float max_nan(float a, float b) {
@@ -246,10 +258,13 @@ group_mlp_maxpool_kernel(const Params p) {
       // the pooling scratch alternates between tiles: a warp may start tile t + 1's layer-3 epilogue while
       // another still combines tile t (they meet again at tile t + 1's barrier before the buffer is reused)
       float *pool = pools + (it & 1) * (MAXE * MAXC);
+      const bool pr = lane == 0 && (warp & 3) == 0;
+      if (pr) PROF(half, it, 0);
       // epilogues of all tensor-core layers but the last -> K-slabs of the next layer
       for (int l = 0; l + 1 < p.NG; ++l) {
         tc::mbar_wait(acc_full + 8 * l, it & 1);
         tc::fence_after_sync();
+        if (pr && l == p.NG - 2) PROF(half, it, 1);
         const int sl = p.Nd[l] / KS;
         const float *bl = biases + l * MAXC;
         for (int s = half; s < sl; s += 2) {
@@ -261,10 +276,13 @@ group_mlp_maxpool_kernel(const Params p) {
         }
         na += sl;
       }
+      if (pr) PROF(half, it, 2);
       if (tile + (int)gridDim.x < p.tiles) gather_layer1(tile + gridDim.x);
+      if (pr) PROF(half, it, 3);
       // layer-3 epilogue: max of the raw accumulators over the rows of a pooling entry (a warp's 32 rows, or 16)
       tc::mbar_wait(acc_full + 8 * (p.NG - 1), it & 1);
       tc::fence_after_sync();
+      if (pr) PROF(half, it, 4);
       for (int s = half; s < C3 / KS; s += 2) {
         float v[16];
         tc::tmem_ld16(lane_base + col[p.NG - 1] + s * KS, v);
@@ -289,8 +307,10 @@ group_mlp_maxpool_kernel(const Params p) {
           }
         }
       }
+      if (pr) PROF(half, it, 5);
       tc::fence_before_sync();
       tc::named_barrier(1, ROW_THREADS);
+      if (pr) PROF(half, it, 6);
       // combine the entries of each list, bias + ReLU, write (B, C3, m, G)
       const int epl = p.ns >= 32 ? p.ns / 32 : 1;                     // entries per list
       for (int c = tid; c < C3; c += ROW_THREADS) {
@@ -308,12 +328,14 @@ group_mlp_maxpool_kernel(const Params p) {
           if (p.out_t) p.out_t[ql * C3 + c] = y;
         }
       }
+      if (pr) PROF(half, it, 7);
     }
   } else if (warp == 8) {
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0) {
       uint32_t na = 0, nw = 0;
-      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
+      for (int tile = blockIdx.x, it = 0; tile < p.tiles; tile += gridDim.x, ++it) {
+        (void)it;
         for (int layer = 0; layer < p.NG; ++layer) {
           const int K = p.Kd[layer], N = p.Nd[layer];
           const uint32_t d = tmem + col[layer];
@@ -324,6 +346,8 @@ group_mlp_maxpool_kernel(const Params p) {
             tc::mbar_wait(sm + Smem::bars + (2 * NA + ws) * 8, (nw / NWS) & 1u);
             tc::mbar_wait(sm + Smem::bars + as * 8, (na / NA) & 1u);
             tc::fence_after_sync();
+            if (s == 0 && layer >= p.NG - 2) PROF(2, it, 2 * (layer - (p.NG - 2)) + 0);          // first slab of the last two layers ready
+            if (s == K / KS - 1 && layer >= p.NG - 2) PROF(2, it, 2 * (layer - (p.NG - 2)) + 1);  // last slab ready
             const uint32_t a_base = sm + Smem::a_ring + as * A_SLOT, w_base = sm + Smem::w_ring + ws * W_SLOT;
 #pragma unroll
             for (int kk = 0; kk < KS / 8; ++kk) {
@@ -393,10 +417,11 @@ __global__ void mlp_pack_kernel(const float *__restrict__ w, int cout, int cin, 
 }
 
 int launch(Params &p, cudaStream_t stream) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static B200DeviceOnce attr_set;
+  const int dev = b200_device();
+  if (attr_set.need(dev)) {
     B200_CUDA(cudaFuncSetAttribute(group_mlp_maxpool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem::total));
-    attr_set = true;
+    attr_set.mark(dev);
   }
   const int grid = p.tiles < b200_sm_count() ? p.tiles : b200_sm_count();
   group_mlp_maxpool_kernel<<<grid, NTHREADS, Smem::total, stream>>>(p);
@@ -407,6 +432,12 @@ int launch(Params &p, cudaStream_t stream) {
 bool width_ok(int c) { return c >= 16 && c <= MAXC && c % 16 == 0; }
 
 }  // namespace
+
+#ifdef MLP_PROFILE
+extern "C" int b200_mlp_read_profile(unsigned long long *host) {
+  return (int)cudaMemcpyFromSymbol(host, g_mlp_prof, sizeof(g_mlp_prof));
+}
+#endif
 
 extern "C" int b200_mlp_pack_weights(const float *w, int cout, int cin, float *packed, void *stream) {
   if (!w || !packed || !width_ok(cout) || cin < KS || cin % KS || cin > 2 * MAXC) return B200_EINVAL;

@@ -17,6 +17,10 @@ from . import ops, pointnet2_utils
 
 # False = always run the composed path (the reference's own op sequence: group ops + torch layers), also in eval mode
 FUSED = True
+# Arithmetic of the fused fp32-grade paths (modules built with passes=3): "f16x3" = csrc/mlp_f16.cu (fp16 hi | lo
+# operands, exact power-of-two scaling, tcgen05 kind::f16; also the 1x1-conv stacks between the geometry ops),
+# "tf32x3" = csrc/mlp_fused.cu (3xTF32) + csrc/pointwise.cu (fp32 FMAs).  passes=1 modules always run plain TF32.
+ARITH = "f16x3"
 
 
 class _BN(nn.Sequential):
@@ -67,6 +71,7 @@ class _FusedMLP:
 
     def __init__(self, mlp):
         self.mlp, self.key, self.layers = mlp, None, None
+        self.key16, self.layers16 = None, None
 
     def get(self):
         params = list(self.mlp.parameters()) + list(self.mlp.buffers())
@@ -83,6 +88,23 @@ class _FusedMLP:
                            (ops.mlp_pack_weights(w3), b3, w3.shape[0])]
             self.key = key
         return self.layers
+
+    def get_f16(self):
+        """(first, [F16Layer]) for ops.group_mlp_maxpool_f16 (first = (w1, b1, max row 1-norm of w1, max |b1|)) or
+        (None, [three F16Layer]) for ops.group_feat_mlp_maxpool_f16"""
+        params = list(self.mlp.parameters()) + list(self.mlp.buffers())
+        key = tuple((p.data_ptr(), p._version) for p in params)
+        if key != self.key16:
+            (w1, b1), (w2, b2), (w3, b3) = self.mlp.folded()
+            if w1.shape[1] == 3:
+                first = (w1, b1, float(w1.abs().sum(dim=1).max()) * (1.0 + 1e-5), float(b1.abs().max()))
+                self.layers16 = (first, ops.f16_stack([(w2, b2), (w3, b3)], first_k_pad=(w1.shape[0] + 31) // 32 * 32))
+            else:
+                c = w1.shape[1] - 3
+                self.layers16 = (None, ops.f16_stack([(w1, b1), (w2, b2), (w3, b3)], first_k_pad=(c + 3 + 31) // 32 * 32,
+                                                     feat_channels=c))
+            self.key16 = key
+        return self.layers16
 
 
 def fusable(mlp, nsample):
@@ -143,11 +165,18 @@ class PointnetSAModuleVotes(nn.Module):
         """the fused kernel on given neighbour lists idx (B,npoint,nsample): -> (new_features (B,C,npoint),
         the same channels-last (B,npoint,C))"""
         radius = self.radius if self.normalize_xyz else 0.0
+        f16 = self.passes == 3 and ARITH == "f16x3"
         if features is None and features_t is None:
+            if f16:
+                first, layers = self._fused.get_f16()
+                return ops.group_mlp_maxpool_f16(xyz, new_xyz, idx, first, layers, radius=radius, channels_last=True)
             return ops.group_mlp_maxpool(xyz, new_xyz, idx, self._fused.get(), radius=radius, passes=self.passes,
                                          channels_last=True)
         if features_t is None:
             features_t = features.transpose(1, 2).contiguous()
+        if f16:
+            return ops.group_feat_mlp_maxpool_f16(xyz, new_xyz, features_t, idx, self._fused.get_f16()[1],
+                                                  radius=radius, channels_last=True)
         return ops.group_feat_mlp_maxpool(xyz, new_xyz, features_t, idx, self._fused.get(), radius=radius,
                                           passes=self.passes, channels_last=True)
 
@@ -176,6 +205,9 @@ class CloudCrop(nn.Module):
             rot = vp_rot.reshape(B, num_seed, 9).contiguous()
             idx = ops.cylinder_query_multi(seed_xyz, pointcloud, rot, self.cylinder_radius, self.hmin,
                                            self.hmax_list, self.nsample, grid=grid)
+            if self.passes == 3 and ARITH == "f16x3":
+                first, layers = self._fused.get_f16()
+                return ops.group_mlp_maxpool_f16(pointcloud, seed_xyz, idx, first, layers, rot=rot)
             return ops.group_mlp_maxpool(pointcloud, seed_xyz, idx, self._fused.get(), rot=rot, passes=self.passes)
         grouped = [g(pointcloud, seed_xyz, vp_rot) for g in self.groupers]
         grouped = torch.stack(grouped, dim=3).view(B, -1, num_seed * num_depth, self.nsample)

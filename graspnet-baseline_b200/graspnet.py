@@ -51,19 +51,91 @@ def _pointwise(x, w, b, relu=True, x2=None):
 
 class _Folded:
     """[(w (Cout,Cin), b (Cout))] of a conv(+BatchNorm) stack with the eval-mode statistics folded in; rebuilt when a
-    parameter or buffer changes"""
+    parameter or buffer changes.  `relu_last`: whether the last layer of the stack is followed by a ReLU."""
 
-    def __init__(self, owner, build):
+    MAX_WIDTH = 256                 # output channels one fp16x3 launch covers (csrc/mlp_f16.cu)
+
+    def __init__(self, owner, build, relu_last=True):
         self.owner, self.build, self.key, self.layers = owner, build, None, None
+        self.relu_last, self.key16, self.groups = relu_last, None, None
+
+    def _key(self):
+        tensors = list(self.owner.parameters()) + list(self.owner.buffers())
+        return tuple((t.data_ptr(), t._version) for t in tensors)
 
     def get(self):
-        tensors = list(self.owner.parameters()) + list(self.owner.buffers())
-        key = tuple((t.data_ptr(), t._version) for t in tensors)
+        key = self._key()
         if key != self.key:
             with torch.no_grad():
                 self.layers = [(ops.pad_weight(w), b.contiguous()) for w, b in self.build()]
             self.key = key
         return self.layers
+
+    def get_f16(self):
+        """The stack as launch groups for ops.pointwise_stack_f16: [[(F16Layer list, channel offset, total channels)]]:
+        consecutive layers share a launch while their accumulators fit the tensor memory (512 columns; layer l+2
+        reuses layer l's); a layer wider than 256 channels is a launch group of its own, its output channels split
+        over several launches."""
+        key = self._key()
+        if key != self.key16:
+            with torch.no_grad():
+                folded = [(w.contiguous(), b.contiguous()) for w, b in self.build()]
+                relus = [True] * (len(folded) - 1) + [self.relu_last]
+                groups, cur = [], []
+
+                def flush():
+                    if cur:
+                        ls = ops.f16_stack([f for f, _ in cur], relu_last=cur[-1][1])
+                        groups.append([(ls, 0, ls[-1].cout)])
+                        del cur[:]
+
+                for (w, b), relu in zip(folded, relus):
+                    cout = w.shape[0]
+                    if cout > self.MAX_WIDTH:
+                        flush()
+                        parts = -(-cout // self.MAX_WIDTH)
+                        step = -(-cout // parts)
+                        step = (step + 15) // 16 * 16           # every part padded to the same width: pairs of
+                        groups.append([(ops.f16_stack([(w[o:o + step].contiguous(), b[o:o + step].contiguous())],
+                                                      relu_last=relu, n_pads=[step]), o, cout)    # parts share a launch
+                                       for o in range(0, cout, step)])
+                        continue
+                    pad = lambda c: (c + 15) // 16 * 16
+                    widths = [pad(f[0].shape[0]) for f, _ in cur] + [pad(cout)]
+                    fits = len(widths) <= 3 and all(widths[i] + widths[i + 1] <= 512 for i in range(len(widths) - 1))
+                    if not fits:
+                        flush()
+                    cur.append(((w, b), relu))
+                flush()
+                self.groups = groups
+            self.key16 = key
+        return self.groups
+
+
+def _stack(x, folded, x2=None):
+    """a conv(+BN+ReLU) stack over point columns: fp16x3 tensor-core launches (csrc/mlp_f16.cu) or, with
+    fused_modules.ARITH = "tf32x3", one exact-fp32 launch per layer (csrc/pointwise.cu)"""
+    if fm.ARITH != "f16x3":
+        layers = folded.get()
+        for i, (w, b) in enumerate(layers):
+            x, x2 = _pointwise(x, w, b, relu=folded.relu_last or i + 1 < len(layers), x2=x2), None
+        return x
+    x = x.contiguous()
+    for group in folded.get_f16():
+        if len(group) == 1:
+            x = ops.pointwise_stack_f16(x, group[0][0], x2=x2)
+        else:                                               # a wide layer: its parts two per launch
+            out = torch.empty((x.shape[0], group[0][2], x.shape[2]), dtype=torch.float32, device=x.device)
+            for i in range(0, len(group), 2):
+                layers, off, _ = group[i]
+                if i + 1 < len(group):
+                    ops.pointwise_stack_f16(x, layers, x2=x2, out=out, out_channel_offset=off, layers2=group[i + 1][0],
+                                            out2=out, out2_channel_offset=group[i + 1][1])
+                else:
+                    ops.pointwise_stack_f16(x, layers, x2=x2, out=out, out_channel_offset=off)
+            x = out
+        x2 = None
+    return x
 
 
 def _fold1d(conv, bn=None):
@@ -116,11 +188,8 @@ class PointnetFPModule(nn.Module):
             dist_recip = 1.0 / (dist + 1e-8)
             weight = dist_recip / torch.sum(dist_recip, dim=2, keepdim=True)
             interpolated = pointnet2_utils.three_interpolate(known_feats, idx, weight)
-        if _fast(self):
-            x, skip = interpolated, unknow_feats             # the concatenation happens inside the first layer
-            for w, b in self._folded.get():
-                x, skip = _pointwise(x, w, b, x2=skip), None
-            return x
+        if _fast(self):                                     # the concatenation happens inside the first layer
+            return _stack(interpolated, self._folded, x2=None if unknow_feats is None else unknow_feats.contiguous())
         x = torch.cat([interpolated, unknow_feats], dim=1) if unknow_feats is not None else interpolated
         return self.mlp(x.unsqueeze(-1)).squeeze(-1)
 
@@ -181,7 +250,7 @@ class ApproachNet(nn.Module):
         self.bn1 = nn.BatchNorm1d(self.in_dim)
         self.bn2 = nn.BatchNorm1d(2 + self.num_view)
         self._folded = _Folded(self, lambda: [_fold1d(self.conv1, self.bn1), _fold1d(self.conv2, self.bn2),
-                                              _fold1d(self.conv3)])
+                                              _fold1d(self.conv3)], relu_last=False)
         self._tables = {}
 
     def tables(self, device):
@@ -199,8 +268,7 @@ class ApproachNet(nn.Module):
         B, num_seed, _ = seed_xyz.size()
         views, frames = self.tables(seed_features.device)
         if _fast(self):
-            (w1, b1), (w2, b2), (w3, b3) = self._folded.get()
-            features = _pointwise(_pointwise(_pointwise(seed_features, w1, b1), w2, b2), w3, b3, relu=False)
+            features = _stack(seed_features, self._folded)
             top_view_inds, top_view_scores, vp_xyz, vp_rot = ops.view_select(features, views, frames)
             view_score = features[:, 2:2 + self.num_view, :].transpose(1, 2)       # a view; the loss wants it contiguous
         else:
@@ -232,14 +300,13 @@ class _Head(nn.Module):
         self.bn1 = nn.BatchNorm1d(128)
         self.bn2 = nn.BatchNorm1d(128)
         self._folded = _Folded(self, lambda: [_fold1d(self.conv1, self.bn1), _fold1d(self.conv2, self.bn2),
-                                              _fold1d(self.conv3)])
+                                              _fold1d(self.conv3)], relu_last=False)
 
     def scores(self, vp_features):
         B, _, num_seed, num_depth = vp_features.size()
         x = vp_features.view(B, -1, num_seed * num_depth)
         if _fast(self):
-            (w1, b1), (w2, b2), (w3, b3) = self._folded.get()
-            x = _pointwise(_pointwise(_pointwise(x, w1, b1), w2, b2), w3, b3, relu=False)
+            x = _stack(x, self._folded)
         else:
             x = F.relu(self.bn1(self.conv1(x)), inplace=True)
             x = F.relu(self.bn2(self.conv2(x)), inplace=True)
@@ -284,6 +351,32 @@ class GraspNetStage1(nn.Module):
         return self.vpmodule(seed_xyz, seed_features, end_points)
 
 
+def _two_heads(operation, tolerance, vp_features, end_points):
+    """OperationNet and ToleranceNet over the same crop features as ONE launch of two stacks (fp16x3 fast path)"""
+    B, _, num_seed, num_depth = vp_features.size()
+    x = vp_features.reshape(B, -1, num_seed * num_depth)
+    if not x.is_contiguous():
+        x = x.contiguous()
+    fo, ft = operation._folded, tolerance._folded
+    key = (fo._key(), ft._key())
+    if getattr(operation, "_pair_key", None) != key:
+        with torch.no_grad():
+            a = [(w.contiguous(), b.contiguous()) for w, b in fo.build()]
+            t = [(w.contiguous(), b.contiguous()) for w, b in ft.build()]
+            pads = [(max(wa.shape[0], wt.shape[0]) + 15) // 16 * 16 for (wa, _), (wt, _) in zip(a, t)]
+            operation._pair = (ops.f16_stack(a, relu_last=False, n_pads=pads), ops.f16_stack(t, relu_last=False, n_pads=pads))
+        operation._pair_key = key
+    la, lt = operation._pair
+    ya, yt = ops.pointwise_stack_f16(x, la, layers2=lt)
+    na = operation.num_angle
+    ya, yt = ya.view(B, -1, num_seed, num_depth), yt.view(B, -1, num_seed, num_depth)
+    end_points['grasp_score_pred'] = ya[:, 0:na]
+    end_points['grasp_angle_cls_pred'] = ya[:, na:2 * na]
+    end_points['grasp_width_pred'] = ya[:, 2 * na:3 * na]
+    end_points['grasp_tolerance_pred'] = yt
+    return end_points
+
+
 class GraspNetStage2(nn.Module):
     def __init__(self, num_angle=12, num_depth=4, cylinder_radius=0.05, hmin=-0.02, hmax_list=(0.01, 0.02, 0.03, 0.04),
                  is_training=True, passes=3):
@@ -299,6 +392,8 @@ class GraspNetStage2(nn.Module):
                                       "the reference's model code; build the network with is_training=False")
         vp_features = self.crop(end_points['fp2_xyz'], end_points['input_xyz'], end_points['grasp_top_view_rot'],
                                 grid=grid)
+        if _fast(self.operation) and fm.ARITH == "f16x3":
+            return _two_heads(self.operation, self.tolerance, vp_features, end_points)
         end_points = self.operation(vp_features, end_points)
         return self.tolerance(vp_features, end_points)
 
@@ -448,11 +543,14 @@ class GraspNetEngine:
         ep['fp2_inds'] = inds[0][:, 0:xyzs[1].shape[1]]
         ep = vp(xyzs[1], f, ep)
         vp_features = gen.crop(xyzs[1], cloud, ep['grasp_top_view_rot'], grid=grid)
-        s_head.wait_stream(main)
-        with torch.cuda.stream(s_head):                # the two heads read the same crop features
-            ep = gen.tolerance(vp_features, ep)
-        ep = gen.operation(vp_features, ep)
-        main.wait_stream(s_head)
+        if fm.ARITH == "f16x3":
+            ep = _two_heads(gen.operation, gen.tolerance, vp_features, ep)      # both heads, one launch
+        else:
+            s_head.wait_stream(main)
+            with torch.cuda.stream(s_head):            # the two heads read the same crop features
+                ep = gen.tolerance(vp_features, ep)
+            ep = gen.operation(vp_features, ep)
+            main.wait_stream(s_head)
         hold.append(vp_features)
         rows, nrows = ops.pred_decode(*[ep[k].float().contiguous() for k in
                                         ("objectness_score", "grasp_score_pred", "grasp_angle_cls_pred",

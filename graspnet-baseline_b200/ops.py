@@ -8,6 +8,7 @@ reference's CHECK_* macros in include/utils.h:10-30 do) -- plus the two
 post-processing ops.  PyTorch is used for device memory and streams only.
 """
 import ctypes
+import math
 
 import torch
 
@@ -177,6 +178,165 @@ def group_feat_mlp_maxpool(xyz, new_xyz, feat_t, idx, layers, radius=0.0, passes
                                                     _ptr(out_t) if channels_last else None, _stream()),
                    "group_feat_mlp_maxpool")
     return (out, out_t) if channels_last else out
+
+
+class F16Layer:
+    """One layer y = act(W x + b) prepared for the fp16x3 tensor-core kernels (csrc/mlp_f16.cu): W split hi | lo in
+    fp16 after an exact power-of-two scale, packed in K-slabs; the zero-padded bias; the two numbers of the range
+    bound (max row 1-norm of W, max |b|)."""
+
+    def __init__(self, w, b, relu=True, k_pad=None, feat_channels=0, n_pad=None):
+        _chk(w, "w", torch.float32)
+        _chk(b, "b", torch.float32)
+        cout, cin = w.shape
+        self.cout, self.cin, self.relu = cout, cin, bool(relu)
+        self.n_pad = (cout + 15) // 16 * 16 if n_pad is None else n_pad
+        self.k_pad = (cin + 31) // 32 * 32 if k_pad is None else k_pad
+        if self.n_pad > 256:
+            raise RuntimeError("b200grasp: fp16x3 layers are at most 256 channels wide (split the output channels)")
+        wmax = float(w.abs().max()) if w.numel() else 0.0
+        self.w_exp = max(-40, min(40, 14 - math.frexp(wmax)[1])) if wmax > 0 and math.isfinite(wmax) else 0
+        self.w_norm1 = float(w.abs().sum(dim=1).max()) * (1.0 + 1e-5)
+        self.b_max = float(b.abs().max())
+        self.bias = torch.zeros(self.n_pad, dtype=torch.float32, device=w.device)
+        self.bias[:cout] = b
+        nbytes = _lib.b200_mlp_f16_packed_bytes(self.n_pad, self.k_pad)
+        self.packed = torch.empty(nbytes, dtype=torch.uint8, device=w.device)
+        with torch.cuda.device(w.device):
+            _abi.check(_lib.b200_mlp_f16_pack(_ptr(w), cout, cin, cin, self.n_pad, self.k_pad, self.w_exp,
+                                              int(feat_channels), _ptr(self.packed), _stream()), "mlp_f16_pack")
+
+    def fill(self, dst, y=None, y_batch_stride=0):
+        dst.w_packed, dst.bias = self.packed.data_ptr(), self.bias.data_ptr()
+        dst.k_pad, dst.n_pad, dst.cout, dst.relu, dst.w_exp = self.k_pad, self.n_pad, self.cout, int(self.relu), self.w_exp
+        dst.w_norm1, dst.b_max = self.w_norm1, self.b_max
+        dst.y = y.data_ptr() if y is not None else None
+        dst.y_batch_stride = int(y_batch_stride)
+
+
+def f16_stack(folded, relu_last=True, first_k_pad=None, feat_channels=0, n_pads=None):
+    """[(w, b)] of consecutive layers -> [F16Layer] whose K paddings chain (layer l reads layer l-1's padded width);
+    n_pads: padded output widths to use instead of the next multiple of 16 (two heads of one launch share them)"""
+    out = []
+    for i, (w, b) in enumerate(folded):
+        k_pad = first_k_pad if i == 0 else (out[-1].n_pad + 31) // 32 * 32
+        out.append(F16Layer(w.contiguous(), b.contiguous(), relu=relu_last or i + 1 < len(folded), k_pad=k_pad,
+                            feat_channels=feat_channels if i == 0 else 0, n_pad=None if n_pads is None else n_pads[i]))
+    return out
+
+
+def _layer_array(layers, ys=None, strides=None):
+    arr = (_abi.MlpLayer * len(layers))()
+    for i, l in enumerate(layers):
+        l.fill(arr[i], None if ys is None else ys[i], 0 if strides is None else strides[i])
+    return arr
+
+
+def group_mlp_maxpool_f16(xyz, new_xyz, idx, first, layers, radius=0.0, rot=None, channels_last=False):
+    """group_mlp_maxpool in fp16x3 arithmetic: first = (w1 (C1,3), b1 (C1), |w1| row 1-norm max, max |b1|) for the
+    CUDA-core layer, layers = [F16Layer, F16Layer]."""
+    _chk(xyz, "xyz", torch.float32)
+    _chk(new_xyz, "new_xyz", torch.float32)
+    _chk(idx, "idx", torch.int32)
+    squeeze = idx.dim() == 3
+    g = 1 if squeeze else idx.shape[0]
+    b, n, _ = xyz.shape
+    m, ns = idx.shape[-2], idx.shape[-1]
+    w1, b1, w1n, b1m = first
+    _chk(w1, "w1", torch.float32)
+    _chk(b1, "b1", torch.float32)
+    if rot is not None:
+        _chk(rot, "rot", torch.float32)
+    c3 = layers[-1].cout
+    out = torch.empty((b, c3, m, g), dtype=torch.float32, device=xyz.device)
+    out_t = torch.empty((b, m, g, c3), dtype=torch.float32, device=xyz.device) if channels_last else None
+    arr = _layer_array(layers)
+    with torch.cuda.device(xyz.device):
+        _abi.check(_lib.b200_group_mlp_maxpool_f16(_ptr(xyz), _ptr(new_xyz), _ptr(rot) if rot is not None else None,
+                                                   _ptr(idx), g, b, n, m, ns, float(radius), _ptr(w1), _ptr(b1),
+                                                   w1.shape[0], float(w1n), float(b1m), arr, _ptr(out),
+                                                   _ptr(out_t) if channels_last else None, _stream()),
+                   "group_mlp_maxpool_f16")
+    if squeeze:
+        out = out.view(b, c3, m)
+        out_t = out_t.view(b, m, c3) if channels_last else None
+    return (out, out_t) if channels_last else out
+
+
+def group_feat_mlp_maxpool_f16(xyz, new_xyz, feat_t, idx, layers, radius=0.0, channels_last=False):
+    """group_feat_mlp_maxpool in fp16x3 arithmetic: layers = three F16Layer, the first packed with feat_channels = C"""
+    _chk(xyz, "xyz", torch.float32)
+    _chk(new_xyz, "new_xyz", torch.float32)
+    _chk(feat_t, "feat_t", torch.float32)
+    _chk(idx, "idx", torch.int32)
+    b, n, _ = xyz.shape
+    m, ns = idx.shape[-2], idx.shape[-1]
+    c = feat_t.shape[2]
+    if feat_t.shape[:2] != (b, n):
+        raise RuntimeError("feat_t must be (B,N,C) channels-last")
+    c3 = layers[-1].cout
+    out = torch.empty((b, c3, m), dtype=torch.float32, device=xyz.device)
+    out_t = torch.empty((b, m, c3), dtype=torch.float32, device=xyz.device) if channels_last else None
+    arr = _layer_array(layers)
+    with torch.cuda.device(xyz.device):
+        _abi.check(_lib.b200_group_feat_mlp_maxpool_f16(_ptr(xyz), _ptr(new_xyz), _ptr(feat_t), _ptr(idx), b, n, m, ns,
+                                                        c, float(radius), arr, _ptr(out),
+                                                        _ptr(out_t) if channels_last else None, _stream()),
+                   "group_feat_mlp_maxpool_f16")
+    return (out, out_t) if channels_last else out
+
+
+def pointwise_stack_f16(x, layers, x2=None, keep=None, out=None, out_channel_offset=0, layers2=None, out2=None,
+                        out2_channel_offset=0):
+    """[x (B,C1,n) | x2 (B,C2,n)] through 1..3 F16Layer in one launch -> the last layer's output (B,Cout,n); with
+    keep = [bool per layer] a list of every kept layer's output.  `out` (B,Ctot,n) + out_channel_offset: write the LAST
+    layer's channels there instead (layers whose output channels are split over several stacks).
+    layers2: a second stack of the same padded shapes over the same input, run by the same launch (its last layer
+    goes to out2 at out2_channel_offset, or to a new tensor); returns (first result, second result)."""
+    _chk(x, "x", torch.float32)
+    b, c1, n = x.shape
+    c2 = 0
+    if x2 is not None:
+        _chk(x2, "x2", torch.float32)
+        c2 = x2.shape[1]
+    nl = len(layers)
+    keep = [False] * (nl - 1) + [True] if keep is None else list(keep)
+    ys, strides = [], []
+    for i, l in enumerate(layers):
+        if i + 1 == nl and out is not None:
+            ys.append(out[:, out_channel_offset:, :])
+            strides.append(out.shape[1] * n)
+        elif keep[i]:
+            ys.append(torch.empty((b, l.cout, n), dtype=torch.float32, device=x.device))
+            strides.append(l.cout * n)
+        else:
+            ys.append(None)
+            strides.append(0)
+    heads = 1 if layers2 is None else 2
+    arr = (_abi.MlpLayer * (heads * nl))()
+    for i, l in enumerate(layers):
+        l.fill(arr[i], None, strides[i])
+        if ys[i] is not None:
+            arr[i].y = ys[i].data_ptr()
+    y2 = None
+    if layers2 is not None:
+        if len(layers2) != nl:
+            raise RuntimeError("b200grasp: the two stacks of a launch must have the same depth")
+        for i, l in enumerate(layers2):
+            l.fill(arr[nl + i], None, 0)
+        if out2 is not None:
+            y2, view, stride2 = out2, out2[:, out2_channel_offset:, :], out2.shape[1] * n
+        else:
+            y2 = torch.empty((b, layers2[-1].cout, n), dtype=torch.float32, device=x.device)
+            view, stride2 = y2, layers2[-1].cout * n
+        arr[2 * nl - 1].y = view.data_ptr()
+        arr[2 * nl - 1].y_batch_stride = stride2
+    with torch.cuda.device(x.device):
+        _abi.check(_lib.b200_pointwise_stack_f16(_ptr(x), c1, _ptr(x2) if x2 is not None else None, c2, b, n, arr,
+                                                 nl, heads, _stream()), "pointwise_stack_f16")
+    kept = [y for y, k in zip(ys, keep) if k]
+    first = out if out is not None else (kept[0] if len(kept) == 1 else kept)
+    return first if layers2 is None else (first, y2)
 
 
 def gather_points_grad(grad_out, idx, n):

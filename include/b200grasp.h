@@ -108,6 +108,49 @@ int b200_group_feat_mlp_maxpool(const float *xyz, const float *new_xyz, const fl
  * cout a multiple of 16 up to 256, cin a multiple of 16 up to 512. */
 int b200_mlp_pack_weights(const float *w, int cout, int cin, float *packed, void *stream);
 
+/* ---- The same modules, and the stacks of 1x1 convolutions between them, in "fp16x3" arithmetic (csrc/mlp_f16.cu):
+ * operands split hi + lo in fp16 with exact power-of-two scales (weights per layer, activations per warp of 32 rows
+ * from a rigorous bound), three tcgen05.mma kind::f16 products per K = 16 step, fp32 accumulation -- fp32-grade like
+ * 3xTF32 at twice the tensor rate and half the accumulation steps; weights stay resident in shared memory when they
+ * fit.  One tensor-core layer y = act(W x + b), BatchNorm folded by the caller: */
+typedef struct {
+  const void *w_packed;       /* b200_mlp_f16_pack of W (cout, cin) zero-padded to (n_pad, k_pad)                  */
+  const float *bias;          /* [n_pad], zero padded                                                              */
+  int k_pad, n_pad;           /* k_pad % 32 == 0 (= the previous layer's n_pad rounded up to 32), n_pad % 16 == 0,
+                                 16 <= n_pad <= 256                                                                */
+  int cout;                   /* real output channels                                                              */
+  int relu;                   /* apply ReLU                                                                        */
+  int w_exp;                  /* W was multiplied by 2^w_exp before the split (so that max |W| lands near 2^13)    */
+  float w_norm1, b_max;       /* max_c sum_k |W[c,k]| and max_c |b[c]| (of the unscaled W, b): the range bound     */
+  float *y;                   /* pointwise stacks: this layer's output [B, *, n] (NULL = not written; the last
+                                 layer's must be set); grouped modules: NULL                                       */
+  long long y_batch_stride;   /* floats between batches of y                                                       */
+} b200_mlp_layer;
+size_t b200_mlp_f16_packed_bytes(int n_pad, int k_pad);
+/* w[cout, cin] (row stride ldw) -> packed.  feat_channels = C > 0: the input columns are [x y z | C features] (the
+ * reference's concatenation order, pointnet2_utils.py:351-355) and are packed as [features | x y z | pad]. */
+int b200_mlp_f16_pack(const float *w, int cout, int cin, int ldw, int n_pad, int k_pad, int w_exp, int feat_channels,
+                      void *packed, void *stream);
+/* b200_group_mlp_maxpool in fp16x3: layer 1 (w1[c1,3], b1[c1], on the CUDA cores; w1_norm1 = max_c (|w|_1 of row c),
+ * b1_max = max |b1|), then layers[0..1] on the tensor cores (layers[0].k_pad = c1 rounded up to 32). */
+int b200_group_mlp_maxpool_f16(const float *xyz, const float *new_xyz, const float *rot, const int32_t *idx, int g,
+                               int b, int n, int m, int ns, float radius, const float *w1, const float *b1, int c1,
+                               float w1_norm1, float b1_max, const b200_mlp_layer *layers, float *out, float *out_t,
+                               void *stream);
+/* b200_group_feat_mlp_maxpool in fp16x3: layers[0..2], layers[0] packed with feat_channels = c. */
+int b200_group_feat_mlp_maxpool_f16(const float *xyz, const float *new_xyz, const float *feat_t, const int32_t *idx,
+                                    int b, int n, int m, int ns, int c, float radius, const b200_mlp_layer *layers,
+                                    float *out, float *out_t, void *stream);
+/* Replaces the Conv1d / Conv2d(1x1) [+ BatchNorm + ReLU] stacks over point columns between the geometry ops
+ * (pointnet2/pointnet2_modules.py:409-414, models/modules.py:52-57, 170-177, 215-222): x = [x1[B,c1,n] | x2[B,c2,n]]
+ * through 1..3 layers in one launch, activations resident on the SM; each layer with y != NULL is written
+ * [B, cout, n] (channel-major, like the input).
+ * nheads = 1 or 2: two stacks of the SAME padded shapes (own weights, biases, outputs) over the same input run as one
+ * launch -- layers[0 .. nlayers) is head 0, layers[nlayers .. 2 nlayers) head 1 (OperationNet | ToleranceNet over the
+ * crop features; the two halves of a layer wider than 256 channels). */
+int b200_pointwise_stack_f16(const float *x1, int c1, const float *x2, int c2, int b, int n,
+                             const b200_mlp_layer *layers, int nlayers, int nheads, void *stream);
+
 /* Replaces ball_query(new_xyz[B,M,3], xyz[B,N,3], radius, nsample) -> [B,M,nsample] i32
  * (ball_query.cpp:13-37, ball_query.h:9-10; ball_query_gpu.cu:14-49). */
 int b200_ball_query(const float *new_xyz, const float *xyz, int b, int n, int m, float radius,
