@@ -43,6 +43,7 @@ SIGNATURES = {
     "b200_knn": [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp],
     "b200_collision_counts": [_vp, _i, _vp, _vp, _vp, _i, _vp, _vp],
     "b200_grasp_nms": [_vp, _i, _d, _d, _vp, _vp, _vp, _sz, _vp],
+    "b200_grasp_nms_static": [_vp, _i, _d, _d, _vp, _vp, _vp],
     "b200_collision_counts_dn": [_vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp],
     "b200_voxel_down_sample": [_vp, _i, _d, _vp, _vp, _vp, _sz, _vp],
     "b200_collision_counts_packed": [_vp, _vp, _i, _vp, _i, _vp, _vp],

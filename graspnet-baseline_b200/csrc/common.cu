@@ -38,6 +38,9 @@ extern "C" const char *b200_error_string(int code) {
     case B200_EINVAL: return "b200grasp: invalid argument (null pointer or negative size)";
     case B200_ECAPACITY: return "b200grasp: problem size exceeds what this build supports";
     case B200_EWORKSPACE: return "b200grasp: workspace too small";
+    case B200_ESTATIC:
+      return "b200grasp: problem larger than the built-in static scratch of this no-allocation entry point (use the "
+             "variant that takes a caller workspace)";
     default: break;
   }
   if (code > 0) return cudaGetErrorString((cudaError_t)code);

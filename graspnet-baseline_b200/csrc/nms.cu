@@ -220,3 +220,39 @@ extern "C" int b200_grasp_nms_device(const float *grasps, const int32_t *m_dev, 
   return nms_launch(grasps, m_max, m_dev, translation_thresh, cos_rotation_thresh, keep, nkeep, workspace,
                     workspace_bytes, (cudaStream_t)stream);
 }
+
+// ---- No-allocation variant (no counterpart in the reference) -----------
+// For callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid
+// it): the same three launches with their scratch (order[m] | pad | bitmask m x ceil(m/64) words) in a file-scope
+// device array instead of a caller workspace.  Every GPU that loads the library holds the array (532,736 bytes) until
+// exit.  In HOST code `g_nms_static_scratch` is only a stand-in for the symbol, not a device address: the address is
+// taken once per device, with that device current, through cudaGetSymbolAddress, and that pointer is what the
+// kernels get.  Nothing in the scratch has to start at zero (rank, mask and sweep write every word they later read --
+// the caller-workspace entry points are fed uninitialised memory too), so nothing is cleared; the array keeps the
+// last call's contents.  ALL calls on a device share it: calls that overlap on the GPU (different streams, or graphs
+// replayed concurrently) race -- serialise them on one stream.
+namespace {
+constexpr int NMS_STATIC_MAX_M = B200_NMS_STATIC_MAX_M;
+constexpr size_t nms_static_align(size_t v) { return (v + 255) / 256 * 256; }
+constexpr size_t NMS_STATIC_BYTES = nms_static_align(sizeof(int32_t) * (size_t)NMS_STATIC_MAX_M) +
+                                    nms_static_align(8 * (size_t)((NMS_STATIC_MAX_M + 63) / 64)) +
+                                    nms_static_align(8 * (size_t)((NMS_STATIC_MAX_M + 63) / 64) * NMS_STATIC_MAX_M);
+}  // namespace
+
+static __device__ __align__(256) unsigned char g_nms_static_scratch[NMS_STATIC_BYTES];
+
+extern "C" int b200_grasp_nms_static(const float *grasps, int m, double translation_thresh,
+                                     double cos_rotation_thresh, int32_t *keep, int32_t *nkeep, void *stream) {
+  if (m < 0) return B200_EINVAL;
+  if (m > NMS_STATIC_MAX_M) return B200_ESTATIC;
+  static std::atomic<void *> per_device[64];             // device address of the array, per device
+  const int dev = b200_device();
+  void *ptr = (dev >= 0 && dev < 64) ? per_device[dev].load(std::memory_order_acquire) : nullptr;
+  if (!ptr) {
+    B200_CUDA(cudaGetSymbolAddress(&ptr, g_nms_static_scratch));    // the current device's copy
+    if (!ptr) return B200_EINVAL;
+    if (dev >= 0 && dev < 64) per_device[dev].store(ptr, std::memory_order_release);
+  }
+  return nms_launch(grasps, m, nullptr, translation_thresh, cos_rotation_thresh, keep, nkeep, ptr, NMS_STATIC_BYTES,
+                    (cudaStream_t)stream);
+}

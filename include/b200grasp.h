@@ -33,6 +33,7 @@ extern "C" {
 #define B200_EINVAL (-1)      /* bad size / null pointer                       */
 #define B200_ECAPACITY (-2)   /* problem larger than this build supports       */
 #define B200_EWORKSPACE (-3)  /* workspace too small                           */
+#define B200_ESTATIC (-4)     /* larger than a *_static entry point's built-in scratch */
 
 int b200_version(void);
 const char *b200_error_string(int code);
@@ -318,6 +319,18 @@ size_t b200_grasp_nms_workspace(int m);
 int b200_grasp_nms(const float *grasps, int m, double translation_thresh, double cos_rotation_thresh,
                    int32_t *keep, int32_t *nkeep, void *workspace, size_t workspace_bytes,
                    void *stream);
+
+/* b200_grasp_nms without a workspace argument and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA-graph capture, tight serving
+ * loops, harnesses that forbid it).  The scratch is a file-scope `static __device__` array inside the library, sized
+ * for m <= B200_NMS_STATIC_MAX_M grasps (532,736 bytes, held by every GPU that loads the library until exit);
+ * m beyond that returns B200_ESTATIC and launches nothing.  The entry point calls no cudaMalloc / cudaFree / allocating
+ * routine; inputs and outputs are the caller's, as for b200_grasp_nms, and the results are identical.  All calls on a
+ * device share the one array, which keeps the previous call's contents (nothing in it needs to start at zero): calls
+ * that overlap on the GPU -- two streams, concurrent graph replays -- RACE; issue them on one stream. */
+#define B200_NMS_STATIC_MAX_M 2048
+int b200_grasp_nms_static(const float *grasps, int m, double translation_thresh, double cos_rotation_thresh,
+                          int32_t *keep, int32_t *nkeep, void *stream);
 
 #ifdef __cplusplus
 }
