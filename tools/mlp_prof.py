@@ -63,11 +63,23 @@ with torch.no_grad():
         run()
 torch.cuda.synchronize()
 NG = 2
-buf = (ctypes.c_ulonglong * ((NG + 1 if f16 else 3) * 16 * 8))()
+xyzp = f16 and which in ("crop", "sa1")
+buf = (ctypes.c_ulonglong * ((5 if f16 else 3) * 16 * 8))()
 assert (prof.b200_mlp_f16_read_profile if f16 else prof.b200_mlp_read_profile)(buf) == 0
 a = np.array(buf, dtype=np.int64).reshape(-1, 16, 8)
 t0 = a[0, 0, 0]
-if f16:
+if xyzp:
+    t0 = a[0, 0, 0]
+    print(which, "xyz_pipe_kernel, cycles relative to the issuer's first tile")
+    print("A0/A1: tile start, acc0 ready, [slab: start, published] x 2, [pool of t-1: acc1 ready, done]")
+    print("P1/P2: start, -, -, barrier passed, combine | source done, -, [pool: acc1 ready, done]")
+    print("MMA  : -, -, layer-2 slab 0..3 issued at, layer 2 committed, layer 1 (this tile) committed")
+    for t in range(3, 9):
+        for r, nm in enumerate(("A0 ", "A1 ", "P1 ", "P2 ", "MMA")):
+            n = 8
+            print("tile %2d %s %s" % (t, nm, " ".join("%7d" % (a[r, t, e] - t0 if a[r, t, e] else 0) for e in range(n))))
+    print("cycles per tile (issuer, tiles 3..11): %.0f" % ((a[4, 11, 6] - a[4, 3, 6]) / 8.0))
+elif f16:
     print(which, arith, "cycles relative to start; group rows = that group's k-th tile (tile 2k + g): start, gathered (before turn wait), "
           "source slabs out, acc(last-1) ready, mid epilogues out, acc(last) ready, last epilogue read, combine done; "
           "mma rows (per tile): first/last slab ready of the last two layers")

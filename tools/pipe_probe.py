@@ -8,6 +8,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import bench
 import b200grasp
+if os.environ.get("B200_ARITH"):
+    b200grasp.fused_modules.ARITH = os.environ["B200_ARITH"]
+print("arith", b200grasp.fused_modules.ARITH)
 net = bench.make_net("cuda")
 P = 640
 host = [bench.scene_cloud(5000 + i) for i in range(P)]
