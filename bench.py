@@ -35,6 +35,13 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+def log(msg):
+    """progress marker on stderr (stdout carries the one JSON line)"""
+    sys.stderr.write("[bench %.1fs] %s\n" % (time.perf_counter() - _T0, msg))
+    sys.stderr.flush()
+
+
+_T0 = time.perf_counter()
 METRIC = "scenes/sec (20k pts, 1024 seeds, collision+NMS)"
 UNIT = "scenes/s"
 WORKLOAD = ("cfg2: GraspNet inference (seeded random weights, eval), batch 1, 20000 pts -> SA 2048/1024/512/256 -> "
@@ -105,6 +112,18 @@ def fused_mlp_report(sc, timed, dev):
                                      "roofline": {"bound": "tensor", "achieved": round(tf, 1), "peak": round(peak / 2, 1),
                                                   "unit": "TFLOP/s", "frac": round(tf / (peak / 2), 4)}})
 
+        # the same two modules in fp16x3 arithmetic (csrc/mlp_f16.cu: xyz_pipe_kernel), the path the engine runs
+        f1, l1h = sa1._fused.get_f16()
+        fc, lch = crop._fused.get_f16()
+        for name, fn in (("sa1", lambda: ops.group_mlp_maxpool_f16(xyz, new_xyz, idx1, f1, l1h, radius=0.04)),
+                         ("cloudcrop", lambda: ops.group_mlp_maxpool_f16(xyz, seeds, idxc, fc, lch, rot=rot))):
+            ms = timed(fn, n, 3) / n
+            tf = mma_flops[name] * 3 / (ms * 1e-3) / 1e12
+            rep["cases"].append({"module": name, "arith": "f16x3", "passes": 3, "ms": round(ms, 4),
+                                 "fp32_equivalent_tflops": round(flops[name] / (ms * 1e-3) / 1e12, 1),
+                                 "roofline": {"bound": "tensor", "achieved": round(tf, 1), "peak": round(peak, 1),
+                                              "unit": "TFLOP/s", "frac": round(tf / peak, 4)}})
+
         def composed_sa1():
             g, _ = sa1.grouper(xyz, new_xyz, None)
             return F.max_pool2d(sa1.mlp_module(g), kernel_size=[1, 64])
@@ -123,7 +142,8 @@ def fused_mlp_report(sc, timed, dev):
         rep["composed_ms"] = {"what": "same modules unfused: b200 group ops + torch SharedMLP (cuDNN, TF32 allowed) + "
                                       "max_pool2d; the neighbourhood queries they repeat are timed alone and subtracted",
                               "sa1_plus_cloudcrop": round((timed(composed_sa1, n, 3) + timed(composed_crop, n, 3)) / n - tq, 4)}
-    rep["fused_ms_sa1_plus_cloudcrop_3xtf32"] = round(sum(c["ms"] for c in rep["cases"] if c["passes"] == 3), 4)
+    rep["fused_ms_sa1_plus_cloudcrop_3xtf32"] = round(sum(c["ms"] for c in rep["cases"] if c["passes"] == 3 and "arith" not in c), 4)
+    rep["fused_ms_sa1_plus_cloudcrop_f16x3"] = round(sum(c["ms"] for c in rep["cases"] if c.get("arith") == "f16x3"), 4)
     return rep
 
 
@@ -191,28 +211,61 @@ def cpu_inference(net, oracle, torch, cloud):
     return rows, mask, free[oracle.grasp_nms(free)]
 
 
+def cpu_modules():
+    """The network's module classes for the CPU port WITHOUT loading libb200grasp.so: the package's module files
+    (graspnet.py, fused_modules.py, pointnet2_utils.py, synth.py -- the reference-shaped composed path) are imported
+    under a private package name whose `_abi` is a stub with no library behind it, and whose pointnet2 `_ext` is the
+    C oracle.  Nothing of the CUDA product is mapped into the process that times the CPU baseline."""
+    import importlib
+    import types
+    name = "b200grasp_cpu"
+    if name in sys.modules:
+        return sys.modules[name]
+    pkg_dir = os.path.join(ROOT, "graspnet-baseline_b200")
+    pkg = types.ModuleType(name)
+    pkg.__path__ = [pkg_dir]
+    pkg.__package__ = name
+    sys.modules[name] = pkg
+
+    class _NoLib:
+        def __getattr__(self, k):
+            raise RuntimeError("the CPU baseline must not call the CUDA library (%s)" % k)
+
+    abi = types.ModuleType(name + "._abi")
+    abi.lib, abi.LIB_PATH, abi.MlpLayer = _NoLib(), None, None
+    abi.check = lambda code, what: None
+    sys.modules[name + "._abi"] = abi
+    pkg._abi = abi
+    for sub in ("ops", "pointnet2_utils", "synth", "fused_modules", "graspnet"):
+        setattr(pkg, sub, importlib.import_module(name + "." + sub))
+    return pkg
+
+
+def make_net_cpu(pkg):
+    net = pkg.graspnet.GraspNet(input_feature_dim=0, num_view=300, num_angle=12, num_depth=4, cylinder_radius=0.05,
+                                hmin=-0.02, hmax_list=HMAX, is_training=False)
+    pkg.synth.fill_state_dict(net, WEIGHT_SEED)
+    return net.eval()
+
+
 def time_cpu(steps, warmup):
     # the C port is OpenMP-parallel; torchrun exports OMP_NUM_THREADS=1, which would make this a 1-thread run
     os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
     import torch
     import oracle
-    import b200grasp
-    from b200grasp import fused_modules, pointnet2_utils
     oracle.cpu.build()
     torch.set_num_threads(os.cpu_count() or 1)
-    net = make_net("cpu")
-    cloud = scene_cloud(1234)
-    fused, ext = fused_modules.FUSED, pointnet2_utils._ext
-    fused_modules.FUSED, pointnet2_utils._ext = False, OracleOps(oracle, torch)
-    try:
-        for _ in range(max(warmup, 1)):
-            cpu_inference(net, oracle, torch, cloud)
-        t0 = time.perf_counter()
-        for _ in range(steps):
-            out = cpu_inference(net, oracle, torch, cloud)
-        dt = time.perf_counter() - t0
-    finally:
-        fused_modules.FUSED, pointnet2_utils._ext = fused, ext
+    pkg = cpu_modules()
+    pkg.fused_modules.FUSED = False
+    pkg.pointnet2_utils._ext = OracleOps(oracle, torch)
+    net = make_net_cpu(pkg)
+    cloud = pkg.synth.tabletop_cloud(20000, 1234)
+    for _ in range(warmup):
+        cpu_inference(net, oracle, torch, cloud)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        out = cpu_inference(net, oracle, torch, cloud)
+    dt = time.perf_counter() - t0
     return steps / dt, dt / steps, out
 
 
@@ -276,10 +329,11 @@ class Clocks(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(self.sm), "source": self.source}
 
 
-# per-launch DRAM bytes from the committed ncu --set full capture (profiles/r01_top_kernels_full.txt)
-NCU_TRAFFIC = {"fps_sa1": 257536,
-               # the CloudCrop launch of group_mlp_maxpool_kernel in profiles/r01_infer_kernels_full.txt (read + write)
-               "group_mlp_maxpool_cloudcrop": 1720320}
+# per-launch DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) from the ncu --set full captures committed
+# under profiles/ (a bench run cannot profile itself; the `traffic_source` key of the roofline names the file)
+NCU_TRAFFIC = {"fps_sa1": 257536,                        # profiles/r01_top_kernels_full.txt
+               # the CloudCrop launch of xyz_pipe_kernel, captured this round: profiles/r02_mlp_f16_ncu.txt
+               "group_mlp_maxpool_cloudcrop": 1582592}
 
 # ---------------------------------------------------------------- algorithmic bytes
 
@@ -411,6 +465,65 @@ def inference_op_times(torch, b200grasp, net, cloud, flush, reps=7):
             "torch_layers_and_launch_gaps_ms": round(total - ours, 4), "ops": rows}
 
 
+# ---------------------------------------------------------------- extra legs (rank 0, N = 1)
+
+def nms_leg(torch, b200grasp, timed_local, dev):
+    """GraspGroup.nms at M = 1024 with MANY survivors (the headline scene keeps 23 of 1024: its in-graph NMS sees a
+    few dozen rows).  Grasps spread over a whole table-top cloud: few pairs are within 3 cm AND 30 degrees."""
+    from b200grasp import ops, synth
+    cloud = synth.tabletop_cloud(20000, 77)
+    out = []
+    for name, pts in (("spread over the scene", cloud), ("on 64 scene points (heavy suppression)", cloud[:64])):
+        g = torch.from_numpy(synth.synthetic_grasps(pts, 1024, 5)).to(dev)
+        keep, nkeep = ops.grasp_nms(g, 0.03, math.cos(30.0 / 180.0 * math.pi))
+        n = 20
+        ms = timed_local(lambda: ops.grasp_nms(g, 0.03, math.cos(30.0 / 180.0 * math.pi)), n, 3) / n
+        out.append({"grasps": 1024, "placement": name, "kept": int(nkeep.item()), "ms": round(ms, 4),
+                    "pairs_per_s": round(1024 * 1023 / 2 / (ms * 1e-3), 0)})
+    return {"what": "b200_grasp_nms alone (rank + 64x64 bitmask tiles in fp64 + single-CTA sweep), L2 flushed", "cases": out}
+
+
+def cfg4_leg(torch, b200grasp, timed_local, dev, peak):
+    """BASELINE.json configs[3]: 200k points, FPS to 4096 seeds, 4096 grasps collision-checked against the FULL
+    cloud (no voxelisation), NMS of the 4096.  Parity of these shapes: tests/test_gpu_full_size.py."""
+    from b200grasp import ops, synth
+    n_pts, n_seed = 200000, 4096
+    cloud64 = synth.tabletop_cloud(n_pts, 9, extent=0.6, dtype=np.float64)
+    cloud = torch.from_numpy(cloud64.astype(np.float32))[None].to(dev)
+    g_host = synth.synthetic_grasps(cloud64, n_seed, 2)
+    T = torch.from_numpy(np.ascontiguousarray(g_host[:, 13:16], dtype=np.float64)).to(dev)
+    R = torch.from_numpy(np.ascontiguousarray(g_host[:, 4:13], dtype=np.float64)).to(dev)
+    det = object.__new__(b200grasp.ModelFreeCollisionDetector)      # the detector's own half-space bounds, no scene
+    det.finger_width, det.finger_length = 0.01, 0.06                # (utils/collision_detector.py:29-30)
+    thr = torch.from_numpy(np.ascontiguousarray(det._thresholds(b200grasp.GraspGroup(g_host), 0.05))).to(dev)
+    scene = torch.from_numpy(cloud64).to(dev)
+    g = torch.from_numpy(g_host).to(dev)
+    n = 5
+    fps_ms = timed_local(lambda: ops.furthest_point_sampling(cloud, n_seed), n, 2) / n
+    inds = ops.furthest_point_sampling(cloud, n_seed)
+    seeds = ops.gather_xyz(cloud, inds, transposed=False)
+    grid_ms = timed_local(lambda: ops.query_grid_build(cloud, 0.026), n, 2) / n
+    grid = ops.query_grid_build(cloud, 0.026)
+    ball_ms = timed_local(lambda: ops.ball_query(seeds, cloud, 0.04, 64, grid=grid), n, 2) / n
+    col_ms = timed_local(lambda: ops.collision_counts(scene, T, R, thr), n, 2) / n
+    nms_ms = timed_local(lambda: ops.grasp_nms(g, 0.03, math.cos(30.0 / 180.0 * math.pi)), n, 2) / n
+    pairs = float(n_pts) * n_seed
+    col_bytes = n_pts * 24 + n_seed * (3 + 9 + 10) * 8 + n_seed * 24
+    return {"workload": "cfg4: 200000 points (table-top, 1.2 m), FPS -> 4096, grid ball query r=0.04 ns=64 of the 4096 seeds, "
+                        "4096 grasps x full cloud collision (fp64), NMS of 4096",
+            "fps_ms": round(fps_ms, 4), "fps_ns_per_sample": round(fps_ms * 1e6 / (n_seed - 1), 1),
+            "grid_build_ms": round(grid_ms, 4), "ball_query_ms": round(ball_ms, 4),
+            "collision_ms": round(col_ms, 4), "collision_pair_tests_per_s": round(pairs / (col_ms * 1e-3), 0),
+            "collision_fp64_flops_per_s": round(pairs * 30 / (col_ms * 1e-3), 0),
+            "collision_roofline": {"bound": "hbm", "achieved": round(col_bytes / (col_ms * 1e-3) / 1e9, 2), "peak": peak,
+                                   "unit": "GB/s", "frac": round(col_bytes / (col_ms * 1e-3) / 1e9 / peak, 5),
+                                   "alg_bytes": col_bytes,
+                                   "note": "819 M point-grasp tests of ~30 fp64 operations on 5 MB of input: bound by "
+                                           "the fp64 pipe, not by HBM (the frac says how far from bandwidth-bound it is)"},
+            "nms_ms": round(nms_ms, 4),
+            "scene_ms_sum": round(fps_ms + grid_ms + ball_ms + col_ms + nms_ms, 4)}
+
+
 # ---------------------------------------------------------------- our arm
 
 def run_ours(args, rank, world, local_rank):
@@ -483,16 +596,25 @@ def run_ours(args, rank, world, local_rank):
     pool_host[0] = cloud_host
     pool = torch.from_numpy(np.stack(pool_host)).to(dev)
 
+    WINDOWS = 9
+
     def timed_stream(run, steps, warmup):
+        """WINDOWS back-to-back timed regions of EXACTLY `steps` scenes each (one CUDA-event pair per region, barrier +
+        synchronize on both sides, max over ranks); returns (median, min, max) milliseconds per region.  At the
+        driver's --steps 20 one region is ~6 ms: a single one is a noisy sample (round 1: 9-13 % spread)."""
         run(warmup, 0)
-        barrier()
-        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        t0.record(stream)
-        run(steps, warmup)
-        pipe.join()
-        t1.record(stream)
-        barrier()
-        return b200grasp.sharding.whole_job_throughput(steps, t0.elapsed_time(t1), device=dev)[1]
+        ms, first = [], warmup
+        for _ in range(WINDOWS):
+            barrier()
+            t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0.record(stream)
+            run(steps, first)
+            pipe.join()
+            t1.record(stream)
+            barrier()
+            ms.append(b200grasp.sharding.whole_job_throughput(steps, t0.elapsed_time(t1), device=dev)[1])
+            first += steps
+        return float(np.median(ms)), min(ms), max(ms)
 
     def resident_stream(count, first):
         for i in range(first, first + count):
@@ -501,8 +623,9 @@ def run_ours(args, rank, world, local_rank):
     def host_stream(count, first):                          # e2e: host cloud in, host results out, every scene
         return pipe.run(pool_host[i % POOL] for i in range(first, first + count))
 
+    log("headline stream")
     clocks.start()                                          # samples only while the timed region below runs
-    total_ms = timed_stream(resident_stream, args.steps, max(args.warmup, PIPE_DEPTH))
+    total_ms, total_min, total_max = timed_stream(resident_stream, args.steps, max(args.warmup, PIPE_DEPTH))
     clk = clocks.summary()
     launches = pipe.launches                                # our kernels per scene (library counter at capture)
     # the resident stream really processed the pool's clouds: a slot fed from HBM returns what the same cloud fed
@@ -513,7 +636,9 @@ def run_ours(args, rank, world, local_rank):
         if not (a["nrows"] == b["nrows"] and a["nrows"] > 0 and np.array_equal(a["mask"], b["mask"])
                 and np.array_equal(a["kept"], b["kept"])):
             raise SystemExit("bench: device-fed and host-fed scenes of the stream disagree")
-    e2e_ms = timed_stream(host_stream, args.steps, max(args.warmup, PIPE_DEPTH))
+    log("e2e stream")
+    e2e_ms, e2e_min, e2e_max = timed_stream(host_stream, args.steps, max(args.warmup, PIPE_DEPTH))
+    log("latency")
     lat_ms = timed(eng.run_graph, min(args.steps, 50), args.warmup) / min(args.steps, 50)   # one scene alone, L2 flushed
     lat_e2e_ms = timed(lambda: eng.infer(None), min(args.steps, 50), args.warmup) / min(args.steps, 50)
 
@@ -528,6 +653,7 @@ def run_ours(args, rank, world, local_rank):
         mask = det.detect(gg, approach_dist=0.05, collision_thresh=0.01)
         return gg, mask, gg[~mask].nms(device=dev)
 
+    log("call sequence")
     seq_steps = min(args.steps, 20)
     seq_ms = timed(call_sequence, seq_steps, args.warmup) / seq_steps
     h2d, d2h = eng.host_in.numel(), eng.host_out.numel()
@@ -539,6 +665,7 @@ def run_ours(args, rank, world, local_rank):
     infer_counts = {"decoded_grasps": int(got["nrows"]), "colliding": int(got["mask"].sum()),
                     "kept_after_nms": int(got["kept"].shape[0])}
 
+    log("geometry path")
     # ================= geometry ops alone (pipeline.GeometryScene: stand-in features instead of the MLPs)
     gsteps = min(args.steps, 20)
     geo_total_ms = timed(sc.run_graph, gsteps, args.warmup)
@@ -592,6 +719,7 @@ def run_ours(args, rank, world, local_rank):
 
     if rank != 0:
         return None
+    log("legacy leg")
     # ---- the reference's legacy CUDA ops on this same GPU (geometry ops only; rank 0)
     legacy = None
     ext = load_legacy() if world == 1 and not args.lean else None
@@ -630,6 +758,22 @@ def run_ours(args, rank, world, local_rank):
                        "ours_whole_step_graph_latency_ms": round(lat_ms, 4),
                        "ours_whole_step_stream_ms_per_scene": round(total_ms / args.steps, 4),
                        "forward_speedup_vs_graph_latency": round(legf_ms / lat_ms, 2)})
+        # the reference's END-TO-END scene as its scripts run it (test.py:86-96, demo_pointcloud.py:228-249): forward on
+        # its legacy CUDA ops, pred_decode, D2H, ModelFreeCollisionDetector (open3d voxel + numpy detect) and nms on
+        # the host.  The host part is timed with the C port of oracle/post.py (the verbatim numpy detect() takes ~1.3 s
+        # per scene; the port is what the CPU baseline uses too) -- conservative for the reference.
+        import oracle
+        oracle.cpu.build()
+        rows_h = gg.grasp_group_array.astype(np.float32)
+        t0 = time.perf_counter()
+        for _ in range(3):
+            scene_h = oracle.voxel_down_sample(cloud_host.astype(np.float64), 0.01)
+            m_h = oracle.collision_detect(scene_h, rows_h, 0.01, 0.05, 0.01)
+            oracle.grasp_nms(rows_h[~m_h])
+        post_ms = (time.perf_counter() - t0) / 3 * 1e3
+        leg_e2e_ms = legf_ms + post_ms
+        legacy.update({"legacy_host_postprocess_ms": round(post_ms, 3), "legacy_e2e_ms_per_scene": round(leg_e2e_ms, 3)})
+    log("batch64")
     # ---- config 3 shape: 64 scenes per graph launch on this GPU (throughput mode; extra, not the headline)
     batch64 = None
     if world == 1 and not args.no_batch64 and not args.lean:
@@ -670,9 +814,18 @@ def run_ours(args, rank, world, local_rank):
                                             "launch on one GPU", "ms_per_64_scenes": round(i_ms, 4),
                                 "scenes_per_s": round(64.0 / (i_ms * 1e-3), 1), "gpu_launches_per_step": eng64.launches}
         del eng64
+    log("fused mlp report + extra legs")
     # ---- SURVEY.md 8(f) f1 (extra, not part of the step): group -> shared MLP -> max-pool fused on the tensor cores
     fused_mlp = fused_mlp_report(sc, timed, dev) if world == 1 and not args.lean else None
+    extra = {}
+    if world == 1 and not args.lean:
+        log("nms leg")
+        extra["nms_1024"] = nms_leg(torch, b200grasp, timed_local, dev)
+        log("cfg4 leg")
+        extra["cfg4"] = cfg4_leg(torch, b200grasp, timed_local, dev, peaks()[0])
+        log("inference op times")
     infer_ops = inference_op_times(torch, b200grasp, net, eng.cloud, flush) if not args.lean else None
+    log("per-kernel pass")
     # ---- per-kernel pass (rank 0): CUDA events around every launch, L2 flushed before each pass
     per = {}
     reps = 9
@@ -717,19 +870,33 @@ def run_ours(args, rank, world, local_rank):
                                                  crop.nsample)
         layers = crop._fused.get()
         n_it = 20
-        crop_ms = timed_local(lambda: b200grasp.ops.group_mlp_maxpool(eng.cloud, seeds, cidx, layers, rot=rot9,
-                                                                      passes=crop.passes), n_it, 3) / n_it
+        f16 = crop.passes == 3 and b200grasp.fused_modules.ARITH == "f16x3"
+        if f16:
+            first, l16 = crop._fused.get_f16()
+            run_crop = lambda: b200grasp.ops.group_mlp_maxpool_f16(eng.cloud, seeds, cidx, first, l16, rot=rot9)
+        else:
+            run_crop = lambda: b200grasp.ops.group_mlp_maxpool(eng.cloud, seeds, cidx, layers, rot=rot9, passes=crop.passes)
+        crop_ms = timed_local(run_crop, n_it, 3) / n_it
     crop_rows = cidx.shape[0] * cidx.shape[2] * cidx.shape[3]
-    mma_flops = 2.0 * crop_rows * (64 * 128 + 128 * 256) * crop.passes      # tf32 tensor-core flops actually issued
+    # tensor-core flops actually issued: three products per K step (hi.hi + hi.lo + lo.hi)
+    mma_flops = 2.0 * crop_rows * (64 * 128 + 128 * 256) * crop.passes
     tpeak, twhich = tensor_peak()
+    if not f16:
+        tpeak = tpeak / 2                                                   # kind::tf32 runs at half the f16 / bf16 rate
     tf = mma_flops / (crop_ms * 1e-3) / 1e12
-    roof = {"bound": "tensor", "kernel": "group_mlp_maxpool (CloudCrop: 262144 rows x 3->64->128->256, 3xTF32)",
-            "achieved": round(tf, 1), "peak": round(tpeak / 2, 1), "unit": "TFLOP/s", "frac": round(tf / (tpeak / 2), 4),
-            "traffic": NCU_TRAFFIC["group_mlp_maxpool_cloudcrop"], "ms": round(crop_ms, 4),
-            "peak_source": twhich + " bf16 / 2 (tf32 runs at half the bf16 rate)",
-            "algorithmic": "flops = 2 x rows x (64x128 + 128x256) x 3 passes of tcgen05.mma kind::tf32 per launch "
-                           "(the K=3 first layer runs on the CUDA cores and is not counted); fp32-equivalent useful "
-                           "rate = a third of achieved",
+    roof = {"bound": "tensor",
+            "kernel": "group_mlp_maxpool (CloudCrop: 262144 rows x 3->64->128->256, %s)" % ("fp16x3, xyz_pipe_kernel" if f16 else "3xTF32"),
+            "achieved": round(tf, 1), "peak": round(tpeak, 1), "unit": "TFLOP/s", "frac": round(tf / tpeak, 4),
+            "traffic": NCU_TRAFFIC["group_mlp_maxpool_cloudcrop"],
+            "traffic_source": "profiles/r02_mlp_f16_ncu.txt (ncu --set full of this launch, this round); algorithmic "
+                              "bytes = cloud + seeds + rotations + index lists read once = 1.34 MB, the output (4 MB) "
+                              "stays in L2",
+            "ms": round(crop_ms, 4),
+            "peak_source": twhich + (" bf16 cuBLAS burst; tcgen05 kind::f16 measured at 2156 TFLOP/s issue-bound "
+                                     "(profiles/r02_mma_rate.txt)" if f16 else " bf16 / 2 (tf32 runs at half the rate)"),
+            "algorithmic": "flops = 2 x rows x (64x128 + 128x256) x 3 products of tcgen05.mma per launch (the K=3 first "
+                           "layer runs on the CUDA cores and is not counted); fp32-equivalent useful rate = a third of "
+                           "achieved",
             "note": "dominant kernel of the headline stream by SM-time; the largest kernel of a single scene's latency "
                     "is fps_sa1 (latency_kernel)",
             "latency_kernel": fps_roof,
@@ -741,10 +908,20 @@ def run_ours(args, rank, world, local_rank):
     e2e = world * args.steps / (e2e_ms * 1e-3)
     line = {"metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(total_ms / args.steps, 4), "higher_is_better": True,
+            "timing": {"windows": WINDOWS, "what": "median of %d back-to-back timed regions of exactly `steps` scenes each; "
+                                                    "value = steps / median" % WINDOWS,
+                       "window_ms": {"median": round(total_ms, 4), "min": round(total_min, 4), "max": round(total_max, 4)},
+                       "scenes_per_s": {"median": round(value, 1), "min": round(world * args.steps / (total_max * 1e-3), 1),
+                                        "max": round(world * args.steps / (total_min * 1e-3), 1)}},
+            "latency": {"single_scene_ms": round(lat_ms, 4), "single_scene_e2e_ms": round(lat_e2e_ms, 4),
+                        "what": "one scene alone through one GraspNetEngine graph, L2 flushed before every iteration; "
+                                "e2e = host cloud in (pinned), host results out"},
             "scaling": "weak", "vs_baseline": None, "dtype": "f32 (fp64 collision/NMS, int32 indices)",
             "data": "synthetic",
             "config": {"workload": WORKLOAD, "scenes_per_step_per_gpu": 1, "weights": "synth.fill_state_dict(seed %d), eval-mode BatchNorm" % WEIGHT_SEED,
-                       "grouped_mlp_arithmetic": "3xTF32 on tcgen05 (fp32-grade); the other layers exact fp32 FMAs (csrc/pointwise.cu)",
+                       "grouped_mlp_arithmetic": "fp16x3 on tcgen05 kind::f16 (hi|lo fp16 operands, exact power-of-two scaling, "
+                                                 "fp32 accumulate: fp32-grade) for the grouped MLPs and the 1x1-conv stacks "
+                                                 "(csrc/mlp_f16.cu)",
                        "execution": "GraspNetPipeline: %d scenes in flight, each a batch-1 CUDA graph (GraspNetEngine, "
                                     "forked over streams by data dependence) on its own stream" % PIPE_DEPTH,
                        "l2": "inputs rotate through a pool of %d different clouds (%d MB > 126 MB L2) resident in HBM; "
@@ -756,6 +933,7 @@ def run_ours(args, rank, world, local_rank):
             "clocks": clk, "gpu_launches": launches * args.steps,
             "e2e": {"value": round(e2e, 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": round(e2e_ms / args.steps, 4),
+                    "window_ms": {"median": round(e2e_ms, 4), "min": round(e2e_min, 4), "max": round(e2e_max, 4)},
                     "api": "GraspNetPipeline.run(clouds): per scene the host cloud is copied into a pinned buffer and from "
                            "there into the slot's static input, one graph launch (network + pred_decode + voxel + "
                            "collision + NMS on the device), one copy of the results (decoded count | mask | kept rows | "
@@ -765,6 +943,17 @@ def run_ours(args, rank, world, local_rank):
                     "call_sequence": "net(end_points), pred_decode, GraspGroup, ModelFreeCollisionDetector(...).detect, "
                                      ".nms() through the drop-ins, one after the other as test.py:86-96 (eager, "
                                      "numpy round trips); results equal the engine's (checked in this run)"},
+            "vs_legacy_cuda": None if not legacy or "legacy_e2e_ms_per_scene" not in legacy else {
+                "what": "north_star's target (>= 10x the reference legacy-CUDA end-to-end scenes/s on one B200): the "
+                        "reference's scene = GraspNet forward on its own pointnet2._ext (built unmodified for sm_100, "
+                        "torch / cuDNN layers, TF32 allowed) + host post-processing (C port of detect() + nms: "
+                        "conservative, the verbatim numpy is slower), against this package's e2e stream and latency",
+                "legacy_e2e_scenes_per_s": round(1e3 / legacy["legacy_e2e_ms_per_scene"], 2),
+                "ours_e2e_scenes_per_s": round(e2e, 2),
+                "e2e_ratio": round(e2e * legacy["legacy_e2e_ms_per_scene"] / 1e3, 1),
+                "latency_ratio": round(legacy["legacy_e2e_ms_per_scene"] / lat_e2e_ms, 1),
+                "forward_only_ratio_vs_stream": round(legacy["legacy_forward_ms"] / (total_ms / args.steps), 1)},
+            "nms_1024": extra.get("nms_1024"), "cfg4": extra.get("cfg4"),
             "roofline": roof, "legacy_cuda": legacy, "batch64": batch64, "fused_mlp": fused_mlp,
             "inference_ops": infer_ops,
             "geometry_path": {"what": "the geometry ops + post-processing alone (pipeline.GeometryScene: stand-in "
@@ -807,14 +996,16 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return 0
-        args.steps = min(args.steps, 40)                    # bounded sample: a scene takes ~0.3-1 s on the host cores
-        args.warmup = min(args.warmup, 2)
+        # the driver's --steps / --warmup are honoured (a scene takes ~0.3 s on 16 cores: the default 400 + 16 run in
+        # about two minutes); only an absurd request is bounded
+        args.steps = min(args.steps, 600)
         sps, sec, _ = time_cpu(args.steps, args.warmup)
         cores = os.cpu_count()
         cb = {"value": round(sps, 4), "unit": UNIT, "cores": cores, "kind": "port",
               "sample": "%d whole scenes of the cfg2 workload: the network's reference op sequence with the pointnet2 ops "
                         "answered by oracle/geom_oracle.c (OpenMP) and the layers by torch CPU (all threads), then "
-                        "pred_decode / voxel / collision / NMS restated in oracle/post.py" % args.steps}
+                        "pred_decode / voxel / collision / NMS restated in oracle/post.py; a CPU PORT (the reference "
+                        "has no CPU implementation of its pointnet2 ops), libb200grasp.so is not loaded" % args.steps}
         emit({"metric": METRIC, "value": round(sps, 4), "unit": UNIT, "n_gpus": world, "steps": args.steps,
                           "warmup": args.warmup, "ms_per_step": round(sec * 1e3, 3), "higher_is_better": True,
                           "scaling": "weak", "vs_baseline": None, "dtype": "f32 (fp64 collision/NMS, int32 indices)", "data": "synthetic",

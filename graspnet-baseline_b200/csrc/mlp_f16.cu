@@ -735,7 +735,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_f16_kernel(const Params p) {
       }
     } else {
       // ---- any depth, one accumulator per layer:  S(0);  tile t:  E_0(t) .. E_{last-1}(t) | S(t+1) | last(t) | combine(t)
-      // (with aliased accumulators -- layer 2 in layer 0's columns -- S(t+1) follows last(t))
+      // (with aliased accumulators -- layer 2 in layer 0's columns -- or a single layer, S(t+1) follows last(t))
       float bn = 0.f;
       int en = 0;
       gather_a(0); gather_b();
@@ -761,7 +761,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_f16_kernel(const Params p) {
         if (pr && t >= 0) PROF(pair, t, 2);
 #pragma unroll 1
         for (int h = 0; h < 2; ++h) {                                 // S(t+1) before last(t), or after it (aliased)
-          if (h == (p.alias ? 1 : 0) && t + 1 < ntile) {
+          // (the next tile's source slabs go out BEFORE this tile's last layer is read, except when layer 0's
+          // accumulator is the one the tensor core is waiting to get back -- aliased columns, or a single-layer
+          // stack: then a source longer than the ring would wait for MMAs that wait for this read)
+          if (h == ((p.alias || last == 0) ? 1 : 0) && t + 1 < ntile) {
             prepare(t + 1, bn); en = warp_scale_exp(bn);
             emit_source(en);
             gather_a(t + 2); gather_b();

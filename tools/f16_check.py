@@ -55,7 +55,7 @@ def ref_grouped(xyz, new_xyz, idx, folded, radius=0.0, rot=None, feats=None):
 
 def main():
     which = sys.argv[1:] or ["crop", "sa1", "sa2", "sa3", "dense"]
-    B = 1
+    B = int(os.environ.get("B200_B", "1"))
     xyz = torch.from_numpy(np.stack([b200grasp.synth.tabletop_cloud(20000, 5 + i) for i in range(B)])).cuda()
     torch.manual_seed(0)
     inds = ops.furthest_point_sampling(xyz, 2048)
