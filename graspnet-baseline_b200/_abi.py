@@ -43,6 +43,10 @@ SIGNATURES = {
     "b200_knn": [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp],
     "b200_collision_counts": [_vp, _i, _vp, _vp, _vp, _i, _vp, _vp],
     "b200_grasp_nms": [_vp, _i, _d, _d, _vp, _vp, _vp, _sz, _vp],
+    "b200_label_object_table_set": [_vp, _i, _vp, _vp, _vp, _vp, ctypes.POINTER(_f)],
+    "b200_label_view_stats": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _vp, _vp, _vp],
+    "b200_label_view_scores": [_vp, _vp, ctypes.c_longlong, _vp, _vp, _vp],
+    "b200_label_top_gather": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _vp],
     "b200_grasp_nms_static": [_vp, _i, _d, _d, _vp, _vp, _vp],
     "b200_collision_counts_dn": [_vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp],
     "b200_voxel_down_sample": [_vp, _i, _d, _vp, _vp, _vp, _sz, _vp],
@@ -81,6 +85,8 @@ lib.b200_voxel_down_sample_workspace.argtypes = [_i]
 lib.b200_voxel_down_sample_workspace.restype = _sz
 lib.b200_collision_mask_workspace.argtypes = [_i]
 lib.b200_collision_mask_workspace.restype = _sz
+lib.b200_label_object_table_bytes.argtypes = [_i]
+lib.b200_label_object_table_bytes.restype = _sz
 lib.b200_mlp_f16_packed_bytes.argtypes = [_i, _i]
 lib.b200_mlp_f16_packed_bytes.restype = _sz
 lib.b200_query_grid_workspace.argtypes = [_i, _i]
@@ -100,7 +106,7 @@ lib.b200_fps_set_multi.restype = None
 lib.b200_fps_set_speculation.argtypes = [_i]
 lib.b200_fps_set_speculation.restype = None
 
-EXPORTS = sorted(list(SIGNATURES) + ["b200_grasp_nms_workspace", "b200_voxel_down_sample_workspace", "b200_query_grid_workspace", "b200_collision_mask_workspace", "b200_mlp_f16_packed_bytes", "b200_error_string", "b200_version", "b200_launch_count"])
+EXPORTS = sorted(list(SIGNATURES) + ["b200_grasp_nms_workspace", "b200_voxel_down_sample_workspace", "b200_query_grid_workspace", "b200_collision_mask_workspace", "b200_mlp_f16_packed_bytes", "b200_label_object_table_bytes", "b200_error_string", "b200_version", "b200_launch_count"])
 
 
 def check(code, what):

@@ -387,11 +387,13 @@ class GraspNetStage2(nn.Module):
         self.tolerance = ToleranceNet(num_angle, num_depth)
 
     def forward(self, end_points, grid=None):
-        if self.is_training:
-            raise NotImplementedError("b200grasp: label matching for training (utils/label_generation.py) stays with "
-                                      "the reference's model code; build the network with is_training=False")
-        vp_features = self.crop(end_points['fp2_xyz'], end_points['input_xyz'], end_points['grasp_top_view_rot'],
-                                grid=grid)
+        if self.is_training:                             # models/graspnet.py:49-55: crop around the labelled grasp points
+            from .label_generation import match_grasp_view_and_label
+            grasp_top_views_rot, _, _, _, end_points = match_grasp_view_and_label(end_points)
+            seed_xyz = end_points['batch_grasp_point']
+        else:
+            grasp_top_views_rot, seed_xyz = end_points['grasp_top_view_rot'], end_points['fp2_xyz']
+        vp_features = self.crop(seed_xyz, end_points['input_xyz'], grasp_top_views_rot, grid=grid)
         if _fast(self.operation) and fm.ARITH == "f16x3":
             return _two_heads(self.operation, self.tolerance, vp_features, end_points)
         end_points = self.operation(vp_features, end_points)
@@ -413,6 +415,9 @@ class GraspNet(nn.Module):
 
     def forward(self, end_points):
         end_points = self.view_estimator(end_points)
+        if self.is_training:                             # models/graspnet.py:70-75
+            from .label_generation import process_grasp_labels
+            end_points = process_grasp_labels(end_points)
         return self.grasp_generator(end_points)
 
 

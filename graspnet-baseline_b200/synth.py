@@ -98,6 +98,64 @@ def synthetic_grasps(scene, m, seed=0, dtype=np.float32):
     return np.ascontiguousarray(g, dtype=dtype)
 
 
+def training_labels(clouds, num_objects=5, num_grasp_points=1200, num_view=300, num_angle=12, num_depth=4, seed=0,
+                    device="cpu"):
+    """Synthetic labels of a training batch with the keys and shapes graspnet_dataset.py:238-246 produces (SURVEY.md
+    8(d) item 5): clouds (B,N,3) numpy -> dict of 'objectness_label' (B,N) i64 and per-scene lists (one entry per
+    object) of 'object_poses_list' (3,4), 'grasp_points_list' (Np,3), 'grasp_offsets_list' (Np,V,A,D,3) [angle, depth,
+    width], 'grasp_labels_list' (Np,V,A,D) friction coefficients U(0,1.2) with 70 % zeros (and a few -1),
+    'grasp_tolerance_list' (Np,V,A,D).  Objects sit on points of the cloud so that seeds find near grasp points."""
+    import torch
+    rng = np.random.default_rng(seed)
+    B, N, _ = clouds.shape
+    out = {k: [] for k in ("object_poses_list", "grasp_points_list", "grasp_offsets_list", "grasp_labels_list",
+                           "grasp_tolerance_list")}
+    obj_label = np.zeros((B, N), np.int64)
+    f = np.float32
+    V, A, D = num_view, num_angle, num_depth
+    for b in range(B):
+        scene = {k: [] for k in out}
+        centres = clouds[b][rng.choice(N, num_objects, replace=False)]
+        near = np.linalg.norm(clouds[b][:, None, :] - centres[None], axis=2).min(axis=1) < 0.08
+        obj_label[b] = near
+        for o in range(num_objects):
+            q, _ = np.linalg.qr(rng.standard_normal((3, 3)))
+            if np.linalg.det(q) < 0:
+                q[:, 0] = -q[:, 0]
+            pose = np.concatenate([q, centres[o][:, None]], axis=1).astype(f)
+            pts = (rng.standard_normal((num_grasp_points, 3)) * 0.03).astype(f)           # object frame
+            lab = rng.uniform(0.0, 1.2, (num_grasp_points, V, A, D)).astype(f)
+            r = rng.random(lab.shape)
+            lab[r < 0.7] = 0.0
+            lab[r > 0.995] = -1.0
+            off = np.empty((num_grasp_points, V, A, D, 3), f)
+            off[..., 0] = (np.arange(A, dtype=f) * (np.pi / A))[None, None, :, None]
+            off[..., 1] = (np.arange(1, D + 1, dtype=f) * 0.01)[None, None, None, :]
+            off[..., 2] = rng.uniform(0.0, 0.12, lab.shape).astype(f)
+            tol = rng.uniform(0.0, 0.05, lab.shape).astype(f)
+            for k, v in (("object_poses_list", pose), ("grasp_points_list", pts), ("grasp_offsets_list", off),
+                         ("grasp_labels_list", lab), ("grasp_tolerance_list", tol)):
+                scene[k].append(torch.from_numpy(v).to(device))
+        for k in out:
+            out[k].append(scene[k])
+    out["objectness_label"] = torch.from_numpy(obj_label).to(device)
+    return out
+
+
+def training_predictions(seed, b, ns, v=300, a=12, d=4):
+    """seeded stand-ins for the network outputs the loss reads (numpy; the tests rebuild the same values)"""
+    rng = np.random.default_rng(seed)
+    f = np.float32
+    return {"objectness_score": rng.standard_normal((b, 2, ns)).astype(f),
+            "view_score": rng.uniform(0, 1.5, (b, ns, v)).astype(f),
+            "grasp_top_view_inds": rng.integers(0, v, (b, ns)).astype(np.int64),
+            "grasp_top_view_rot": np.zeros((b, ns, 3, 3), f),       # read but unused by models/loss.py:71
+            "grasp_score_pred": rng.uniform(0, 2, (b, a, ns, d)).astype(f),
+            "grasp_angle_cls_pred": rng.standard_normal((b, a, ns, d)).astype(f),
+            "grasp_width_pred": rng.uniform(0, 0.1, (b, a, ns, d)).astype(f),
+            "grasp_tolerance_pred": rng.uniform(0, 0.05, (b, a, ns, d)).astype(f)}
+
+
 def mlp_params(seed, dims):
     """Seeded parameters of a shared MLP (SharedMLP(dims, bn=True), reference pytorch_utils.py:11-36):
     [(conv weight (Cout,Cin), bn gamma, beta, running mean, running var)] per layer.  numpy only, so the golden

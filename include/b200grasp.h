@@ -226,6 +226,36 @@ int b200_grasp_nms_device(const float *grasps, const int32_t *m_dev, int m_max, 
 int b200_gather_rows(const float *rows, int cols, const int32_t *index, const int32_t *k_dev, int k_max, float *out,
                      void *stream);
 
+/* ---- training-path label generation fused with the nearest-grasp-point search (csrc/labels.cu).
+ * Replaces the index_select / cat / gather chain of utils/label_generation.py:58-118 (process_grasp_labels) and
+ * :125-149 (match_grasp_view_and_label) for everything the loss reads, without building the (B,Ns,V,A,D[,3]) tensors.
+ * A batch is described by device tables: an object table (one entry per object of every scene, filled on the HOST
+ * with b200_label_object_table_set and copied to the device: labels[Np,V,A,D], offsets[Np,V,A,D,3], tolerance[Np,V,A,D]
+ * device pointers, view_inds[V] i32 = for every template view of the scene frame the nearest rotated template view
+ * (label_generation.py:58-60, knn k = 1), the pose rotation), obj_first[B] (first object of scene b), the merged grasp
+ * points of all scenes (point_obj[ ] = object within its scene, point_local[ ] = row within the object,
+ * point_first[B]) and nn[B,Ns] i64 = the seed's nearest merged point within its scene (knn k = 1, 0-based, :84-86).
+ *  b200_label_view_stats: lmin[B,Ns,V] = smallest label of the row (nn, view_inds[v]) with label > 0 and width <=
+ *    max_width (+inf if none); *umax_key = the largest gathered label of the batch (order-preserving integer image;
+ *    zeroed by the callee first).
+ *  b200_label_view_scores: scores[n] = log(u_max / lmin) or 0 -- 'batch_grasp_view_label' (:113-118); *umax_out = u_max.
+ *  b200_label_top_gather: for top_view[B,Ns] i64: out_label[B,Ns,A*D] (transformed), out_offset[B,Ns,A*D,3],
+ *    out_tol[B,Ns,A*D], out_rot[B,Ns,9] = pose rotation x view_rot_tmpl[view_inds[top]] (view_rot_tmpl[V,9] = the
+ *    template frames, loss_utils.py:68-96). */
+size_t b200_label_object_table_bytes(int n_objects);
+int b200_label_object_table_set(void *host_table, int i, const float *labels, const float *offsets,
+                                const float *tolerance, const int32_t *view_inds, const float *rot9_host);
+int b200_label_view_stats(const void *objs, const int32_t *obj_first, const int32_t *point_obj,
+                          const int32_t *point_local, const int32_t *point_first, const long long *nn, int b, int ns,
+                          int v, int ad, float max_width, float *lmin, uint32_t *umax_key, void *stream);
+int b200_label_view_scores(const float *lmin, const uint32_t *umax_key, long long n, float *scores, float *umax_out,
+                           void *stream);
+int b200_label_top_gather(const void *objs, const int32_t *obj_first, const int32_t *point_obj,
+                          const int32_t *point_local, const int32_t *point_first, const long long *nn,
+                          const long long *top_view, const float *view_rot_tmpl, const uint32_t *umax_key, int b, int ns,
+                          int v, int ad, float max_width, float *out_label, float *out_offset, float *out_tol,
+                          float *out_rot, void *stream);
+
 /* Grid-accelerated forms of b200_ball_query / b200_cylinder_query_multi: identical results (the first
  * nsample hits IN INDEX ORDER, padded with the first hit, zeros if none), but the cloud is first binned
  * into a uniform grid held in `workspace` (b200_query_grid_workspace(b, n) bytes of device memory, no

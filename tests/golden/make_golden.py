@@ -352,8 +352,79 @@ def make_graspnet():
               "fp2 |max|", float(ep["fp2_features"].abs().max()))
 
 
+def make_training():
+    """utils/label_generation.py (process_grasp_labels, match_grasp_view_and_label), models/loss.py (get_loss) and the
+    training-mode forward of models/graspnet.py, imported and run unmodified on the CPU (knn = the reference's
+    knn_cpu.cpp built into oracle/_ref, pointnet2._ext answered by the C oracle)."""
+    import torch
+    sys.path.insert(0, ROOT)
+    import oracle
+    oracle.cpu.build()
+    sys.path.insert(0, os.path.join(ROOT, "graspnet-baseline_b200"))
+    import synth
+    for d in ("models", "pointnet2", "utils", "knn"):
+        sys.path.insert(0, os.path.join(REF, d))
+    sys.path.insert(0, os.path.join(ROOT, "oracle", "_ref"))
+    import pointnet2_utils as ref_pu
+    ref_pu._ext = _OracleExt(oracle, torch)
+    import graspnet as ref_graspnet
+    import label_generation as ref_lg
+    import loss as ref_loss
+    torch.set_num_threads(os.cpu_count() or 1)
+    # ---- (1) labels + loss on seeded stand-in predictions
+    for name, seed, b, n, ns, nobj, npts in (("a", 5, 2, 3000, 64, 3, 40), ("b", 9, 1, 2000, 96, 2, 25)):
+        cloud = np.stack([synth.tabletop_cloud(n, seed + i) for i in range(b)])
+        lab = synth.training_labels(cloud, num_objects=nobj, num_grasp_points=npts, seed=seed)
+        rng = np.random.default_rng(seed + 100)
+        inds = np.stack([rng.choice(n, ns, replace=False) for _ in range(b)]).astype(np.int32)
+        ep = dict(lab)
+        ep["input_xyz"] = torch.from_numpy(cloud)
+        ep["fp2_inds"] = torch.from_numpy(inds)
+        ep["fp2_xyz"] = torch.from_numpy(np.stack([cloud[i][inds[i]] for i in range(b)]))
+        ep.update({k: torch.from_numpy(v) for k, v in synth.training_predictions(seed + 200, b, ns).items()})
+        ep = ref_lg.process_grasp_labels(ep)
+        save = {"seed": seed, "dims": np.array([b, n, ns, nobj, npts]), "fp2_inds": inds,
+                "batch_grasp_point": ep["batch_grasp_point"].numpy(),
+                "batch_grasp_view_label": ep["batch_grasp_view_label"].numpy(),
+                "u_max_check": np.float32(0)}
+        rot, labels, offsets, tol, ep = ref_lg.match_grasp_view_and_label(ep)
+        save.update({"batch_grasp_view_rot": rot.numpy(), "batch_grasp_label": labels.numpy(),
+                     "batch_grasp_offset": offsets.numpy(), "batch_grasp_tolerance": tol.numpy()})
+        loss, ep = ref_loss.get_loss(ep)
+        for k in sorted(ep):
+            if k.startswith("loss/") or k.startswith("stage"):
+                save["stat:" + k] = np.float64(ep[k].item())
+        np.savez_compressed(os.path.join(HERE, f"training_{name}.npz"), **save)
+        print("training", name, "loss", float(loss), "view label max", float(ep["batch_grasp_view_label"].max()))
+    # ---- (2) the whole training-mode forward (BatchNorm on batch statistics) + loss
+    seed, b, n = 17, 2, 5000
+    net = ref_graspnet.GraspNet(input_feature_dim=0, num_view=300, num_angle=12, num_depth=4, cylinder_radius=0.05,
+                                hmin=-0.02, hmax_list=[0.01, 0.02, 0.03, 0.04], is_training=True)
+    synth.fill_state_dict(net, seed)
+    net.train()
+    cloud = np.stack([synth.tabletop_cloud(n, seed + i) for i in range(b)])
+    ep = dict(synth.training_labels(cloud, num_objects=3, num_grasp_points=40, seed=seed))
+    ep["point_clouds"] = torch.from_numpy(cloud)
+    with torch.no_grad():
+        ep = net(ep)
+        loss, ep = ref_loss.get_loss(ep)
+    save = {"seed": seed, "dims": np.array([b, n]), "fp2_inds": ep["fp2_inds"].numpy(),
+            "grasp_top_view_inds": ep["grasp_top_view_inds"].numpy(),
+            "objectness_score": ep["objectness_score"].numpy(),
+            "grasp_score_pred": ep["grasp_score_pred"].numpy()[:, :, ::8],
+            "batch_grasp_view_label": ep["batch_grasp_view_label"].numpy()[:, ::16]}
+    for k in sorted(ep):
+        if k.startswith("loss/"):
+            save["stat:" + k] = np.float64(ep[k].item())
+    np.savez_compressed(os.path.join(HERE, "training_forward.npz"), **save)
+    print("training forward loss", float(loss))
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["collision", "knn", "decode", "mlp", "graspnet"]
+    which = sys.argv[1:] or ["collision", "knn", "decode", "mlp", "graspnet", "training"]
+    if "training" in which:
+        make_training()
+        sys.exit(0) if which == ["training"] else None
     if "graspnet" in which:
         make_graspnet()
         sys.exit(0) if which == ["graspnet"] else None
