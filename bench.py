@@ -524,6 +524,66 @@ def cfg4_leg(torch, b200grasp, timed_local, dev, peak):
             "scene_ms_sum": round(fps_ms + grid_ms + ball_ms + col_ms + nms_ms, 4)}
 
 
+def training_leg(torch, dist, b200grasp, dev, world, rank):
+    """forward (with label generation) + get_loss + backward + Adam at batch 8 per GPU, 20000 points, 5 objects x 300
+    annotated grasp points per scene (the dataset has ~1200: 14 GB of labels per GPU; the label kernels' traffic does
+    not depend on it).  N > 1: DistributedDataParallel over NCCL; the gradient all-reduce (4 MB) is timed alone and as
+    the difference to a step under no_sync().  N = 1: the same step on the reference's legacy CUDA ops + the composed
+    label chain beside it."""
+    from b200grasp.train_step import TrainStep
+    import gc
+    ts = TrainStep(dev, batch=8, num_grasp_points=300)
+    ms = ts.time(4, 2)
+    ms_nosync = ts.time(4, 1, sync=False) if world > 1 else ms
+    ar = ts.allreduce_ms()
+    # label generation alone: fused kernels vs the composed index_select chain, on the step's own seeds
+    from b200grasp import label_generation as lg
+    with torch.no_grad():
+        ep = dict(ts.labels)
+        inds = torch.stack([torch.randperm(20000, device=dev)[:1024] for _ in range(8)])
+        ep["fp2_xyz"] = torch.gather(ts.clouds, 1, inds[..., None].expand(-1, -1, 3)).contiguous()
+        ep["grasp_top_view_inds"] = torch.randint(0, 300, (8, 1024), device=dev)
+        lab = {}
+        for name, fused in (("fused", True), ("composed", False)):
+            for it in range(3):
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                e = lg.process_grasp_labels(dict(ep), fused=fused)
+                lg.match_grasp_view_and_label(e)
+                e1.record()
+                torch.cuda.synchronize()
+                lab[name] = e0.elapsed_time(e1)
+            del e
+    out = {"workload": "cfg5: GraspNet training step (forward with label generation + get_loss + backward + Adam), batch 8 "
+                       "per GPU, 20000 points, 5 objects x 300 grasp points x (300,12,4) labels per scene; composed path "
+                       "(this library's ops with backward kernels + torch layers, BatchNorm on batch statistics), "
+                       "cuDNN TF32 allowed (torch default)",
+           "n_gpus": world, "ms_per_step": round(ms, 2), "scenes_per_s": round(world * 8 / (ms * 1e-3), 1),
+           "ddp": None if world == 1 else {"backend": "nccl", "gradient_bytes": ts.param_bytes,
+                                          "ms_per_step_no_sync": round(ms_nosync, 2),
+                                          "allreduce_exposed_ms": round(ms - ms_nosync, 3),
+                                          "allreduce_alone_ms": round(ar, 4),
+                                          "allreduce_share": round(max(ms - ms_nosync, 0.0) / ms, 4)},
+           "label_generation_ms_batch8": {k: round(v, 3) for k, v in lab.items()},
+           "label_generation_note": "process_grasp_labels + match_grasp_view_and_label for 8 scenes: csrc/labels.cu "
+                                    "(reads 8 x 236 MB of label / offset rows once) vs the reference's index_select / "
+                                    "cat / gather chain on the same knn"}
+    del ts
+    gc.collect()
+    torch.cuda.empty_cache()
+    if world == 1:
+        ext = load_legacy()
+        if ext is not None:
+            tl = TrainStep(dev, batch=8, num_grasp_points=300, ext=ext, fused_labels=False)
+            out["legacy_ops_ms_per_step"] = round(tl.time(2, 1), 2)
+            out["speedup_vs_legacy_ops"] = round(out["legacy_ops_ms_per_step"] / ms, 2)
+            del tl
+            gc.collect()
+            torch.cuda.empty_cache()
+    return out
+
+
 # ---------------------------------------------------------------- our arm
 
 def run_ours(args, rank, world, local_rank):
@@ -717,6 +777,11 @@ def run_ours(args, rank, world, local_rank):
     if not (np.array_equal(got_m.numpy().astype(bool), ref_m) and np.array_equal(got_k.numpy(), ref_k.grasp_group_array)):
         raise SystemExit("bench: device-resident post-processing and the drop-in call sequence disagree")
 
+    # ---- BASELINE.json configs[4]: the training step, batch 8 per GPU, under DDP when N > 1 (all ranks: collective)
+    training = None
+    if not args.lean and not args.no_training:
+        log("training leg")
+        training = training_leg(torch, dist, b200grasp, dev, world, rank)
     if rank != 0:
         return None
     log("legacy leg")
@@ -953,7 +1018,7 @@ def run_ours(args, rank, world, local_rank):
                 "e2e_ratio": round(e2e * legacy["legacy_e2e_ms_per_scene"] / 1e3, 1),
                 "latency_ratio": round(legacy["legacy_e2e_ms_per_scene"] / lat_e2e_ms, 1),
                 "forward_only_ratio_vs_stream": round(legacy["legacy_forward_ms"] / (total_ms / args.steps), 1)},
-            "nms_1024": extra.get("nms_1024"), "cfg4": extra.get("cfg4"),
+            "nms_1024": extra.get("nms_1024"), "cfg4": extra.get("cfg4"), "training": training,
             "roofline": roof, "legacy_cuda": legacy, "batch64": batch64, "fused_mlp": fused_mlp,
             "inference_ops": infer_ops,
             "geometry_path": {"what": "the geometry ops + post-processing alone (pipeline.GeometryScene: stand-in "
@@ -977,6 +1042,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-batch64", action="store_true")
+    ap.add_argument("--no-training", action="store_true")
     ap.add_argument("--lean", action="store_true", help="headline, e2e and latency legs only (the command ncu lists "
                                                         "the launches of): no legacy / batch-64 / fused-MLP / per-op legs")
     args = ap.parse_args()
