@@ -555,6 +555,13 @@ def training_leg(torch, dist, b200grasp, dev, world, rank):
                 torch.cuda.synchronize()
                 lab[name] = e0.elapsed_time(e1)
             del e
+        e = dict(ep)
+        e['_time_label_kernels'] = True
+        for _ in range(3):
+            e = lg.process_grasp_labels(dict(e), fused=True)
+        k_ms, k_bytes = e['_label_kernel_ms'], e['_label_kernel_bytes']
+        del e
+    hbm = peaks()[0]
     out = {"workload": "cfg5: GraspNet training step (forward with label generation + get_loss + backward + Adam), batch 8 "
                        "per GPU, 20000 points, 5 objects x 300 grasp points x (300,12,4) labels per scene; composed path "
                        "(this library's ops with backward kernels + torch layers, BatchNorm on batch statistics), "
@@ -566,6 +573,10 @@ def training_leg(torch, dist, b200grasp, dev, world, rank):
                                           "allreduce_alone_ms": round(ar, 4),
                                           "allreduce_share": round(max(ms - ms_nosync, 0.0) / ms, 4)},
            "label_generation_ms_batch8": {k: round(v, 3) for k, v in lab.items()},
+           "label_view_stats_roofline": {"bound": "hbm", "kernel": "label_view_stats + label_view_scores (csrc/labels.cu), 8 scenes",
+                                          "alg_bytes": int(k_bytes), "ms": round(k_ms, 4),
+                                          "achieved": round(k_bytes / (k_ms * 1e-3) / 1e9, 1), "peak": hbm, "unit": "GB/s",
+                                          "frac": round(k_bytes / (k_ms * 1e-3) / 1e9 / hbm, 4)},
            "label_generation_note": "process_grasp_labels + match_grasp_view_and_label for 8 scenes: csrc/labels.cu "
                                     "(reads 8 x 236 MB of label / offset rows once) vs the reference's index_select / "
                                     "cat / gather chain on the same knn"}

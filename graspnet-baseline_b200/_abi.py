@@ -43,7 +43,7 @@ SIGNATURES = {
     "b200_knn": [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp],
     "b200_collision_counts": [_vp, _i, _vp, _vp, _vp, _i, _vp, _vp],
     "b200_grasp_nms": [_vp, _i, _d, _d, _vp, _vp, _vp, _sz, _vp],
-    "b200_label_object_table_set": [_vp, _i, _vp, _vp, _vp, _vp, ctypes.POINTER(_f)],
+    "b200_label_object_table_set": [_vp, _i, _vp, _vp, _vp, _vp, _vp],
     "b200_label_view_stats": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _vp, _vp, _vp],
     "b200_label_view_scores": [_vp, _vp, ctypes.c_longlong, _vp, _vp, _vp],
     "b200_label_top_gather": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _vp],

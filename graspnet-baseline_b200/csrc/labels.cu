@@ -28,7 +28,7 @@ struct ObjTable {                       // per object of a scene (device array, 
   const float *offsets;                 // (Np, V, A, D, 3)
   const float *tolerance;               // (Np, V, A, D)
   const int32_t *view_inds;             // (V): template view v of the scene frame <- view view_inds[v] of the object frame
-  float rot[9];                         // the object's rotation (pose[:3, :3]), row-major
+  const float *rot;                     // the object's rotation (pose[:3, :3]), 9 floats row-major, device memory
 };
 
 __device__ __forceinline__ unsigned ordered_key(float f) {            // monotone float -> unsigned
@@ -117,8 +117,9 @@ label_top_gather_kernel(const ObjTable *__restrict__ objs, const int32_t *__rest
   if (lane < 9) {                                                     // pose rotation times the template frame of view src
     const int r = lane / 3, c = lane % 3;
     const float *t = view_rot_tmpl + (size_t)src * 9;
-    out_rot[seed * 9 + lane] = __fmaf_rn(o.rot[3 * r + 2], __ldg(t + 6 + c),
-                                         __fmaf_rn(o.rot[3 * r + 1], __ldg(t + 3 + c), __fmul_rn(o.rot[3 * r], __ldg(t + c))));
+    out_rot[seed * 9 + lane] = __fmaf_rn(__ldg(o.rot + 3 * r + 2), __ldg(t + 6 + c),
+                                         __fmaf_rn(__ldg(o.rot + 3 * r + 1), __ldg(t + 3 + c),
+                                                   __fmul_rn(__ldg(o.rot + 3 * r), __ldg(t + c))));
   }
 }
 
@@ -128,11 +129,10 @@ extern "C" size_t b200_label_object_table_bytes(int n_objects) { return sizeof(O
 
 // HOST helper: fills entry i of a host-side object table (the caller copies the table to the device)
 extern "C" int b200_label_object_table_set(void *host_table, int i, const float *labels, const float *offsets,
-                                           const float *tolerance, const int32_t *view_inds, const float *rot9_host) {
-  if (!host_table || i < 0 || !labels || !offsets || !tolerance || !view_inds || !rot9_host) return B200_EINVAL;
+                                           const float *tolerance, const int32_t *view_inds, const float *rot9) {
+  if (!host_table || i < 0 || !labels || !offsets || !tolerance || !view_inds || !rot9) return B200_EINVAL;
   ObjTable &o = static_cast<ObjTable *>(host_table)[i];
-  o.labels = labels; o.offsets = offsets; o.tolerance = tolerance; o.view_inds = view_inds;
-  for (int k = 0; k < 9; ++k) o.rot[k] = rot9_host[k];
+  o.labels = labels; o.offsets = offsets; o.tolerance = tolerance; o.view_inds = view_inds; o.rot = rot9;
   return 0;
 }
 

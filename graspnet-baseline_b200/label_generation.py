@@ -94,49 +94,67 @@ def _process_composed(end_points):
     return end_points
 
 
+_TEMPLATES = {}
+
+
+def _template_cached(num_view, device):
+    key = (num_view, str(device))
+    if key not in _TEMPLATES:
+        _TEMPLATES[key] = _template(num_view, device)
+    return _TEMPLATES[key]
+
+
 class _LabelTables:
     """Device tables of one batch for csrc/labels.cu: per object {label / offset / tolerance pointers, view map, pose
-    rotation}, per merged grasp point {object, row within the object}, per scene {first object, first point}."""
+    rotation}, per merged grasp point {object, row within the object}, per scene {first object, first point}.  Built
+    with a handful of batched launches for all objects of all scenes and no device -> host copy."""
 
     def __init__(self, end_points, device):
         poses_list = end_points['object_poses_list']
-        self.keep = []                                   # tensors the pointer table refers to
-        n_obj = sum(len(p) for p in poses_list)
+        flat = lambda key: [t for scene in end_points[key] for t in scene]
+        poses, pts = flat('object_poses_list'), flat('grasp_points_list')
+        labels, offsets, tol = flat('grasp_labels_list'), flat('grasp_offsets_list'), flat('grasp_tolerance_list')
+        n_obj = len(poses)
+        for t, name in [(x, "grasp_labels") for x in labels] + [(x, "grasp_offsets") for x in offsets] + \
+                       [(x, "grasp_tolerance") for x in tol]:
+            ops._chk(t, name, torch.float32)
+        _, self.V, self.A, self.D = labels[0].size()
+        views, self.frames = _template_cached(self.V, device)
+        pose = torch.stack(poses, 0)                                     # (O, 3, 4)
+        self.rot = pose[:, :, :3].contiguous()                           # (O, 3, 3)
+        # for every template view of the scene frame, the nearest rotated template view (label_generation.py:52-60)
+        views_trans = torch.matmul(self.rot, views.T)                    # (O, 3, V) = (R views^T)
+        vi = knn(views_trans.contiguous(), views.T.unsqueeze(0).expand(n_obj, -1, -1).contiguous(), k=1) - 1
+        self.view_inds = vi.reshape(n_obj, self.V).to(torch.int32).contiguous()
+        # all grasp points in their scene's frame
+        counts = [int(p.size(0)) for p in pts]
+        oid = torch.repeat_interleave(torch.arange(n_obj, device=device), torch.tensor(counts, device=device),
+                                      output_size=sum(counts))
+        allp = torch.cat(pts, 0)
+        merged = torch.einsum('nij,nj->ni', self.rot[oid], allp) + pose[oid, :, 3]
         host = (ctypes.c_uint8 * _abi.lib.b200_label_object_table_bytes(n_obj))()
-        obj_first, point_first, point_obj, point_local, merged = [], [], [], [], []
+        obj_first, point_first, point_obj, point_local, self.merged = [], [], [], [], []
         oi = npts = 0
-        self.V = self.A = self.D = None
-        for i, poses in enumerate(poses_list):
+        for poses_b in poses_list:
             obj_first.append(oi)
             point_first.append(npts)
-            pts_scene = []
-            for o, pose in enumerate(poses):
-                labels = end_points['grasp_labels_list'][i][o]
-                offsets = end_points['grasp_offsets_list'][i][o]
-                tol = end_points['grasp_tolerance_list'][i][o]
-                pts = end_points['grasp_points_list'][i][o]
-                for t, name in ((labels, "grasp_labels"), (offsets, "grasp_offsets"), (tol, "grasp_tolerance")):
-                    ops._chk(t, name, torch.float32)
-                n, self.V, self.A, self.D = labels.size()
-                views, self.frames = _template(self.V, device)
-                _, vi = _object_views(pose, views)
-                vi32 = vi.to(torch.int32).contiguous()
-                self.keep += [labels, offsets, tol, vi32]
-                rot = (ctypes.c_float * 9)(*pose[:3, :3].detach().reshape(-1).cpu().tolist())
-                _abi.check(_abi.lib.b200_label_object_table_set(host, oi, ops._ptr(labels), ops._ptr(offsets), ops._ptr(tol),
-                                                               ops._ptr(vi32), rot), "label_object_table_set")
-                pts_scene.append(_rigid(pts, pose))
-                point_obj.append(torch.full((n,), o, dtype=torch.int32))
-                point_local.append(torch.arange(n, dtype=torch.int32))
+            n_scene = 0
+            for o in range(len(poses_b)):
+                _abi.check(_abi.lib.b200_label_object_table_set(
+                    host, oi, ops._ptr(labels[oi]), ops._ptr(offsets[oi]), ops._ptr(tol[oi]),
+                    ctypes.c_void_p(self.view_inds.data_ptr() + 4 * self.V * oi),
+                    ctypes.c_void_p(self.rot.data_ptr() + 36 * oi)), "label_object_table_set")
+                point_obj.append(np.full(counts[oi], o, np.int32))
+                point_local.append(np.arange(counts[oi], dtype=np.int32))
+                n_scene += counts[oi]
                 oi += 1
-                npts += n
-            merged.append(torch.cat(pts_scene, dim=0))
-        self.merged = merged                             # per scene (Np', 3), scene frame
-        i32 = lambda v: torch.tensor(v, dtype=torch.int32).to(device)
+            self.merged.append(merged[npts: npts + n_scene])            # per scene (Np', 3), scene frame
+            npts += n_scene
+        self.keep = [labels, offsets, tol]                               # what the pointer table refers to
+        i32 = lambda v: torch.from_numpy(np.asarray(v, dtype=np.int32)).to(device, non_blocking=True)
         self.obj_first, self.point_first = i32(obj_first), i32(point_first)
-        self.point_obj = torch.cat(point_obj).to(device)
-        self.point_local = torch.cat(point_local).to(device)
-        self.objs = torch.frombuffer(host, dtype=torch.uint8).clone().to(device) if n_obj else torch.empty(0, dtype=torch.uint8, device=device)
+        self.point_obj, self.point_local = i32(np.concatenate(point_obj)), i32(np.concatenate(point_local))
+        self.objs = torch.frombuffer(host, dtype=torch.uint8).clone().to(device, non_blocking=True)
         self.umax_key = torch.zeros(1, dtype=torch.int32, device=device)
         self.nn = None
 
@@ -147,12 +165,20 @@ def _process_fused(end_points):
     dev = seeds.device
     with torch.no_grad():
         tb = _LabelTables(end_points, dev)
-        tb.nn = torch.stack([_nearest(tb.merged[i], seeds[i]) for i in range(B)], 0).contiguous()      # (B, Ns) int64
+        if len({int(m.size(0)) for m in tb.merged}) == 1:               # equal point counts: one batched search
+            ref = torch.stack(tb.merged, 0).transpose(1, 2).contiguous()
+            tb.nn = (knn(ref, seeds.transpose(1, 2).contiguous(), k=1).reshape(B, Ns) - 1).contiguous()
+        else:
+            tb.nn = torch.stack([_nearest(tb.merged[i], seeds[i]) for i in range(B)], 0).contiguous()   # (B, Ns) int64
         V, AD = tb.V, tb.A * tb.D
         lmin = torch.empty((B, Ns, V), dtype=torch.float32, device=dev)
         scores = torch.empty((B, Ns, V), dtype=torch.float32, device=dev)
         umax = torch.empty(1, dtype=torch.float32, device=dev)
         lib, st = _abi.lib, ops._stream()
+        timing = end_points.get('_time_label_kernels')
+        if timing:
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+            ev[0].record()
         with torch.cuda.device(dev):
             _abi.check(lib.b200_label_view_stats(ops._ptr(tb.objs), ops._ptr(tb.obj_first), ops._ptr(tb.point_obj),
                                                  ops._ptr(tb.point_local), ops._ptr(tb.point_first), ops._ptr(tb.nn), B, Ns,
@@ -160,7 +186,13 @@ def _process_fused(end_points):
                        "label_view_stats")
             _abi.check(lib.b200_label_view_scores(ops._ptr(lmin), ops._ptr(tb.umax_key), lmin.numel(), ops._ptr(scores),
                                                   ops._ptr(umax), st), "label_view_scores")
+        if timing:                                        # bench.py: the streaming pass alone (it synchronises)
+            ev[1].record()
+            ev[1].synchronize()
+            end_points['_label_kernel_ms'] = ev[0].elapsed_time(ev[1])
+            end_points['_label_kernel_bytes'] = B * Ns * V * (AD * 16 + 8)     # label + offset rows read, lmin + score written
         end_points['batch_grasp_point'] = torch.stack([tb.merged[i][tb.nn[i]] for i in range(B)], 0)
+        end_points['batch_grasp_point'] = end_points['batch_grasp_point'].contiguous()
         end_points['batch_grasp_view_label'] = scores
         end_points['batch_grasp_label_max'] = umax
         end_points['_label_tables'] = tb

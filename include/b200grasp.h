@@ -232,7 +232,7 @@ int b200_gather_rows(const float *rows, int cols, const int32_t *index, const in
  * A batch is described by device tables: an object table (one entry per object of every scene, filled on the HOST
  * with b200_label_object_table_set and copied to the device: labels[Np,V,A,D], offsets[Np,V,A,D,3], tolerance[Np,V,A,D]
  * device pointers, view_inds[V] i32 = for every template view of the scene frame the nearest rotated template view
- * (label_generation.py:58-60, knn k = 1), the pose rotation), obj_first[B] (first object of scene b), the merged grasp
+ * (label_generation.py:58-60, knn k = 1), rot9 = device pointer to the pose rotation), obj_first[B] (first object of scene b), the merged grasp
  * points of all scenes (point_obj[ ] = object within its scene, point_local[ ] = row within the object,
  * point_first[B]) and nn[B,Ns] i64 = the seed's nearest merged point within its scene (knn k = 1, 0-based, :84-86).
  *  b200_label_view_stats: lmin[B,Ns,V] = smallest label of the row (nn, view_inds[v]) with label > 0 and width <=
@@ -244,7 +244,7 @@ int b200_gather_rows(const float *rows, int cols, const int32_t *index, const in
  *    template frames, loss_utils.py:68-96). */
 size_t b200_label_object_table_bytes(int n_objects);
 int b200_label_object_table_set(void *host_table, int i, const float *labels, const float *offsets,
-                                const float *tolerance, const int32_t *view_inds, const float *rot9_host);
+                                const float *tolerance, const int32_t *view_inds, const float *rot9);
 int b200_label_view_stats(const void *objs, const int32_t *obj_first, const int32_t *point_obj,
                           const int32_t *point_local, const int32_t *point_first, const long long *nn, int b, int ns,
                           int v, int ad, float max_width, float *lmin, uint32_t *umax_key, void *stream);

@@ -103,7 +103,8 @@ def test_fused_labels_equal_composed_at_full_view_count(b200):
         rot, labels, offsets, tol, ep = b200.label_generation.match_grasp_view_and_label(ep)
         outs.append((ep["batch_grasp_point"], ep["batch_grasp_view_label"], rot, labels, offsets, top, tol))
     f, c = outs
-    assert torch.equal(f[0], c[0]) and torch.equal(f[4], c[4]) and torch.equal(f[6], c[6])
+    assert (f[0] - c[0]).abs().max() <= 1e-6                              # batched einsum vs per-object matmul: last ulp
+    assert torch.equal(f[4], c[4]) and torch.equal(f[6], c[6])            # same nearest points, same rows
     assert (f[1] - c[1]).abs().max() <= 2e-6 * c[1].abs().max()           # logf (CUDA libm) vs torch.log
     assert (f[3] - c[3]).abs().max() <= 2e-6 * c[3].abs().max()
     assert (f[2] - c[2]).abs().max() <= 2e-6
