@@ -483,6 +483,51 @@ def nms_leg(torch, b200grasp, timed_local, dev):
     return {"what": "b200_grasp_nms alone (rank + 64x64 bitmask tiles in fp64 + single-CTA sweep), L2 flushed", "cases": out}
 
 
+def cfg1_leg(torch, b200grasp, dev):
+    """BASELINE.json configs[0]: ModelFreeCollisionDetector (voxel 0.01) + detect (approach 0.05, thresh 0.01) +
+    GraspGroup.nms on the reference's fixture scene doc/example_data (513,688 valid points -> 7237 voxels; committed
+    as tests/golden/scene_example.npz) with 1024 synthetic grasps, through the drop-in classes with HOST arrays in and
+    out (wall clock), next to the same calls on the host cores (C port of the numpy path, oracle/post.py)."""
+    import oracle
+    from b200grasp import synth
+    path = os.path.join(ROOT, "tests", "golden", "scene_example.npz")
+    if not os.path.exists(path):
+        return None
+    pts, g = synth.fixture_scene(path)
+    sample = pts[g["sample_idx"]].astype(np.float32)
+    grasps = synth.synthetic_grasps(sample, 1024, int(g["grasp_seed"]))
+
+    def gpu_step():
+        det = b200grasp.ModelFreeCollisionDetector(pts, voxel_size=0.01, device=dev)
+        gg = b200grasp.GraspGroup(grasps)
+        mask = det.detect(gg, approach_dist=0.05, collision_thresh=0.01)
+        return mask, gg[~mask].nms(device=dev)
+
+    def cpu_step():
+        scene = oracle.voxel_down_sample(pts, 0.01)
+        mask = oracle.collision_detect(scene, grasps, 0.01, 0.05, 0.01)
+        return mask, grasps[~mask][oracle.grasp_nms(grasps[~mask])]
+
+    def wall(fn, n):
+        fn()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(n):
+            out = fn()
+        torch.cuda.synchronize()
+        return (time.perf_counter() - t0) / n * 1e3, out
+
+    g_ms, (gm, gk) = wall(gpu_step, 10)
+    c_ms, (cm, ck) = wall(cpu_step, 3)
+    same = bool(np.array_equal(gm, cm) and np.array_equal(gk.grasp_group_array, ck) and np.array_equal(gm, g["mask_voxel"]))
+    return {"workload": "cfg1: detector construction (513688 points -> voxel 0.01 -> %d points) + detect of 1024 grasps + nms, "
+                        "host arrays in / out" % int(g["num_voxels"]),
+            "gpu_ms": round(g_ms, 3), "cpu_port_ms": round(c_ms, 2), "cpu_cores": os.cpu_count(), "speedup": round(c_ms / g_ms, 1),
+            "colliding": int(gm.sum()), "kept_after_nms": int(len(gk)),
+            "results_equal_cpu_port_and_reference_detect": same,
+            "h2d_bytes": int(pts.nbytes + grasps.shape[0] * 22 * 8 + grasps.nbytes)}
+
+
 def cfg4_leg(torch, b200grasp, timed_local, dev, peak):
     """BASELINE.json configs[3]: 200k points, FPS to 4096 seeds, 4096 grasps collision-checked against the FULL
     cloud (no voxelisation), NMS of the 4096.  Parity of these shapes: tests/test_gpu_full_size.py."""
@@ -897,6 +942,8 @@ def run_ours(args, rank, world, local_rank):
     if world == 1 and not args.lean:
         log("nms leg")
         extra["nms_1024"] = nms_leg(torch, b200grasp, timed_local, dev)
+        log("cfg1 leg")
+        extra["cfg1"] = cfg1_leg(torch, b200grasp, dev)
         log("cfg4 leg")
         extra["cfg4"] = cfg4_leg(torch, b200grasp, timed_local, dev, peaks()[0])
         log("inference op times")
@@ -1029,7 +1076,7 @@ def run_ours(args, rank, world, local_rank):
                 "e2e_ratio": round(e2e * legacy["legacy_e2e_ms_per_scene"] / 1e3, 1),
                 "latency_ratio": round(legacy["legacy_e2e_ms_per_scene"] / lat_e2e_ms, 1),
                 "forward_only_ratio_vs_stream": round(legacy["legacy_forward_ms"] / (total_ms / args.steps), 1)},
-            "nms_1024": extra.get("nms_1024"), "cfg4": extra.get("cfg4"), "training": training,
+            "cfg1": extra.get("cfg1"), "nms_1024": extra.get("nms_1024"), "cfg4": extra.get("cfg4"), "training": training,
             "roofline": roof, "legacy_cuda": legacy, "batch64": batch64, "fused_mlp": fused_mlp,
             "inference_ops": infer_ops,
             "geometry_path": {"what": "the geometry ops + post-processing alone (pipeline.GeometryScene: stand-in "

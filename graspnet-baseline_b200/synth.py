@@ -98,6 +98,32 @@ def synthetic_grasps(scene, m, seed=0, dtype=np.float32):
     return np.ascontiguousarray(g, dtype=dtype)
 
 
+def depth_to_cloud(depth, intrinsic, factor_depth):
+    """(H,W) depth image -> (H,W,3) float64 camera-frame points: z = depth / factor, x = (u - cx) z / fx,
+    y = (v - cy) z / fy (the pinhole back-projection of utils/data_utils.py:18-43)"""
+    h, w = depth.shape
+    u, v = np.meshgrid(np.arange(w), np.arange(h))
+    z = depth / factor_depth
+    x = (u - intrinsic[0, 2]) * z / intrinsic[0, 0]
+    y = (v - intrinsic[1, 2]) * z / intrinsic[1, 1]
+    return np.stack([x, y, z], axis=-1)
+
+
+def fixture_scene(path):
+    """The reference's example scene (doc/example_data: depth.png, meta.mat, workspace_mask.png) from the committed
+    fixture tests/golden/scene_example.npz -> (points (513688,3) float64 in image order, fixture dict).  The file holds
+    the depth image cropped to the workspace mask, the mask and the intrinsics (tests/golden/make_golden.py scene)."""
+    g = np.load(path)
+    y0, y1, x0, x1 = [int(v) for v in g["crop"]]
+    h, w = [int(v) for v in g["shape"]]
+    depth = np.zeros((h, w), np.uint16)
+    depth[y0:y1, x0:x1] = g["depth_crop"]
+    mask = np.zeros((h, w), bool)
+    mask[y0:y1, x0:x1] = np.unpackbits(g["mask_crop"])[: (y1 - y0) * (x1 - x0)].reshape(y1 - y0, x1 - x0).astype(bool)
+    cloud = depth_to_cloud(depth, g["intrinsic"], float(g["factor_depth"]))
+    return cloud[mask], g
+
+
 def training_labels(clouds, num_objects=5, num_grasp_points=1200, num_view=300, num_angle=12, num_depth=4, seed=0,
                     device="cpu"):
     """Synthetic labels of a training batch with the keys and shapes graspnet_dataset.py:238-246 produces (SURVEY.md

@@ -420,8 +420,62 @@ def make_training():
     print("training forward loss", float(loss))
 
 
+def make_scene():
+    """BASELINE.json configs[0]: the reference's own fixture scene doc/example_data/{depth.png, meta.mat,
+    workspace_mask.png} -> point cloud with the reference's utils/data_utils.py:18-43 imported unchanged (recipe of
+    image_demo.py:95-134), voxel 0.01, 1024 synthetic grasps, the reference's detect() run verbatim.  The file keeps the
+    depth image (cropped to the mask's bounding box, uint16), the mask and the intrinsics -- 0.4 MB instead of 12 MB of
+    points -- plus a subsample of the cloud the reference code produced, so the test can rebuild and pin it."""
+    import scipy.io as scio
+    from PIL import Image
+    sys.path.insert(0, ROOT)
+    import oracle
+    oracle.cpu.build()
+    sys.path.insert(0, os.path.join(ROOT, "graspnet-baseline_b200"))
+    import synth
+    _stub_open3d()
+    sys.path.insert(0, os.path.join(REF, "utils"))
+    from data_utils import CameraInfo, create_point_cloud_from_depth_image
+    import collision_detector as ref_cd
+    d = os.path.join(REF, "doc", "example_data")
+    depth = np.array(Image.open(os.path.join(d, "depth.png")))
+    meta = scio.loadmat(os.path.join(d, "meta.mat"))
+    K, factor = meta["intrinsic_matrix"], float(meta["factor_depth"].item())
+    wmask = np.array(Image.open(os.path.join(d, "workspace_mask.png")).convert("L"))
+    cam = CameraInfo(depth.shape[1], depth.shape[0], K[0, 0], K[1, 1], K[0, 2], K[1, 2], factor)
+    cloud = create_point_cloud_from_depth_image(depth, cam, organized=True)
+    mask = (wmask & (depth > 0)).astype(bool)
+    pts = cloud[mask]                                                   # (513688, 3) float64
+    ys, xs = np.where(mask)
+    y0, y1, x0, x1 = ys.min(), ys.max() + 1, xs.min(), xs.max() + 1
+    # 20000-point sample as demo_pointcloud.py:178-186 draws it (without replacement when there are enough points)
+    rng = np.random.RandomState(0)
+    idxs = rng.choice(len(pts), 20000, replace=False)
+    sample = pts[idxs].astype(np.float32)
+    # the detector on the full cloud at voxel 0.01 (open3d restated: oracle.voxel_down_sample), 1024 synthetic grasps
+    scene_v = oracle.voxel_down_sample(pts.astype(np.float64), 0.01)
+    grasps = synth.synthetic_grasps(sample, 1024, 7)
+    det = ref_cd.ModelFreeCollisionDetector.__new__(ref_cd.ModelFreeCollisionDetector)
+    det.finger_width, det.finger_length, det.voxel_size, det.scene_points = 0.01, 0.06, 0.01, scene_v
+    gg = _GG(grasps)
+    m1, empty, ious = det.detect(gg, approach_dist=0.05, collision_thresh=0.01, return_empty_grasp=True, return_ious=True)
+    det.scene_points = sample.astype(np.float64)                        # and against the 20000-point sample, unvoxelised
+    m2 = det.detect(gg, approach_dist=0.05, collision_thresh=0.01)
+    np.savez_compressed(os.path.join(HERE, "scene_example.npz"),
+                        depth_crop=depth[y0:y1, x0:x1].astype(np.uint16), mask_crop=np.packbits(mask[y0:y1, x0:x1]),
+                        crop=np.array([y0, y1, x0, x1]), shape=np.array(depth.shape), intrinsic=K.astype(np.float64),
+                        factor_depth=np.float64(factor), num_points=len(pts), cloud_every_997=pts[::997],
+                        cloud_sum=pts.sum(axis=0), sample_idx=idxs.astype(np.int32), num_voxels=len(scene_v),
+                        grasp_seed=7, mask_voxel=m1, empty_voxel=empty, ious_voxel=np.stack(ious), mask_sample=m2)
+    print("scene", pts.shape, "voxels", len(scene_v), "colliding", int(m1.sum()), int(m2.sum()),
+          os.path.getsize(os.path.join(HERE, "scene_example.npz")))
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["collision", "knn", "decode", "mlp", "graspnet", "training"]
+    which = sys.argv[1:] or ["collision", "knn", "decode", "mlp", "graspnet", "training", "scene"]
+    if "scene" in which:
+        make_scene()
+        sys.exit(0) if which == ["scene"] else None
     if "training" in which:
         make_training()
         sys.exit(0) if which == ["training"] else None
