@@ -50,6 +50,7 @@ SIGNATURES = {
     "b200_grasp_nms_static": [_vp, _i, _d, _d, _vp, _vp, _vp],
     "b200_collision_counts_dn": [_vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp],
     "b200_voxel_down_sample": [_vp, _i, _d, _vp, _vp, _vp, _sz, _vp],
+    "b200_voxel_down_sample_checked": [_vp, _i, _d, _vp, _vp, _vp, _vp, _sz, _vp],
     "b200_collision_counts_packed": [_vp, _vp, _i, _vp, _i, _vp, _vp],
     "b200_collision_mask_device": [_vp, _vp, _i, _vp, _vp, _i, _d, _d, _d, _vp, _vp, _sz, _vp],
     "b200_compact_rows": [_vp, _i, _vp, _vp, _i, _vp, _vp, _vp],

@@ -11,7 +11,7 @@ import numpy as np
 import torch
 
 from . import ops as _ext
-from .voxel import voxel_down_sample_device
+from .voxel import check_voxel_input, voxel_down_sample_device
 
 
 class ModelFreeCollisionDetector():
@@ -22,7 +22,8 @@ class ModelFreeCollisionDetector():
         self.device = torch.device(device if device is not None else "cuda")
         # open3d voxel_down_sample in the reference (:32-35); here on the device, no host round trip:
         # detect() reads the row count from device memory
-        self._scene_dev, self._nvox_dev = voxel_down_sample_device(scene_points, voxel_size, self.device)
+        self._scene_dev, self._nvox_dev, self._nbad_dev = voxel_down_sample_device(scene_points, voxel_size, self.device,
+                                                                                   return_bad=True)
         self._scene_host = None
 
     @property
@@ -37,7 +38,7 @@ class ModelFreeCollisionDetector():
     def scene_points(self, value):
         self._scene_host = np.asarray(value, dtype=np.float64)
         self._scene_dev = torch.from_numpy(np.ascontiguousarray(self._scene_host)).to(self.device)
-        self._nvox_dev = None
+        self._nvox_dev = self._nbad_dev = None
 
     def _thresholds(self, grasp_group, approach_dist):
         h = grasp_group.heights
@@ -59,6 +60,9 @@ class ModelFreeCollisionDetector():
         packed[:, 12:22] = self._thresholds(grasp_group, approach_dist)
         d = torch.from_numpy(packed).to(self.device, non_blocking=True)
         counts = _ext.collision_counts_packed(self._scene_dev, d, self._nvox_dev).cpu().numpy().astype(np.int64)
+        if self._nbad_dev is not None:                   # (the constructor does not synchronise: checked at first use)
+            check_voxel_input(self._nbad_dev)
+            self._nbad_dev = None
         heights = grasp_group.heights[:, np.newaxis]
         widths = grasp_group.widths[:, np.newaxis]
         vox3 = self.voxel_size ** 3

@@ -30,12 +30,15 @@ nms_rank_kernel(const float *__restrict__ grasps, int m, const int32_t *__restri
   if (m_dev) m = min(m, __ldg(m_dev));         // row count produced on the device (decode / compaction)
   if ((int)(blockIdx.x * RT) >= m) return;
   const int i = blockIdx.x * RT + threadIdx.x;
-  const float si = i < m ? __ldg(grasps + (size_t)i * G) : 0.f;
+  // scores are ranked under a TOTAL order -- NaN counts as -inf, ties by row number -- so that the ranks are always a
+  // permutation (with the plain comparisons NaN rows collided and left order[] slots unwritten: garbage row numbers)
+  auto key = [](float s) { return isnan(s) ? -INFINITY : s; };
+  const float si = i < m ? key(__ldg(grasps + (size_t)i * G)) : 0.f;
   int rank = 0;
   for (int j0 = 0; j0 < m; j0 += RT) {
     const int j = j0 + threadIdx.x;
     __syncthreads();
-    sc[threadIdx.x] = j < m ? __ldg(grasps + (size_t)j * G) : 0.f;
+    sc[threadIdx.x] = j < m ? key(__ldg(grasps + (size_t)j * G)) : 0.f;
     __syncthreads();
     const int jn = min(RT, m - j0);
     for (int t = 0; t < jn; ++t) {

@@ -34,9 +34,11 @@ __global__ void __launch_bounds__(VT)
 voxel_bounds_kernel(const double *__restrict__ pts, int n, long long *__restrict__ mins) {
   long long m0 = 0x7fffffffffffffffLL, m1 = m0, m2 = m0;
   for (int i = blockIdx.x * VT + threadIdx.x; i < n; i += gridDim.x * VT) {
-    m0 = min(m0, order_key(pts[3 * (size_t)i]));
-    m1 = min(m1, order_key(pts[3 * (size_t)i + 1]));
-    m2 = min(m2, order_key(pts[3 * (size_t)i + 2]));
+    const double x = pts[3 * (size_t)i], y = pts[3 * (size_t)i + 1], z = pts[3 * (size_t)i + 2];
+    if (!(isfinite(x) && isfinite(y) && isfinite(z))) continue;     // invalid points take no part (see voxel_key_kernel)
+    m0 = min(m0, order_key(x));
+    m1 = min(m1, order_key(y));
+    m2 = min(m2, order_key(z));
   }
 #pragma unroll
   for (int o = 16; o >= 1; o >>= 1) {
@@ -57,14 +59,21 @@ voxel_key_kernel(const double *__restrict__ pts, int n, double voxel, const long
   const int i = blockIdx.x * VT + threadIdx.x;
   if (i >= n) return;
   const double half = __dmul_rn(voxel, 0.5);
+  // A point that is not finite, or falls outside 2^21 voxels per axis from the cloud's minimum corner (open3d raises
+  // "voxel_size is too small" there), gets the key ~0: it sorts behind every voxel, is left out of the means and is
+  // COUNTED in *overflow (b200_voxel_down_sample_checked hands the count out; the host API raises on it).
   unsigned long long key = 0;
+  bool bad = false;
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
     const double origin = __dsub_rn(order_val(mins[a]), half);
     const double q = floor(__ddiv_rn(__dsub_rn(pts[3 * (size_t)i + a], origin), voxel));
-    long long c = (long long)q;
-    if (!(q >= 0.0) || q >= 2097152.0) { *overflow = 1; c = 0; }          // 21 bits per axis
-    key = (key << 21) | (unsigned long long)c;
+    bad |= !(q >= 0.0) || q >= 2097152.0;                               // 21 bits per axis; NaN / inf fail the first test
+    key = (key << 21) | (unsigned long long)(bad ? 0 : (long long)q);
+  }
+  if (bad) {
+    key = ~0ull;
+    atomicAdd(overflow, 1);
   }
   keys[i] = key;
   order[i] = i;
@@ -79,12 +88,17 @@ voxel_head_kernel(const unsigned long long *__restrict__ keys, int n, int *__res
 __global__ void __launch_bounds__(VT)
 voxel_mean_kernel(const double *__restrict__ pts, const unsigned long long *__restrict__ keys,
                   const int *__restrict__ order, const int *__restrict__ head, const int *__restrict__ row,
-                  int n, double *__restrict__ out, int *__restrict__ nvox) {
+                  int n, double *__restrict__ out, int *__restrict__ nvox, const int *__restrict__ overflow,
+                  int *__restrict__ nbad) {
   const int i = blockIdx.x * VT + threadIdx.x;
   if (i >= n) return;
-  if (i == n - 1) *nvox = row[i] + 1;                  // row[] = exclusive scan of head, shifted by one below
+  if (i == n - 1) {                                    // row[] = exclusive scan of head, shifted by one below;
+    *nvox = row[i] + 1 - (keys[i] == ~0ull ? 1 : 0);   // the run of excluded points, if any, is the last one
+    if (nbad) *nbad = *overflow;
+  }
   if (!head[i]) return;
   const unsigned long long k = keys[i];
+  if (k == ~0ull) return;
   double sx = 0.0, sy = 0.0, sz = 0.0;
   int cnt = 0;
   for (int j = i; j < n && keys[j] == k; ++j) {        // sorted order is stable => ascending point index
@@ -138,12 +152,14 @@ voxel_row_fix_kernel(int *__restrict__ row, int n) {    // inclusive sum of head
 
 extern "C" size_t b200_voxel_down_sample_workspace(int n) { return layout(n).total; }
 
-extern "C" int b200_voxel_down_sample(const double *points, int n, double voxel_size, double *out,
-                                      int32_t *nvox, void *workspace, size_t workspace_bytes, void *stream) {
+extern "C" int b200_voxel_down_sample_checked(const double *points, int n, double voxel_size, double *out,
+                                              int32_t *nvox, int32_t *nbad, void *workspace, size_t workspace_bytes,
+                                              void *stream) {
   if (n < 0 || !nvox || !(voxel_size > 0.0)) return B200_EINVAL;
   cudaStream_t st = (cudaStream_t)stream;
   if (n == 0) {
     B200_CUDA(cudaMemsetAsync(nvox, 0, sizeof(int32_t), st));
+    if (nbad) B200_CUDA(cudaMemsetAsync(nbad, 0, sizeof(int32_t), st));
     return 0;
   }
   if (!points || !out || !workspace) return B200_EINVAL;
@@ -170,7 +186,12 @@ extern "C" int b200_voxel_down_sample(const double *points, int n, double voxel_
   B200_CUDA(cub::DeviceScan::InclusiveSum(ws + L.cub, cub_bytes, head, row, n, st));
   voxel_row_fix_kernel<<<grid, VT, 0, st>>>(row, n);
   B200_LAUNCH_CHECK();
-  voxel_mean_kernel<<<grid, VT, 0, st>>>(points, keys_b, ord_b, head, row, n, out, nvox);
+  voxel_mean_kernel<<<grid, VT, 0, st>>>(points, keys_b, ord_b, head, row, n, out, nvox, overflow, nbad);
   B200_LAUNCH_CHECK();
   return 0;
+}
+
+extern "C" int b200_voxel_down_sample(const double *points, int n, double voxel_size, double *out,
+                                      int32_t *nvox, void *workspace, size_t workspace_bytes, void *stream) {
+  return b200_voxel_down_sample_checked(points, n, voxel_size, out, nvox, nullptr, workspace, workspace_bytes, stream);
 }

@@ -720,19 +720,21 @@ def grasp_nms_device(grasps, m_dev, translation_thresh, cos_rotation_thresh, out
     return out, nkeep
 
 
-def voxel_down_sample(points, voxel_size):
+def voxel_down_sample(points, voxel_size, return_bad=False):
     """points (N,3) f64 -> (out (N,3) f64 of which the first nvox rows are valid, nvox (1,) i32), both on
-    the device   [utils/collision_detector.py:32-35 -> open3d voxel_down_sample, restated]"""
+    the device   [utils/collision_detector.py:32-35 -> open3d voxel_down_sample, restated].
+    return_bad: also nbad (1,) i32 = points left out (not finite, or beyond 2^21 voxels per axis)."""
     _chk(points, "points", torch.float64)
     n = points.shape[0]
     out = torch.empty((max(n, 1), 3), dtype=torch.float64, device=points.device)
-    nvox = torch.empty((1,), dtype=torch.int32, device=points.device)
+    counts = torch.empty((2,), dtype=torch.int32, device=points.device)
+    nvox, nbad = counts[0:1], counts[1:2]
     nbytes = _lib.b200_voxel_down_sample_workspace(n)
     ws = torch.empty((nbytes,), dtype=torch.uint8, device=points.device)
     with torch.cuda.device(points.device):
-        _abi.check(_lib.b200_voxel_down_sample(_ptr(points), n, float(voxel_size), _ptr(out), _ptr(nvox), _ptr(ws),
-                                               nbytes, _stream()), "voxel_down_sample")
-    return out, nvox
+        _abi.check(_lib.b200_voxel_down_sample_checked(_ptr(points), n, float(voxel_size), _ptr(out), _ptr(nvox),
+                                                       _ptr(nbad), _ptr(ws), nbytes, _stream()), "voxel_down_sample")
+    return (out, nvox, nbad) if return_bad else (out, nvox)
 
 
 def grasp_nms(grasps, translation_thresh, cos_rotation_thresh):

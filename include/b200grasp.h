@@ -340,6 +340,11 @@ int b200_collision_counts_packed(const double *scene, const int32_t *n_dev, int 
 size_t b200_voxel_down_sample_workspace(int n);
 int b200_voxel_down_sample(const double *points, int n, double voxel_size, double *out, int32_t *nvox,
                            void *workspace, size_t workspace_bytes, void *stream);
+/* The same; *nbad (device int, may be NULL) = number of input points LEFT OUT of the result because they are not
+ * finite or lie outside 2^21 voxels per axis from the cloud's minimum corner (open3d raises "voxel_size is too small"
+ * in that case; collision_detector.py:32-35 would propagate it).  b200_voxel_down_sample leaves them out silently. */
+int b200_voxel_down_sample_checked(const double *points, int n, double voxel_size, double *out, int32_t *nvox,
+                                   int32_t *nbad, void *workspace, size_t workspace_bytes, void *stream);
 
 /* GraspGroup.nms (graspnetAPI -> grasp_nms.nms_grasp; call sites demo_pointcloud.py:249,
  * grasp_service.py:276).  grasps[M,17] f32; keep[M] i32 receives the surviving

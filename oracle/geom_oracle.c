@@ -482,7 +482,9 @@ HOT void oracle_collision_counts(const double *scene, int n, const double *T, co
 static int cmp_desc_stable(const void *a, const void *b, void *ctx) {
   const float *g = (const float *)ctx;
   const int ia = *(const int *)a, ib = *(const int *)b;
-  const float sa = g[(size_t)ia * 17], sb = g[(size_t)ib * 17];
+  float sa = g[(size_t)ia * 17], sb = g[(size_t)ib * 17];
+  if (sa != sa) sa = -INFINITY;                  /* total order: NaN scores rank last (as -inf), ties by row number */
+  if (sb != sb) sb = -INFINITY;
   if (sa > sb) return -1;
   if (sa < sb) return 1;
   return ia < ib ? -1 : (ia > ib);

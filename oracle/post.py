@@ -94,7 +94,14 @@ def voxel_down_sample(points, voxel_size):
     p = np.asarray(points, dtype=np.float64)
     if p.shape[0] == 0:
         return p.reshape(0, 3)
+    # points that are not finite, or beyond 2^21 voxels per axis from the minimum corner, are left out (csrc/voxel.cu;
+    # open3d raises "voxel_size is too small" for the range case)
+    p = p[np.isfinite(p).all(axis=1)]
+    if p.shape[0] == 0:
+        return p.reshape(0, 3)
     origin = p.min(axis=0) - voxel_size * 0.5
+    q = np.floor((p - origin) / voxel_size)
+    p = p[(q < 2097152.0).all(axis=1)]
     key = np.floor((p - origin) / voxel_size).astype(np.int64)
     order = np.lexsort((key[:, 2], key[:, 1], key[:, 0]))  # stable
     ks = key[order]

@@ -81,3 +81,50 @@ def test_decode_then_postprocess_on_device(b200, oracle_mod):
     assert (mask[:m].cpu().numpy().astype(bool) == want_mask).all()
     assert (kept[: int(nkept.item())].cpu().numpy() == want).all()
     assert 0 < len(want) < m
+
+
+def test_nms_nan_and_duplicate_scores_keep_a_total_order(b200, oracle_mod):
+    """NaN scores rank last (as -inf), equal scores by row number: the rank kernel always produces a permutation
+    (with plain comparisons NaN rows collided and the sweep read unwritten order[] slots)"""
+    import math
+    rng = np.random.default_rng(4)
+    cloud = b200.synth.tabletop_cloud(4000, 2)
+    g = b200.synth.synthetic_grasps(cloud[:300], 700, 6)
+    g[rng.choice(700, 60, replace=False), 0] = np.nan
+    g[rng.choice(700, 200, replace=False), 0] = 0.5                   # mass ties
+    g[5, 0], g[6, 0] = np.inf, -np.inf
+    keep, nkeep = b200.ops.grasp_nms(torch.from_numpy(g).cuda(), 0.03, math.cos(30.0 / 180.0 * math.pi))
+    got = keep[: int(nkeep.item())].cpu().numpy()
+    want = oracle_mod.grasp_nms(g)
+    assert (got == want).all()
+    assert len(set(got.tolist())) == len(got) and got.min() >= 0 and got.max() < 700
+    assert got[0] == 5                                                # +inf first; the NaN rows come after every number
+    first_nan = np.flatnonzero(np.isnan(g[got, 0]))
+    assert len(first_nan) == 0 or np.isnan(g[got[first_nan[0]:], 0]).all()
+
+
+def test_voxel_down_sample_leaves_out_and_reports_invalid_points(b200, oracle_mod):
+    """a NaN / inf point or a far outlier (beyond 2^21 voxels from the minimum corner) is excluded from the result and
+    counted; the host API raises (open3d: "voxel_size is too small"); the detector raises at first use"""
+    cloud = b200.synth.tabletop_cloud(5000, 8).astype(np.float64)
+    clean = oracle_mod.voxel_down_sample(cloud, 0.01)
+    bad = cloud.copy()
+    bad[17] = np.nan
+    bad[4000, 1] = np.inf
+    out, nvox, nbad = b200.ops.voxel_down_sample(torch.from_numpy(bad).cuda(), 0.01, return_bad=True)
+    assert int(nbad.item()) == 2
+    got = out[: int(nvox.item())].cpu().numpy()
+    want = oracle_mod.voxel_down_sample(bad, 0.01)
+    assert got.shape == want.shape and (got == want).all()
+    assert abs(len(got) - len(clean)) <= 2
+    far = cloud.copy()
+    far[0] = [1e6, 0.0, 0.6]                                          # 1e8 voxels away along x
+    out, nvox, nbad = b200.ops.voxel_down_sample(torch.from_numpy(far).cuda(), 0.01, return_bad=True)
+    assert int(nbad.item()) == 1
+    assert (out[: int(nvox.item())].cpu().numpy() == oracle_mod.voxel_down_sample(far, 0.01)).all()
+    with pytest.raises(RuntimeError):
+        b200.voxel.voxel_down_sample(far, 0.01)
+    det = b200.ModelFreeCollisionDetector(bad, voxel_size=0.01)
+    with pytest.raises(RuntimeError):
+        det.detect(b200.GraspGroup(b200.synth.synthetic_grasps(cloud, 16, 1)))
+    assert (b200.voxel.voxel_down_sample(cloud, 0.01) == clean).all()  # clean input: unchanged behaviour
