@@ -13,7 +13,7 @@ import os
 import sys
 
 from . import _abi  # noqa: F401  (raises ImportError if the CUDA library is missing)
-from . import ops, pointnet2_utils, knn_modules, grasp, voxel, collision_detector, decode, postprocess, synth, sharding, fused_modules, graspnet, label_generation, loss  # noqa: F401
+from . import ops, pointnet2_utils, knn_modules, grasp, voxel, collision_detector, decode, postprocess, synth, sharding, fused_modules, graspnet, label_generation, loss, custom_ops  # noqa: F401
 from .grasp import GraspGroup  # noqa: F401
 from .collision_detector import ModelFreeCollisionDetector  # noqa: F401
 from .decode import pred_decode, pred_decode_device  # noqa: F401

@@ -749,3 +749,36 @@ def grasp_nms(grasps, translation_thresh, cos_rotation_thresh):
         _abi.check(_lib.b200_grasp_nms(_ptr(grasps), m, float(translation_thresh), float(cos_rotation_thresh),
                                        _ptr(keep), _ptr(nkeep), _ptr(ws), nbytes, _stream()), "grasp_nms")
     return keep, nkeep
+
+
+def enable_nvtx(on=True):
+    """Wrap every public op of this module in an NVTX range named after it (per-op ranges for
+    nsys / ncu --nvtx).  Also switched on by the environment variable B200GRASP_NVTX=1 at import."""
+    import functools
+    import inspect
+    import sys
+    mod = sys.modules[__name__]
+    for name, fn in list(vars(mod).items()):
+        if name.startswith("_") or name == "enable_nvtx" or not inspect.isfunction(fn) or fn.__module__ != __name__:
+            continue
+        base = getattr(fn, "__wrapped_op__", fn)
+        if not on:
+            setattr(mod, name, base)
+            continue
+
+        def make(f, label):
+            @functools.wraps(f)
+            def wrapped(*a, **k):
+                torch.cuda.nvtx.range_push(label)
+                try:
+                    return f(*a, **k)
+                finally:
+                    torch.cuda.nvtx.range_pop()
+            wrapped.__wrapped_op__ = f
+            return wrapped
+        setattr(mod, name, make(base, "b200grasp." + name))
+
+
+import os as _os
+if _os.environ.get("B200GRASP_NVTX") == "1":
+    enable_nvtx(True)
