@@ -21,6 +21,13 @@ FUSED = True
 # operands, exact power-of-two scaling, tcgen05 kind::f16; also the 1x1-conv stacks between the geometry ops),
 # "tf32x3" = csrc/mlp_fused.cu (3xTF32) + csrc/pointwise.cu (fp32 FMAs).  passes=1 modules always run plain TF32.
 ARITH = "f16x3"
+# The 1x1-conv stacks of the backbone's FP modules and of ApproachNet (K = 512 / 256 / 302: up to 96 truncating
+# accumulator updates per output in fp16x3) can run on the exact-fp32 kernel of csrc/pointwise.cu instead:
+# measured (profiles/r02_graspnet_parity.txt, tools/pipe_probe.py): "fp32" brings the network-level error against the
+# exact (float64) network from 1.2e-5 / 2.1e-5 (view scores / objectness) to 5e-6 / 1.0e-5 and the single-scene
+# latency from 0.89 to 0.85 ms, at 3365 instead of 3664 scenes/s in the stream.  Parity first: "fp32" is the default;
+# the two grasp heads (one launch) and all grouped MLPs stay on the tensor cores.
+STACK_ARITH = "fp32"
 
 
 class _BN(nn.Sequential):

@@ -112,10 +112,11 @@ class _Folded:
         return self.groups
 
 
-def _stack(x, folded, x2=None):
+def _stack(x, folded, x2=None, exact_ok=False):
     """a conv(+BN+ReLU) stack over point columns: fp16x3 tensor-core launches (csrc/mlp_f16.cu) or, with
-    fused_modules.ARITH = "tf32x3", one exact-fp32 launch per layer (csrc/pointwise.cu)"""
-    if fm.ARITH != "f16x3":
+    fused_modules.ARITH = "tf32x3" (or STACK_ARITH = "fp32" for the stacks that allow it), one exact-fp32 launch per
+    layer (csrc/pointwise.cu)"""
+    if fm.ARITH != "f16x3" or (exact_ok and fm.STACK_ARITH == "fp32"):
         layers = folded.get()
         for i, (w, b) in enumerate(layers):
             x, x2 = _pointwise(x, w, b, relu=folded.relu_last or i + 1 < len(layers), x2=x2), None
@@ -189,7 +190,8 @@ class PointnetFPModule(nn.Module):
             weight = dist_recip / torch.sum(dist_recip, dim=2, keepdim=True)
             interpolated = pointnet2_utils.three_interpolate(known_feats, idx, weight)
         if _fast(self):                                     # the concatenation happens inside the first layer
-            return _stack(interpolated, self._folded, x2=None if unknow_feats is None else unknow_feats.contiguous())
+            return _stack(interpolated, self._folded, x2=None if unknow_feats is None else unknow_feats.contiguous(),
+                          exact_ok=True)
         x = torch.cat([interpolated, unknow_feats], dim=1) if unknow_feats is not None else interpolated
         return self.mlp(x.unsqueeze(-1)).squeeze(-1)
 
@@ -268,7 +270,7 @@ class ApproachNet(nn.Module):
         B, num_seed, _ = seed_xyz.size()
         views, frames = self.tables(seed_features.device)
         if _fast(self):
-            features = _stack(seed_features, self._folded)
+            features = _stack(seed_features, self._folded, exact_ok=True)
             top_view_inds, top_view_scores, vp_xyz, vp_rot = ops.view_select(features, views, frames)
             view_score = features[:, 2:2 + self.num_view, :].transpose(1, 2)       # a view; the loss wants it contiguous
         else:

@@ -8,6 +8,13 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
+def pytest_sessionstart(session):
+    """B200_STACK_ARITH=fp32 runs the suite with the exact-fp32 FP / ApproachNet stacks (fused_modules.STACK_ARITH)"""
+    if os.environ.get("B200_STACK_ARITH"):
+        import b200grasp
+        b200grasp.fused_modules.STACK_ARITH = os.environ["B200_STACK_ARITH"]
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
 

@@ -306,6 +306,41 @@ class _OracleExt:
         return self.t.from_numpy(self.o.three_interpolate(*self._np(features, idx, weight)))
 
 
+class _OracleExt64(_OracleExt):
+    """the same for the float64 run of the network: every INDEX op sees the float32 coordinates (so the indices are
+    the fp32 run's), the three feature ops -- gather / group (copies) and three_interpolate (a 3-tap weighted sum) --
+    are evaluated in float64 with numpy"""
+
+    def _f32(self, t):
+        return np.ascontiguousarray(t.detach().cpu().numpy().astype(np.float32))
+
+    def furthest_point_sampling(self, xyz, npoint):
+        return self.t.from_numpy(self.o.furthest_point_sampling(self._f32(xyz), npoint))
+
+    def ball_query(self, new_xyz, xyz, radius, nsample):
+        return self.t.from_numpy(self.o.ball_query(self._f32(new_xyz), self._f32(xyz), radius, nsample))
+
+    def cylinder_query(self, new_xyz, xyz, rot, radius, hmin, hmax, nsample):
+        return self.t.from_numpy(self.o.cylinder_query(self._f32(new_xyz), self._f32(xyz), self._f32(rot), radius, hmin,
+                                                       hmax, nsample))
+
+    def three_nn(self, unknown, known):
+        d2, idx = self.o.three_nn(self._f32(unknown), self._f32(known))
+        return self.t.from_numpy(d2.astype(np.float64)), self.t.from_numpy(idx)
+
+    def gather_points(self, features, idx):
+        f, i = features.numpy(), idx.numpy()
+        return self.t.from_numpy(np.stack([f[b][:, i[b]] for b in range(len(f))]))
+
+    def group_points(self, features, idx):
+        f, i = features.numpy(), idx.numpy()
+        return self.t.from_numpy(np.stack([f[b][:, i[b]] for b in range(len(f))]))
+
+    def three_interpolate(self, features, idx, weight):
+        f, i, w = features.numpy(), idx.numpy(), weight.numpy()
+        return self.t.from_numpy(np.stack([(f[b][:, i[b]] * w[b][None]).sum(axis=-1) for b in range(len(f))]))
+
+
 def make_graspnet():
     import torch
     sys.path.insert(0, ROOT)
@@ -347,6 +382,24 @@ def make_graspnet():
             save[k] = ep[k].numpy()[:, :, ::4]
         for i, r in enumerate(rows):
             save["rows_%d" % i] = r.numpy()
+        # the same network and cloud evaluated in float64 (same indices: the index ops see the float32 coordinates):
+        # the EXACT answer up to 1e-12, against which the reference's own float32 result above and any other float32
+        # implementation can be measured (tests/test_gpu_graspnet.py::test_error_against_exact_network)
+        ref_pu._ext = _OracleExt64(oracle, torch)
+        net64 = net.double()
+        with torch.no_grad():                              # models/graspnet.py:70-75, the two stages one by one: the view
+            ep64 = net64.view_estimator({"point_clouds": torch.from_numpy(cloud).double()})   # frames come out in float32
+            ep64["grasp_top_view_rot"] = ep64["grasp_top_view_rot"].double()
+            ep64 = net64.grasp_generator(ep64)
+        ref_pu._ext = _OracleExt(oracle, torch)
+        assert (ep64["sa1_inds"].numpy() == ep["sa1_inds"].numpy()).all()
+        assert (ep64["fp2_inds"].numpy() == ep["fp2_inds"].numpy()).all()
+        for k, sl in (("sa4_features", (slice(None), slice(None), slice(None, None, 4))),
+                      ("fp2_features", (slice(None), slice(None), slice(None, None, 8))),
+                      ("objectness_score", (slice(None),)), ("view_score", (slice(None), slice(None, None, 8))),
+                      ("grasp_top_view_score", (slice(None),))):
+            save["exact:" + k] = ep64[k].numpy()[sl]
+        save["exact:grasp_top_view_inds"] = ep64["grasp_top_view_inds"].numpy()
         np.savez_compressed(os.path.join(HERE, f"graspnet_{name}.npz"), **save)
         print("graspnet", name, cloud.shape, [tuple(r.shape) for r in rows],
               "fp2 |max|", float(ep["fp2_features"].abs().max()))

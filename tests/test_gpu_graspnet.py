@@ -61,13 +61,14 @@ def test_forward_matches_reference_network(b200, name):
     cpu = lambda k: ep[k].cpu().numpy()
     assert (cpu("sa1_inds") == g["sa1_inds"]).all() and (cpu("fp2_inds") == g["fp2_inds"]).all()
     close(cpu("sa1_features")[:, :, ::16], g["sa1_features"], what="golden %s sa1_features" % name)
-    close(cpu("sa4_features")[:, :, ::4], g["sa4_features"], 4 * REL, what="sa4_features")
-    close(cpu("fp2_features")[:, :, ::8], g["fp2_features"], 4 * REL, what="fp2_features")
-    close(cpu("objectness_score"), g["objectness_score"], 4 * REL, what="objectness_score")
-    close(cpu("view_score")[:, ::8], g["view_score"], 4 * REL, what="view_score")
+    loose = 1.0 if b200.fused_modules.STACK_ARITH == "fp32" else 4.0
+    close(cpu("sa4_features")[:, :, ::4], g["sa4_features"], REL, what="sa4_features")
+    close(cpu("fp2_features")[:, :, ::8], g["fp2_features"], loose * REL, what="fp2_features")
+    close(cpu("objectness_score"), g["objectness_score"], max(loose, 1.3) * REL, what="objectness_score")
+    close(cpu("view_score")[:, ::8], g["view_score"], loose * REL, what="view_score")
     same_view = cpu("grasp_top_view_inds") == g["grasp_top_view_inds"]
     assert same_view.mean() >= 0.995, "best view differs on %d seeds" % (~same_view).sum()
-    close(cpu("grasp_top_view_score"), g["grasp_top_view_score"], 4 * REL, what="top view score")
+    close(cpu("grasp_top_view_score"), g["grasp_top_view_score"], loose * REL, what="top view score")
     assert np.abs(cpu("grasp_top_view_xyz") - g["grasp_top_view_xyz"])[same_view].max() <= 1e-6
     assert np.abs(cpu("grasp_top_view_rot") - g["grasp_top_view_rot"])[same_view].max() <= 1e-6
     sub = same_view[:, ::4]
@@ -82,6 +83,42 @@ def test_forward_matches_reference_network(b200, name):
         # rows are in seed order; classes (depth, angle) are argmaxes and may flip on near-ties -> row-wise agreement
         ok = np.abs(got - want).max(axis=1) <= 1e-4
         assert ok.mean() >= 0.98, "scene %d: %d of %d decoded rows differ" % (i, (~ok).sum(), len(ok))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["a", "b"])
+def test_error_against_exact_network(b200, name):
+    """How far is this package's float32 forward from the EXACT network (the reference evaluated in float64 on the
+    same indices, golden key 'exact:*'), next to the reference's own float32 CPU run?  Metric everywhere in this file:
+    max |err| over the tensor / max |exact| over the tensor ("of scale"), not per-element relative error.
+    The reference's fp32 run sits at 0.6-2.8e-6; the tensor-core path (fp16x3: three fp16 products per K = 16 step,
+    the accumulator updated with truncation 3 K / 16 times per output) at 0.2-2e-5, largest on the two objectness
+    channels at the end of the SA1..SA4 -> FP -> ApproachNet chain."""
+    g = np.load(os.path.join(GOLD, "graspnet_%s.npz" % name))
+    net = _net(b200, int(g["seed"])).cuda().eval()
+    with torch.no_grad():
+        ep = net({"point_clouds": torch.from_numpy(g["cloud"]).cuda()})
+    cpu = lambda k: ep[k].cpu().numpy()
+    out = os.path.join(os.path.dirname(os.path.dirname(__file__)), "gpurun_out")
+    if b200.fused_modules.STACK_ARITH == "fp32":        # the default: FP / ApproachNet stacks in exact fp32
+        bound = {"sa4_features": 1e-5, "fp2_features": 1e-5, "objectness_score": 1.2e-5, "view_score": 1e-5,
+                 "grasp_top_view_score": 1e-5}
+    else:                                               # all stacks on the tensor cores (fp16x3)
+        bound = {"sa4_features": 1e-5, "fp2_features": 1.5e-5, "objectness_score": 3e-5, "view_score": 2e-5,
+                 "grasp_top_view_score": 2e-5}
+    sl = {"sa4_features": lambda x: x[:, :, ::4], "fp2_features": lambda x: x[:, :, ::8], "objectness_score": lambda x: x,
+          "view_score": lambda x: x[:, ::8], "grasp_top_view_score": lambda x: x}
+    for k in bound:
+        exact = g["exact:" + k].astype(np.float64)
+        scale = np.abs(exact).max()
+        ours = np.abs(sl[k](cpu(k)).astype(np.float64) - exact).max() / scale
+        ref = np.abs(g[k].astype(np.float64) - exact).max() / scale
+        if os.path.isdir(out):
+            with open(os.path.join(out, "graspnet_parity.txt"), "a") as f:
+                f.write("exact %s %-28s this package %.3g   reference fp32 (CPU) %.3g   of scale\n" % (name, k, ours, ref))
+        assert ours <= bound[k], "%s: %.3g of scale from the exact network (bound %.1g)" % (k, ours, bound[k])
+    same = (cpu("grasp_top_view_inds") == g["exact:grasp_top_view_inds"]).mean()
+    assert same >= 0.995
 
 
 @pytest.mark.gpu

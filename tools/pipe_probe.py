@@ -10,7 +10,9 @@ import bench
 import b200grasp
 if os.environ.get("B200_ARITH"):
     b200grasp.fused_modules.ARITH = os.environ["B200_ARITH"]
-print("arith", b200grasp.fused_modules.ARITH)
+if os.environ.get("B200_STACK_ARITH"):
+    b200grasp.fused_modules.STACK_ARITH = os.environ["B200_STACK_ARITH"]
+print("arith", b200grasp.fused_modules.ARITH, "stacks", b200grasp.fused_modules.STACK_ARITH)
 net = bench.make_net("cuda")
 P = 640
 host = [bench.scene_cloud(5000 + i) for i in range(P)]
