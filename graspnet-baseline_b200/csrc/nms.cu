@@ -49,19 +49,45 @@ nms_rank_kernel(const float *__restrict__ grasps, int m, const int32_t *__restri
   if (i < m) order[rank] = i;
 }
 
+// Does grasp a (translation at, rotation ar, object id ao) suppress grasp c?  The arithmetic of the upstream
+// grasp_nms.nms_grasp is not available (PyPI package, no source in the reference tree), so every open choice of the
+// restatement is a switch (b200_grasp_nms_set_options, include/b200grasp.h); flags = 0 is the documented default:
+// both thresholds strict, fp64 arithmetic on the fp32 rows, cosine comparison, object ids ignored.
+template <typename T>
+__device__ __forceinline__ bool nms_pair(const T (&at)[3], const T (&ar)[9], const double *ct, const double *cr, float ao,
+                                         float co, T tthr, T cthr, T athr, unsigned flags) {
+  if ((flags & B200_NMS_SAME_OBJECT) && ao != co) return false;
+  const T dx = at[0] - (T)ct[0], dy = at[1] - (T)ct[1], dz = at[2] - (T)ct[2];
+  const T dist = sqrt((dx * dx + dy * dy) + dz * dz);
+  if (!((flags & B200_NMS_TRANS_INCLUSIVE) ? dist <= tthr : dist < tthr)) return false;
+  T tr = (T)0;
+#pragma unroll
+  for (int e = 0; e < 9; ++e) tr = tr + ar[e] * (T)cr[e];
+  const T ca = (tr - (T)1) / (T)2;
+  if (flags & B200_NMS_ACOS) {                                        // compare the angle itself
+    const T ang = acos(ca < (T)-1 ? (T)-1 : (ca > (T)1 ? (T)1 : ca));
+    return (flags & B200_NMS_ROT_INCLUSIVE) ? ang <= athr : ang < athr;
+  }
+  return (flags & B200_NMS_ROT_INCLUSIVE) ? ca >= cthr : ca > cthr;
+}
+
+unsigned g_nms_flags = 0u;
+
 __global__ void __launch_bounds__(64)
 nms_mask_kernel(const float *__restrict__ grasps, const int32_t *__restrict__ order, int m,
-                const int32_t *__restrict__ m_dev, int W, double tthr, double cthr,
+                const int32_t *__restrict__ m_dev, int W, double tthr, double cthr, unsigned flags,
                 unsigned long long *__restrict__ mask) {
   const int rb = blockIdx.y, cb = blockIdx.x;
   if (m_dev) m = min(m, __ldg(m_dev));
   if (cb < rb || cb * 64 >= m) return;       // lower triangle never read by the sweep; W = row stride (max rows)
   __shared__ double ct[64][3];
   __shared__ double cr[64][9];
+  __shared__ float cobj[64];
   const int t = threadIdx.x;
   const int c = cb * 64 + t;
   if (c < m) {
     const float *g = grasps + (size_t)__ldg(order + c) * G;
+    cobj[t] = __ldg(g + 16);
 #pragma unroll
     for (int e = 0; e < 3; ++e) ct[t][e] = (double)__ldg(g + 13 + e);
 #pragma unroll
@@ -76,19 +102,37 @@ nms_mask_kernel(const float *__restrict__ grasps, const int32_t *__restrict__ or
   for (int e = 0; e < 3; ++e) at[e] = (double)__ldg(g + 13 + e);
 #pragma unroll
   for (int e = 0; e < 9; ++e) ar[e] = (double)__ldg(g + 4 + e);
+  const float aobj = __ldg(g + 16);
   unsigned long long bits = 0ull;
   const int cn = min(64, m - cb * 64);
-  for (int k = 0; k < cn; ++k) {
-    if (cb * 64 + k <= a) continue;          // only later (lower-score) grasps
-    const double dx = __dsub_rn(at[0], ct[k][0]), dy = __dsub_rn(at[1], ct[k][1]),
-                 dz = __dsub_rn(at[2], ct[k][2]);
-    const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
-    if (!(__dsqrt_rn(d2) < tthr)) continue;
-    double tr = 0.0;
+  if (flags == 0u) {                                                  // the default: exact fp64, fixed association
+    for (int k = 0; k < cn; ++k) {
+      if (cb * 64 + k <= a) continue;          // only later (lower-score) grasps
+      const double dx = __dsub_rn(at[0], ct[k][0]), dy = __dsub_rn(at[1], ct[k][1]),
+                   dz = __dsub_rn(at[2], ct[k][2]);
+      const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+      if (!(__dsqrt_rn(d2) < tthr)) continue;
+      double tr = 0.0;
 #pragma unroll
-    for (int e = 0; e < 9; ++e) tr = __dadd_rn(tr, __dmul_rn(ar[e], cr[k][e]));
-    const double ca = __ddiv_rn(__dsub_rn(tr, 1.0), 2.0);
-    if (ca > cthr) bits |= 1ull << k;
+      for (int e = 0; e < 9; ++e) tr = __dadd_rn(tr, __dmul_rn(ar[e], cr[k][e]));
+      const double ca = __ddiv_rn(__dsub_rn(tr, 1.0), 2.0);
+      if (ca > cthr) bits |= 1ull << k;
+    }
+  } else if (flags & B200_NMS_FP32) {
+    float atf[3], arf[9];
+#pragma unroll
+    for (int e = 0; e < 3; ++e) atf[e] = (float)at[e];
+#pragma unroll
+    for (int e = 0; e < 9; ++e) arf[e] = (float)ar[e];
+    const float athr = acosf((float)cthr);
+    for (int k = 0; k < cn; ++k)
+      if (cb * 64 + k > a && nms_pair<float>(atf, arf, ct[k], cr[k], aobj, cobj[k], (float)tthr, (float)cthr, athr, flags))
+        bits |= 1ull << k;
+  } else {
+    const double athr = acos(cthr);
+    for (int k = 0; k < cn; ++k)
+      if (cb * 64 + k > a && nms_pair<double>(at, ar, ct[k], cr[k], aobj, cobj[k], tthr, cthr, athr, flags))
+        bits |= 1ull << k;
   }
   mask[(size_t)a * W + cb] = bits;
 }
@@ -176,6 +220,8 @@ size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 }  // namespace
 
+extern "C" void b200_grasp_nms_set_options(unsigned flags) { g_nms_flags = flags; }
+
 extern "C" size_t b200_grasp_nms_workspace(int m) {
   if (m <= 0) return 256;
   const size_t W = (size_t)(m + 63) / 64;
@@ -202,7 +248,7 @@ static int nms_launch(const float *grasps, int m, const int32_t *m_dev, double t
   nms_rank_kernel<<<ceil_div(m, RT), RT, 0, st>>>(grasps, m, m_dev, order);
   B200_LAUNCH_CHECK();
   nms_mask_kernel<<<dim3((unsigned)W, (unsigned)W), 64, 0, st>>>(grasps, order, m, m_dev, W, translation_thresh,
-                                                                cos_rotation_thresh, mask);
+                                                                cos_rotation_thresh, g_nms_flags, mask);
   B200_LAUNCH_CHECK();
   nms_sweep_kernel<<<1, ST, 0, st>>>(mask, order, m, m_dev, W, keep, nkeep);
   B200_LAUNCH_CHECK();

@@ -55,10 +55,12 @@ voxel_bounds_kernel(const double *__restrict__ pts, int n, long long *__restrict
 
 __global__ void __launch_bounds__(VT)
 voxel_key_kernel(const double *__restrict__ pts, int n, double voxel, const long long *__restrict__ mins,
-                 unsigned long long *__restrict__ keys, int *__restrict__ order, int *__restrict__ overflow) {
+                 unsigned long long *__restrict__ keys, int *__restrict__ order, int *__restrict__ overflow,
+                 unsigned flags) {
   const int i = blockIdx.x * VT + threadIdx.x;
   if (i >= n) return;
-  const double half = __dmul_rn(voxel, 0.5);
+  // grid origin: min_bound - voxel / 2 (Open3D's VoxelDownSample) unless B200_VOXEL_ORIGIN_AT_MIN
+  const double half = (flags & B200_VOXEL_ORIGIN_AT_MIN) ? 0.0 : __dmul_rn(voxel, 0.5);
   // A point that is not finite, or falls outside 2^21 voxels per axis from the cloud's minimum corner (open3d raises
   // "voxel_size is too small" there), gets the key ~0: it sorts behind every voxel, is left out of the means and is
   // COUNTED in *overflow (b200_voxel_down_sample_checked hands the count out; the host API raises on it).
@@ -150,6 +152,9 @@ voxel_row_fix_kernel(int *__restrict__ row, int n) {    // inclusive sum of head
 
 }  // namespace
 
+static unsigned g_voxel_flags = 0u;
+extern "C" void b200_voxel_set_options(unsigned flags) { g_voxel_flags = flags; }
+
 extern "C" size_t b200_voxel_down_sample_workspace(int n) { return layout(n).total; }
 
 extern "C" int b200_voxel_down_sample_checked(const double *points, int n, double voxel_size, double *out,
@@ -176,7 +181,7 @@ extern "C" int b200_voxel_down_sample_checked(const double *points, int n, doubl
   B200_LAUNCH_CHECK();
   voxel_bounds_kernel<<<min(grid, 4 * b200_sm_count()), VT, 0, st>>>(points, n, mins);
   B200_LAUNCH_CHECK();
-  voxel_key_kernel<<<grid, VT, 0, st>>>(points, n, voxel_size, mins, keys_a, ord_a, overflow);
+  voxel_key_kernel<<<grid, VT, 0, st>>>(points, n, voxel_size, mins, keys_a, ord_a, overflow, g_voxel_flags);
   B200_LAUNCH_CHECK();
   size_t cub_bytes = L.total - L.cub;
   B200_CUDA(cub::DeviceRadixSort::SortPairs(ws + L.cub, cub_bytes, keys_a, keys_b, ord_a, ord_b, n, 0, 63, st));

@@ -351,6 +351,19 @@ int b200_voxel_down_sample_checked(const double *points, int n, double voxel_siz
  * row numbers in descending-score order, *nkeep (device int) their count.
  * workspace: b200_grasp_nms_workspace(m) bytes of device scratch. */
 size_t b200_grasp_nms_workspace(int m);
+/* The two third-party pieces of the path (graspnetAPI's grasp_nms, open3d's voxel_down_sample) are RESTATED: their
+ * sources are not in the reference tree, no reference test or fixture pins them (parity unpinned).  Every choice the
+ * restatement had to make is a switch; 0 = the documented default.  Process-wide, applies to the launches that follow
+ * (all b200_grasp_nms* entry points / b200_voxel_down_sample*); the CPU oracle takes the same flags. */
+#define B200_NMS_TRANS_INCLUSIVE 1u  /* suppress if distance <= translation_thresh        (default: <)              */
+#define B200_NMS_ROT_INCLUSIVE 2u    /* ... and angle <= rotation_thresh                  (default: <)              */
+#define B200_NMS_SAME_OBJECT 4u      /* only grasps with equal object id (column 16)      (default: ids ignored)    */
+#define B200_NMS_FP32 8u             /* pair arithmetic in fp32                           (default: fp64)           */
+#define B200_NMS_ACOS 16u            /* compare acos(clip((tr - 1) / 2)) with the angle   (default: cosines)        */
+#define B200_VOXEL_ORIGIN_AT_MIN 1u  /* voxel grid origin = min_bound                     (default: - voxel / 2)    */
+void b200_grasp_nms_set_options(unsigned flags);
+void b200_voxel_set_options(unsigned flags);
+
 int b200_grasp_nms(const float *grasps, int m, double translation_thresh, double cos_rotation_thresh,
                    int32_t *keep, int32_t *nkeep, void *workspace, size_t workspace_bytes,
                    void *stream);

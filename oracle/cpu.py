@@ -30,6 +30,9 @@ def lib():
         if not os.path.exists(_SO):
             build()
         _lib = ctypes.CDLL(_SO)
+        _lib.oracle_grasp_nms_opts.restype = ctypes.c_int
+        _lib.oracle_grasp_nms_opts.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_double, ctypes.c_double,
+                                               ctypes.c_uint, ctypes.c_void_p]
         _lib.oracle_grasp_nms.restype = ctypes.c_int
         _lib.oracle_grasp_nms.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_double,
                                           ctypes.c_double, ctypes.c_void_p]

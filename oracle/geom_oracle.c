@@ -490,6 +490,56 @@ static int cmp_desc_stable(const void *a, const void *b, void *ctx) {
   return ia < ib ? -1 : (ia > ib);
 }
 
+/* does kept grasp gi suppress gj?  flags: the switches of include/b200grasp.h (B200_NMS_*); 0 = the default */
+static int nms_pair_opts(const float *gi, const float *gj, double tthr, double cthr, unsigned flags) {
+  if ((flags & 4u) && gi[16] != gj[16]) return 0;
+  if (flags & 8u) {                                   /* fp32 arithmetic */
+    const float dx = gi[13] - gj[13], dy = gi[14] - gj[14], dz = gi[15] - gj[15];
+    const float dist = sqrtf((dx * dx + dy * dy) + dz * dz);
+    if (!((flags & 1u) ? dist <= (float)tthr : dist < (float)tthr)) return 0;
+    float tr = 0.f;
+    for (int e = 0; e < 9; ++e) tr = tr + gi[4 + e] * gj[4 + e];
+    const float ca = (tr - 1.f) / 2.f;
+    if (flags & 16u) {
+      const float ang = acosf(ca < -1.f ? -1.f : (ca > 1.f ? 1.f : ca)), athr = acosf((float)cthr);
+      return (flags & 2u) ? ang <= athr : ang < athr;
+    }
+    return (flags & 2u) ? ca >= (float)cthr : ca > (float)cthr;
+  }
+  const double dx = (double)gi[13] - (double)gj[13], dy = (double)gi[14] - (double)gj[14],
+               dz = (double)gi[15] - (double)gj[15];
+  const double dist = sqrt((dx * dx + dy * dy) + dz * dz);
+  if (!((flags & 1u) ? dist <= tthr : dist < tthr)) return 0;
+  double tr = 0.0;
+  for (int e = 0; e < 9; ++e) tr = tr + (double)gi[4 + e] * (double)gj[4 + e];
+  const double ca = (tr - 1.0) / 2.0;
+  if (flags & 16u) {
+    const double ang = acos(ca < -1.0 ? -1.0 : (ca > 1.0 ? 1.0 : ca)), athr = acos(cthr);
+    return (flags & 2u) ? ang <= athr : ang < athr;
+  }
+  return (flags & 2u) ? ca >= cthr : ca > cthr;
+}
+
+int oracle_grasp_nms_opts(const float *grasps, int m, double translation_thresh, double cos_rot_thresh, unsigned flags,
+                          int32_t *keep) {
+  int *order = (int *)malloc(sizeof(int) * (size_t)(m > 0 ? m : 1));
+  unsigned char *dead = (unsigned char *)calloc((size_t)(m > 0 ? m : 1), 1);
+  for (int i = 0; i < m; ++i) order[i] = i;
+  qsort_r(order, (size_t)m, sizeof(int), cmp_desc_stable, (void *)grasps);
+  int nk = 0;
+  for (int a = 0; a < m; ++a) {
+    if (dead[a]) continue;
+    const float *gi = grasps + (size_t)order[a] * 17;
+    keep[nk++] = order[a];
+    for (int c = a + 1; c < m; ++c)
+      if (!dead[c] && nms_pair_opts(gi, grasps + (size_t)order[c] * 17, translation_thresh, cos_rot_thresh, flags))
+        dead[c] = 1;
+  }
+  free(order);
+  free(dead);
+  return nk;
+}
+
 int oracle_grasp_nms(const float *grasps, int m, double translation_thresh, double cos_rot_thresh,
                      int32_t *keep) {
   int *order = (int *)malloc(sizeof(int) * (size_t)(m > 0 ? m : 1));

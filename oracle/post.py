@@ -84,7 +84,7 @@ def collision_detect(scene_points, grasps, voxel_size, approach_dist=0.03, colli
                               return_empty_grasp, empty_thresh, return_ious)
 
 
-def voxel_down_sample(points, voxel_size):
+def voxel_down_sample(points, voxel_size, origin_at_min=False):
     """Restatement of Open3D PointCloud::VoxelDownSample, called at
     collision_detector.py:32-35 (third-party, un-vendored: open3d>=0.8,
     requirements.txt:5 -- PARITY UNPINNED).  origin = min_bound - voxel/2; voxel
@@ -99,7 +99,7 @@ def voxel_down_sample(points, voxel_size):
     p = p[np.isfinite(p).all(axis=1)]
     if p.shape[0] == 0:
         return p.reshape(0, 3)
-    origin = p.min(axis=0) - voxel_size * 0.5
+    origin = p.min(axis=0) - (0.0 if origin_at_min else voxel_size * 0.5)     # B200_VOXEL_ORIGIN_AT_MIN
     q = np.floor((p - origin) / voxel_size)
     p = p[(q < 2097152.0).all(axis=1)]
     key = np.floor((p - origin) / voxel_size).astype(np.int64)
@@ -119,14 +119,20 @@ def voxel_down_sample(points, voxel_size):
     return out
 
 
-def grasp_nms(grasps, translation_thresh=0.03, rotation_thresh=30.0 / 180.0 * math.pi):
+def grasp_nms(grasps, translation_thresh=0.03, rotation_thresh=30.0 / 180.0 * math.pi, flags=0):
     """GraspGroup.nms -> grasp_nms.nms_grasp (third-party C extension, un-vendored,
     no source under /root/reference: PARITY UNPINNED; call sites
-    demo_pointcloud.py:249 etc.).  Returns the kept ROW NUMBERS in score order."""
+    demo_pointcloud.py:249 etc.).  Returns the kept ROW NUMBERS in score order.
+    flags: the open choices of the restatement (B200_NMS_* of include/b200grasp.h); 0 = the default."""
     g = np.ascontiguousarray(grasps, dtype=np.float32)
     m = g.shape[0]
     keep = np.zeros(max(m, 1), np.int32)
-    nk = lib().oracle_grasp_nms(_p(g), m, float(translation_thresh), math.cos(rotation_thresh), _p(keep))
+    if flags:
+        import ctypes
+        nk = lib().oracle_grasp_nms_opts(_p(g), m, ctypes.c_double(float(translation_thresh)),
+                                         ctypes.c_double(math.cos(rotation_thresh)), ctypes.c_uint(flags), _p(keep))
+    else:
+        nk = lib().oracle_grasp_nms(_p(g), m, float(translation_thresh), math.cos(rotation_thresh), _p(keep))
     return keep[:nk].copy()
 
 

@@ -128,3 +128,48 @@ def test_voxel_down_sample_leaves_out_and_reports_invalid_points(b200, oracle_mo
     with pytest.raises(RuntimeError):
         det.detect(b200.GraspGroup(b200.synth.synthetic_grasps(cloud, 16, 1)))
     assert (b200.voxel.voxel_down_sample(cloud, 0.01) == clean).all()  # clean input: unchanged behaviour
+
+
+def test_nms_and_voxel_switches_follow_the_oracle(b200, oracle_mod):
+    """The restated third-party pieces (grasp_nms, open3d voxel_down_sample: parity unpinned) expose their open
+    choices as switches; every setting equals the oracle under the same setting, and the settings that must matter
+    on this input do change the result."""
+    import math
+    from b200grasp import _abi
+    lib = _abi.lib
+    cloud = b200.synth.tabletop_cloud(4000, 2)
+    g = b200.synth.synthetic_grasps(cloud[:150], 900, 6)
+    g[:, 16] = np.arange(900) % 3                                     # three objects
+    # exact boundary cases: grasp 1 sits EXACTLY translation_thresh from grasp 0 with the same rotation
+    g[0, 0], g[1, 0] = 2.0, 1.9
+    g[1, 4:13] = g[0, 4:13]
+    g[0, 13:16] = [0.25, 0.0, 0.5]
+    g[1, 13:16] = [0.25 + 0.03125, 0.0, 0.5]                          # 2^-5: exact in fp32 and fp64
+    gd = torch.from_numpy(g).cuda()
+    cthr = math.cos(30.0 / 180.0 * math.pi)
+    results = {}
+    try:
+        for flags in (0, _abi.NMS_TRANS_INCLUSIVE, _abi.NMS_ROT_INCLUSIVE, _abi.NMS_SAME_OBJECT, _abi.NMS_FP32, _abi.NMS_ACOS,
+                      _abi.NMS_FP32 | _abi.NMS_ACOS | _abi.NMS_TRANS_INCLUSIVE, 31):
+            lib.b200_grasp_nms_set_options(flags)
+            keep, nkeep = b200.ops.grasp_nms(gd, 0.03125, cthr)
+            got = keep[: int(nkeep.item())].cpu().numpy()
+            want = oracle_mod.post.grasp_nms(g, 0.03125, 30.0 / 180.0 * math.pi, flags=flags)
+            assert got.shape == want.shape and (got == want).all(), flags
+            results[flags] = got
+    finally:
+        lib.b200_grasp_nms_set_options(0)
+    assert 1 in results[0] and 1 not in results[_abi.NMS_TRANS_INCLUSIVE]           # the strictness of < matters here
+    assert len(results[_abi.NMS_SAME_OBJECT]) > len(results[0])                     # fewer pairs qualify
+    pts = torch.from_numpy(cloud.astype(np.float64)).cuda()
+    try:
+        lib.b200_voxel_set_options(_abi.VOXEL_ORIGIN_AT_MIN)
+        out, nvox = b200.ops.voxel_down_sample(pts, 0.01)
+        shifted = out[: int(nvox.item())].cpu().numpy()
+    finally:
+        lib.b200_voxel_set_options(0)
+    assert (shifted == oracle_mod.post.voxel_down_sample(cloud.astype(np.float64), 0.01, origin_at_min=True)).all()
+    out, nvox = b200.ops.voxel_down_sample(pts, 0.01)
+    default = out[: int(nvox.item())].cpu().numpy()
+    assert (default == oracle_mod.post.voxel_down_sample(cloud.astype(np.float64), 0.01)).all()
+    assert default.shape != shifted.shape or (default != shifted).any()
