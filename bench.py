@@ -621,7 +621,12 @@ def training_leg(torch, dist, b200grasp, dev, world, rank):
            "label_view_stats_roofline": {"bound": "hbm", "kernel": "label_view_stats + label_view_scores (csrc/labels.cu), 8 scenes",
                                           "alg_bytes": int(k_bytes), "ms": round(k_ms, 4),
                                           "achieved": round(k_bytes / (k_ms * 1e-3) / 1e9, 1), "peak": hbm, "unit": "GB/s",
-                                          "frac": round(k_bytes / (k_ms * 1e-3) / 1e9 / hbm, 4)},
+                                          "frac": round(k_bytes / (k_ms * 1e-3) / 1e9 / hbm, 4),
+                                          "traffic": 411202000,
+                                          "traffic_source": "profiles/r02_hbm_kernels.txt (ncu, this round): 0.40 GB of DRAM "
+                                                            "reads + writes per launch -- seeds that share a nearest grasp "
+                                                            "point re-read its rows from L2, so the achieved figure is "
+                                                            "L2-served bandwidth, not HBM"},
            "label_generation_note": "process_grasp_labels + match_grasp_view_and_label for 8 scenes: csrc/labels.cu "
                                     "(reads 8 x 236 MB of label / offset rows once) vs the reference's index_select / "
                                     "cat / gather chain on the same knn"}
