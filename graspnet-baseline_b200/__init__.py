@@ -30,6 +30,8 @@ def install_dropins():
     sys.modules["pointnet2_utils"] = pointnet2_utils
     sys.modules["knn_modules"] = knn_modules
     sys.modules["collision_detector"] = collision_detector
+    sys.modules["label_generation"] = label_generation       # models/graspnet.py:20
+    sys.modules["loss"] = loss                                # train.py:26
     api = types.ModuleType("graspnetAPI")
     api.GraspGroup = GraspGroup
     sys.modules["graspnetAPI"] = api

@@ -650,6 +650,7 @@ class GraspNetPipeline:
         torch.cuda.synchronize(self.dev)
         self.streams = [torch.cuda.Stream(device=self.dev) for _ in range(depth)]
         self.done = [None] * depth
+        self.uncollected = [False] * depth              # a host result of this slot has not been collected yet
         self.k = 0
 
     @property
@@ -660,6 +661,9 @@ class GraspNetPipeline:
         """queue one scene on the next slot (whose previous scene must have been collected): `cloud` from the host
         (copied through the slot's pinned buffer), or `device_cloud` (N,3) already in HBM"""
         k = self.k % len(self.engines)
+        if self.uncollected[k]:
+            raise RuntimeError("b200grasp: pipeline slot %d still holds an uncollected result (its pinned output buffer "
+                               "would be overwritten): collect() it before submitting scene %d" % (k, self.k))
         self.k += 1
         eng, st = self.engines[k], self.streams[k]
         if cloud is not None:
@@ -676,10 +680,12 @@ class GraspNetPipeline:
             ev = torch.cuda.Event()
             ev.record(st)
         self.done[k] = ev
+        self.uncollected[k] = bool(readback)
         return k
 
     def collect(self, k):
         self.done[k].synchronize()
+        self.uncollected[k] = False
         eng = self.engines[k]
         v = eng.views(eng.host_out, "out")
         n, kk = int(v["nrows0"][0]), int(v["nkept0"][0])

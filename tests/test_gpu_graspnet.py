@@ -284,3 +284,20 @@ def test_backbone_training_step_gradients_match_legacy_ops(b200, legacy):
     assert all(g.abs().max() > 0 for k, g in grads[0].items() if "sa" in k and "weight" in k and "bn" not in k)
     for k in grads[0]:
         close(grads[0][k].cpu().numpy(), grads[1][k].cpu().numpy(), 1e-4, what="grad " + k)
+
+
+@pytest.mark.gpu
+def test_pipeline_refuses_to_overwrite_an_uncollected_result(b200):
+    net = _net(b200, 12).cuda().eval()
+    pipe = b200.graspnet.GraspNetPipeline(net, depth=2, num_point=4000)
+    cloud = b200.synth.tabletop_cloud(4000, 3)
+    a = pipe.submit(cloud)
+    b_ = pipe.submit(cloud)
+    with pytest.raises(RuntimeError):
+        pipe.submit(cloud)                                   # slot `a` again: its host result was never collected
+    ra, rb = pipe.collect(a), pipe.collect(b_)
+    assert ra["nrows"] == rb["nrows"] and (ra["kept"] == rb["kept"]).all()
+    c = pipe.submit(cloud)                                   # fine now
+    assert pipe.collect(c)["nrows"] == ra["nrows"]
+    for _ in range(5):                                       # results that stay on the device need no collect
+        pipe.submit(device_cloud=torch.from_numpy(cloud).cuda(), readback=False)
