@@ -461,6 +461,10 @@ class GraspNetEngine:
         self._out = self.views(self.io_out, "out")
         self.host_in = torch.zeros(self.io_in.numel(), dtype=torch.uint8).pin_memory()
         self.host_out = torch.zeros(self.io_out.numel(), dtype=torch.uint8).pin_memory()
+        # typed views of the pinned buffers, built once (the per-scene host loop of the pipeline is latency-critical)
+        self.host_in_views = self.views(self.host_in, "in")
+        self.host_out_views = self.views(self.host_out, "out")
+        self.host_out_np = {k: v.numpy() for k, v in self.host_out_views.items()}
         self._graph = None
         self._streams = None
         self.launches = 0
@@ -650,6 +654,7 @@ class GraspNetPipeline:
         torch.cuda.synchronize(self.dev)
         self.streams = [torch.cuda.Stream(device=self.dev) for _ in range(depth)]
         self.done = [None] * depth
+        self.events = [torch.cuda.Event() for _ in range(depth)]
         self.uncollected = [False] * depth              # a host result of this slot has not been collected yet
         self.k = 0
 
@@ -667,7 +672,7 @@ class GraspNetPipeline:
         self.k += 1
         eng, st = self.engines[k], self.streams[k]
         if cloud is not None:
-            eng.views(eng.host_in, "in")["cloud"][0].copy_(torch.as_tensor(cloud))
+            eng.host_in_views["cloud"][0].copy_(torch.as_tensor(cloud))
         st.wait_stream(torch.cuda.current_stream(self.dev))
         with torch.cuda.stream(st):
             if device_cloud is not None:
@@ -677,7 +682,7 @@ class GraspNetPipeline:
             eng.run_graph()
             if readback:
                 eng.host_out.copy_(eng.io_out, non_blocking=True)
-            ev = torch.cuda.Event()
+            ev = self.events[k]
             ev.record(st)
         self.done[k] = ev
         self.uncollected[k] = bool(readback)
@@ -686,10 +691,9 @@ class GraspNetPipeline:
     def collect(self, k):
         self.done[k].synchronize()
         self.uncollected[k] = False
-        eng = self.engines[k]
-        v = eng.views(eng.host_out, "out")
+        v = self.engines[k].host_out_np
         n, kk = int(v["nrows0"][0]), int(v["nkept0"][0])
-        return dict(nrows=n, mask=v["mask0"][:n].numpy().astype(bool), kept=v["kept0"][:kk].numpy().copy())
+        return dict(nrows=n, mask=v["mask0"][:n].astype(bool), kept=v["kept0"][:kk].copy())
 
     def join(self):
         """the caller's stream waits for everything submitted so far"""
