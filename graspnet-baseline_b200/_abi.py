@@ -48,6 +48,7 @@ SIGNATURES = {
     "b200_label_view_scores": [_vp, _vp, ctypes.c_longlong, _vp, _vp, _vp],
     "b200_label_top_gather": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _vp],
     "b200_grasp_nms_static": [_vp, _i, _d, _d, _vp, _vp, _vp],
+    "b200_grasp_post_chain": [_vp, _vp, _i, _vp, _vp, _i, _d, _d, _d, _d, _d, _vp, _vp, _vp, _vp, _vp, _sz, _vp],
     "b200_collision_counts_dn": [_vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp],
     "b200_voxel_down_sample": [_vp, _i, _d, _vp, _vp, _vp, _sz, _vp],
     "b200_voxel_down_sample_checked": [_vp, _i, _d, _vp, _vp, _vp, _vp, _sz, _vp],
@@ -86,6 +87,8 @@ lib.b200_voxel_down_sample_workspace.argtypes = [_i]
 lib.b200_voxel_down_sample_workspace.restype = _sz
 lib.b200_collision_mask_workspace.argtypes = [_i]
 lib.b200_collision_mask_workspace.restype = _sz
+lib.b200_grasp_post_chain_workspace.argtypes = [_i]
+lib.b200_grasp_post_chain_workspace.restype = _sz
 lib.b200_label_object_table_bytes.argtypes = [_i]
 lib.b200_label_object_table_bytes.restype = _sz
 lib.b200_mlp_f16_packed_bytes.argtypes = [_i, _i]
@@ -113,10 +116,12 @@ VOXEL_ORIGIN_AT_MIN = 1
 lib.b200_fps_set_speculation.argtypes = [_i]
 lib.b200_fps_set_speculation.restype = None
 
-EXPORTS = sorted(list(SIGNATURES) + ["b200_grasp_nms_workspace", "b200_voxel_down_sample_workspace", "b200_query_grid_workspace", "b200_collision_mask_workspace", "b200_mlp_f16_packed_bytes", "b200_label_object_table_bytes", "b200_grasp_nms_set_options", "b200_voxel_set_options", "b200_error_string", "b200_version", "b200_launch_count"])
+EXPORTS = sorted(list(SIGNATURES) + ["b200_grasp_nms_workspace", "b200_voxel_down_sample_workspace", "b200_query_grid_workspace", "b200_collision_mask_workspace", "b200_grasp_post_chain_workspace", "b200_mlp_f16_packed_bytes", "b200_label_object_table_bytes", "b200_grasp_nms_set_options", "b200_voxel_set_options", "b200_error_string", "b200_version", "b200_launch_count"])
 
 
 def check(code, what):
     """Non-zero status -> RuntimeError (the reference exit(-1)s instead, cuda_utils.h:35-44)."""
     if code != 0:
         raise RuntimeError("%s failed: %s (code %d)" % (what, lib.b200_error_string(code).decode(), code))
+
+POST_CHAIN_MAX_M = 2048                # B200_POST_CHAIN_MAX_M (include/b200grasp.h)

@@ -18,7 +18,7 @@
 // (pinned against the reference itself in tests/golden/collision_*.npz).
 #include <cmath>
 
-#include "common.cuh"
+#include "post_common.cuh"
 
 namespace {
 
@@ -30,7 +30,8 @@ __global__ void __launch_bounds__(CTH)
 collision_kernel(const double *__restrict__ scene, int n, const int32_t *__restrict__ n_dev,
                  const double *__restrict__ T, const double *__restrict__ R,
                  const double *__restrict__ thr, int st, int sr, int sh, int m,
-                 const int32_t *__restrict__ m_dev, int32_t *__restrict__ counts) {
+                 const int32_t *__restrict__ m_dev, int32_t *__restrict__ counts,
+                 const float *__restrict__ rows = nullptr, float fl = 0.f, float fw = 0.f, float ad = 0.f) {
   __shared__ double pts[CPT * 3];
   if (n_dev) n = min(n, __ldg(n_dev));               // scene length produced on the device
   if (m_dev) m = min(m, __ldg(m_dev));               // grasp count produced on the device (decode / compaction)
@@ -43,7 +44,13 @@ collision_kernel(const double *__restrict__ scene, int n, const int32_t *__restr
     pts[i] = i < pn * 3 ? __ldg(scene + (size_t)p0 * 3 + i) : __longlong_as_double(0x7ff8000000000000LL);
   __syncthreads();
   if (g >= m) return;
-  const double *t = T + (size_t)g * st, *r = R + (size_t)g * sr, *h = thr + (size_t)g * sh;   // row strides
+  double tq[3], rq[9], hq[10];
+  const double *t = tq, *r = rq, *h = hq;
+  if (rows) {                                        // fp32 grasp rows: the bounds are derived here (no prep launch)
+    collision_row_params(rows + (size_t)g * 17, fl, fw, ad, tq, rq, hq);
+  } else {
+    t = T + (size_t)g * st; r = R + (size_t)g * sr; h = thr + (size_t)g * sh;              // row strides
+  }
   const double t0 = t[0], t1 = t[1], t2 = t[2];
   const double r0 = r[0], r1 = r[1], r2 = r[2], r3 = r[3], r4 = r[4], r5 = r[5], r6 = r[6],
                r7 = r[7], r8 = r[8];
@@ -151,24 +158,15 @@ __global__ void collision_prep_kernel(const float *__restrict__ grasps, const in
   if (m_dev) m = min(m, __ldg(m_dev));
   const int g = blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= m) return;
-  const float *r = grasps + (size_t)g * 17;
+  double t[3], r[9], h[10];
+  collision_row_params(grasps + (size_t)g * 17, fl, fw, ad, t, r, h);
   double *o = packed + (size_t)g * 22;
-  o[0] = (double)r[13]; o[1] = (double)r[14]; o[2] = (double)r[15];
 #pragma unroll
-  for (int e = 0; e < 9; ++e) o[3 + e] = (double)r[4 + e];
-  const float w = r[1], h = r[2], d = r[3];
-  const float h2 = __fdiv_rn(h, 2.f), w2 = __fdiv_rn(w, 2.f);
-  const float dl = __fsub_rn(d, fl), dlw = __fsub_rn(dl, fw);
-  o[12] = (double)(-h2);                       // -h/2
-  o[13] = (double)h2;                          //  h/2
-  o[14] = (double)dl;                          //  d - finger_length
-  o[15] = (double)d;
-  o[16] = (double)(-__fadd_rn(w2, fw));        // -(w/2 + finger_width)
-  o[17] = (double)(-w2);
-  o[18] = (double)__fadd_rn(w2, fw);
-  o[19] = (double)w2;
-  o[20] = (double)dlw;                         //  d - finger_length - finger_width
-  o[21] = (double)__fsub_rn(dlw, ad);          //  ... - approach_dist
+  for (int e = 0; e < 3; ++e) o[e] = t[e];
+#pragma unroll
+  for (int e = 0; e < 9; ++e) o[3 + e] = r[e];
+#pragma unroll
+  for (int e = 0; e < 10; ++e) o[12 + e] = h[e];
 }
 
 // counts -> mask: global_iou = count / (volume + 1e-6) > collision_thresh
@@ -178,15 +176,7 @@ __global__ void collision_finalize_kernel(const float *__restrict__ grasps, cons
   if (m_dev) m = min(m, __ldg(m_dev));
   const int g = blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= m) return;
-  const float w = grasps[(size_t)g * 17 + 1], h = grasps[(size_t)g * 17 + 2];
-  const float fw2 = __fmul_rn(2.f, fw);                                                   // 2*finger_width (weak scalar)
-  const float lrv = __fdiv_rn(__fmul_rn(__fmul_rn(h, fl), fw), vox3);
-  const float hw = __fmul_rn(h, __fadd_rn(w, fw2));
-  const float bot = __fdiv_rn(__fmul_rn(hw, fw), vox3);
-  const float shf = __fdiv_rn(__fmul_rn(hw, ad), vox3);
-  const float vol = __fadd_rn(__fadd_rn(__fmul_rn(lrv, 2.f), bot), shf);
-  const double iou = __ddiv_rn((double)counts[(size_t)g * 6], (double)__fadd_rn(vol, 1e-6f));
-  mask[g] = iou > thresh ? 1 : 0;
+  mask[g] = collision_row_collides(grasps + (size_t)g * 17, counts[(size_t)g * 6], fl, fw, ad, vox3, thresh) ? 1 : 0;
 }
 
 }  // namespace
@@ -219,6 +209,24 @@ extern "C" int b200_collision_mask_device(const double *scene, const int32_t *n_
   if (rc) return rc;
   collision_finalize_kernel<<<blocks, 128, 0, cs>>>(grasps, counts, m_dev, m_max, fl, fw, ad, vox3, collision_thresh,
                                                     mask);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+// the point-in-gripper counts of fp32 grasp rows, their bounds derived inside the kernel (post_chain.cu)
+int b200i_collision_counts_rows(const double *scene, const int32_t *n_dev, int n_max, const float *rows,
+                                const int32_t *m_dev, int m_max, float fl, float fw, float ad, int32_t *counts,
+                                cudaStream_t st) {
+  if (n_max < 0 || m_max < 0) return B200_EINVAL;
+  if (m_max == 0) return 0;
+  if (!counts || !rows) return B200_EINVAL;
+  B200_CUDA(cudaMemsetAsync(counts, 0, sizeof(int32_t) * 6 * (size_t)m_max, st));
+  if (n_max == 0) return 0;
+  if (!scene) return B200_EINVAL;
+  if (ceil_div(n_max, CPT) > 65535) return B200_ECAPACITY;
+  dim3 grid((unsigned)ceil_div(m_max, CTH), (unsigned)ceil_div(n_max, CPT));
+  collision_kernel<<<grid, CTH, 0, st>>>(scene, n_max, n_dev, nullptr, nullptr, nullptr, 0, 0, 0, m_max, m_dev, counts, rows,
+                                         fl, fw, ad);
   B200_LAUNCH_CHECK();
   return 0;
 }

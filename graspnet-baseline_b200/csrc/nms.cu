@@ -16,7 +16,7 @@
 //                      OR-ed into the remaining removed-words (warp = column word, lane = row,
 //                      one load per lane + a warp OR reduction); finally a popc prefix
 //                      compacts the survivors.
-#include "common.cuh"
+#include "post_common.cuh"
 
 namespace {
 
@@ -32,7 +32,7 @@ nms_rank_kernel(const float *__restrict__ grasps, int m, const int32_t *__restri
   const int i = blockIdx.x * RT + threadIdx.x;
   // scores are ranked under a TOTAL order -- NaN counts as -inf, ties by row number -- so that the ranks are always a
   // permutation (with the plain comparisons NaN rows collided and left order[] slots unwritten: garbage row numbers)
-  auto key = [](float s) { return isnan(s) ? -INFINITY : s; };
+  auto key = [](float s) { return nms_score_key(s); };
   const float si = i < m ? key(__ldg(grasps + (size_t)i * G)) : 0.f;
   int rank = 0;
   for (int j0 = 0; j0 < m; j0 += RT) {
@@ -147,7 +147,8 @@ constexpr int MAXW = 512;                    // 32768 grasps / 64
 __global__ void __launch_bounds__(ST)
 nms_sweep_kernel(const unsigned long long *__restrict__ mask, const int32_t *__restrict__ order, int m,
                  const int32_t *__restrict__ m_dev, int Ws, int32_t *__restrict__ keep,
-                 int32_t *__restrict__ nkeep) {
+                 int32_t *__restrict__ nkeep, const float *__restrict__ rows = nullptr,
+                 float *__restrict__ out_rows = nullptr) {
   __shared__ unsigned long long removed[MAXW];
   __shared__ unsigned long long diag[64];
   __shared__ unsigned long long s_keep;
@@ -214,6 +215,17 @@ nms_sweep_kernel(const unsigned long long *__restrict__ mask, const int32_t *__r
       keep[pos++] = __ldg(order + w * 64 + bit);
     }
   }
+  if (out_rows) {                              // the fused chain: the kept rows themselves, in score order
+    __syncthreads();                           // keep[] and s_prefix settled (same CTA: global writes are visible)
+    __shared__ int s_total;
+    if (tid == 0) s_total = *nkeep;
+    __syncthreads();
+    const int total = s_total * G;
+    for (int t = tid; t < total; t += ST) {
+      const int i = t / G, c = t - i * G;
+      out_rows[t] = rows[(size_t)keep[i] * G + c];
+    }
+  }
 }
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -268,6 +280,26 @@ extern "C" int b200_grasp_nms_device(const float *grasps, const int32_t *m_dev, 
   if (!m_dev) return B200_EINVAL;
   return nms_launch(grasps, m_max, m_dev, translation_thresh, cos_rotation_thresh, keep, nkeep, workspace,
                     workspace_bytes, (cudaStream_t)stream);
+}
+
+// mask + sweep for rows whose score order is already known (post_chain.cu); the sweep gathers the kept rows
+int b200i_nms_ranked(const float *grasps, const int32_t *m_dev, int m_max, const int32_t *order, double translation_thresh,
+                     double cos_rotation_thresh, int32_t *keep, int32_t *nkeep, float *out_rows,
+                     unsigned long long *mask_ws, cudaStream_t st) {
+  if (m_max < 0 || !nkeep || !m_dev) return B200_EINVAL;
+  if (m_max == 0) {
+    B200_CUDA(cudaMemsetAsync(nkeep, 0, sizeof(int32_t), st));
+    return 0;
+  }
+  if (!grasps || !keep || !order || !mask_ws) return B200_EINVAL;
+  if (m_max > 32768) return B200_ECAPACITY;
+  const int W = (m_max + 63) / 64;
+  nms_mask_kernel<<<dim3((unsigned)W, (unsigned)W), 64, 0, st>>>(grasps, order, m_max, m_dev, W, translation_thresh,
+                                                                cos_rotation_thresh, g_nms_flags, mask_ws);
+  B200_LAUNCH_CHECK();
+  nms_sweep_kernel<<<1, ST, 0, st>>>(mask_ws, order, m_max, m_dev, W, keep, nkeep, grasps, out_rows);
+  B200_LAUNCH_CHECK();
+  return 0;
 }
 
 // ---- No-allocation variant (no counterpart in the reference) -----------

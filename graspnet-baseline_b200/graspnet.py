@@ -576,14 +576,22 @@ class GraspNetEngine:
             with torch.cuda.stream(sp):
                 n_s = nrows[s:s + 1]
                 o = self._out                          # results go straight into the one output buffer
-                mask = ops.collision_mask_device(voxels[s][0], voxels[s][1], rows[s], n_s, P["voxel_size"],
-                                                 P["approach_dist"], P["collision_thresh"], out=o["mask%d" % s])
-                free, nfree = ops.compact_rows(rows[s], mask, n_s)
-                k, nk = ops.grasp_nms_device(free, nfree, P["translation_thresh"], math.cos(P["rotation_thresh"]),
-                                             out=o["kept%d" % s], out_count=o["nkept%d" % s])
-                o["nrows%d" % s].copy_(n_s)
+                if rows.shape[1] <= ops.POST_CHAIN_MAX_M:
+                    k, nk, mask = ops.grasp_post_chain(voxels[s][0], voxels[s][1], rows[s], n_s, P["voxel_size"],
+                                                       P["approach_dist"], P["collision_thresh"],
+                                                       P["translation_thresh"], math.cos(P["rotation_thresh"]),
+                                                       out_mask=o["mask%d" % s], out=o["kept%d" % s],
+                                                       out_count=o["nkept%d" % s], out_nrows=o["nrows%d" % s])
+                else:
+                    mask = ops.collision_mask_device(voxels[s][0], voxels[s][1], rows[s], n_s, P["voxel_size"],
+                                                     P["approach_dist"], P["collision_thresh"], out=o["mask%d" % s])
+                    free, nfree = ops.compact_rows(rows[s], mask, n_s)
+                    k, nk = ops.grasp_nms_device(free, nfree, P["translation_thresh"],
+                                                 math.cos(P["rotation_thresh"]), out=o["kept%d" % s],
+                                                 out_count=o["nkept%d" % s])
+                    o["nrows%d" % s].copy_(n_s)
+                    hold += [free, nfree]
                 kept.append((k, nk, mask))
-                hold += [free, nfree]
         for sp in s_post[:B]:
             main.wait_stream(sp)
         for c in (s_chk if nested else []):

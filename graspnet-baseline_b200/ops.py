@@ -720,6 +720,46 @@ def grasp_nms_device(grasps, m_dev, translation_thresh, cos_rotation_thresh, out
     return out, nkeep
 
 
+POST_CHAIN_MAX_M = 2048                  # B200_POST_CHAIN_MAX_M (include/b200grasp.h)
+
+
+def grasp_post_chain(scene, n_dev, grasps, m_dev, voxel_size, approach_dist, collision_thresh, translation_thresh,
+                     cos_rotation_thresh, out_mask=None, out=None, out_count=None, out_nrows=None):
+    """collision_mask_device + compact_rows + grasp_nms_device in one call and five graph nodes (csrc/post_chain.cu;
+    same arithmetic, same results): scene (N,3) f64 (+ n_dev), grasps (Mmax <= POST_CHAIN_MAX_M, 17) f32 with m_dev
+    valid rows -> (kept rows (Mmax,17) in score order, nkept (1,) i32, collision mask (Mmax,) u8).
+    `out_mask` / `out` / `out_count`: buffers to write into; `out_nrows`: (1,) i32 that receives the valid row count."""
+    _chk(scene, "scene", torch.float64)
+    _chk(grasps, "grasps", torch.float32)
+    _chk(m_dev, "m_dev", torch.int32)
+    if n_dev is not None:
+        _chk(n_dev, "n_dev", torch.int32)
+    m = grasps.shape[0]
+    if m > POST_CHAIN_MAX_M:
+        raise ValueError("b200grasp: grasp_post_chain handles at most %d rows (use the separate calls)" % POST_CHAIN_MAX_M)
+    dev = grasps.device
+    mask = torch.zeros((m,), dtype=torch.uint8, device=dev) if out_mask is None else out_mask
+    kept = torch.empty_like(grasps) if out is None else out
+    nkept = torch.empty((1,), dtype=torch.int32, device=dev) if out_count is None else out_count
+    _chk(mask, "out_mask", torch.uint8)
+    _chk(kept, "out", torch.float32)
+    _chk(nkept, "out_count", torch.int32)
+    if out_nrows is not None:
+        _chk(out_nrows, "out_nrows", torch.int32)
+    if mask.numel() != m or tuple(kept.shape) != tuple(grasps.shape):
+        raise ValueError("b200grasp: output buffers must match the grasp rows")
+    nbytes = _lib.b200_grasp_post_chain_workspace(m)
+    ws = torch.empty((nbytes,), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        _abi.check(_lib.b200_grasp_post_chain(_ptr(scene), _ptr(n_dev) if n_dev is not None else None, scene.shape[0],
+                                              _ptr(grasps), _ptr(m_dev), m, float(voxel_size), float(approach_dist),
+                                              float(collision_thresh), float(translation_thresh),
+                                              float(cos_rotation_thresh), _ptr(mask), _ptr(kept), _ptr(nkept),
+                                              _ptr(out_nrows) if out_nrows is not None else None, _ptr(ws), nbytes,
+                                              _stream()), "grasp_post_chain")
+    return kept, nkept, mask
+
+
 def voxel_down_sample(points, voxel_size, return_bad=False):
     """points (N,3) f64 -> (out (N,3) f64 of which the first nvox rows are valid, nvox (1,) i32), both on
     the device   [utils/collision_detector.py:32-35 -> open3d voxel_down_sample, restated].

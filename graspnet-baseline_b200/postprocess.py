@@ -20,10 +20,15 @@ from . import ops as _ext
 
 
 def grasp_postprocess_device(cloud, rows, nrows, voxel_size=0.01, approach_dist=0.05, collision_thresh=0.01,
-                             translation_thresh=0.03, rotation_thresh=30.0 / 180.0 * math.pi):
+                             translation_thresh=0.03, rotation_thresh=30.0 / 180.0 * math.pi, separate_calls=False):
     """cloud (N,3) f32/f64 device tensor; rows (Mmax,17) f32 with nrows (1,) i32 valid rows (e.g. one scene of
-    pred_decode_device) -> (kept rows (Mmax,17) f32 in score order, nkept (1,) i32, collision mask (Mmax,) u8)."""
+    pred_decode_device) -> (kept rows (Mmax,17) f32 in score order, nkept (1,) i32, collision mask (Mmax,) u8).
+    Up to ops.POST_CHAIN_MAX_M rows the stages after the voxel grid run as one fused call (csrc/post_chain.cu);
+    `separate_calls=True` forces the call-by-call sequence (identical results)."""
     scene, nvox = _ext.voxel_down_sample(cloud.double().contiguous(), voxel_size)
+    if rows.shape[0] <= _ext.POST_CHAIN_MAX_M and not separate_calls:
+        return _ext.grasp_post_chain(scene, nvox, rows, nrows, voxel_size, approach_dist, collision_thresh,
+                                     translation_thresh, math.cos(rotation_thresh))
     mask = _ext.collision_mask_device(scene, nvox, rows, nrows, voxel_size, approach_dist, collision_thresh)
     free, nfree = _ext.compact_rows(rows, mask, nrows)
     kept, nkept = _ext.grasp_nms_device(free, nfree, translation_thresh, math.cos(rotation_thresh))

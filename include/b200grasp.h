@@ -380,6 +380,21 @@ int b200_grasp_nms(const float *grasps, int m, double translation_thresh, double
 int b200_grasp_nms_static(const float *grasps, int m, double translation_thresh, double cos_rotation_thresh,
                           int32_t *keep, int32_t *nkeep, void *stream);
 
+/* The whole sequence after pred_decode in one call (five graph nodes instead of nine):
+ *   gg = gg[~mfcdetector.detect(gg, approach_dist, collision_thresh)]; gg = gg.nms()
+ * (test.py:93-96, demo_pointcloud.py:228-249; = b200_collision_mask_device + b200_compact_rows +
+ * b200_grasp_nms_device + b200_gather_rows, same arithmetic, bit-identical results).  scene: (n_max, 3) fp64 voxel
+ * centres of which *n_dev are valid (n_dev may be NULL); grasps: (m_max, 17) fp32 rows of which *m_dev are valid,
+ * m_max <= B200_POST_CHAIN_MAX_M (else B200_ECAPACITY: use the separate calls).  Outputs: collision_mask (m_max) u8,
+ * kept_rows (m_max, 17) in score order with *nkept rows valid, and (optional) *nrows_out = the valid row count. */
+#define B200_POST_CHAIN_MAX_M 2048
+size_t b200_grasp_post_chain_workspace(int m_max);
+int b200_grasp_post_chain(const double *scene, const int32_t *n_dev, int n_max, const float *grasps,
+                          const int32_t *m_dev, int m_max, double voxel_size, double approach_dist,
+                          double collision_thresh, double translation_thresh, double cos_rotation_thresh,
+                          uint8_t *collision_mask, float *kept_rows, int32_t *nkept, int32_t *nrows_out,
+                          void *workspace, size_t workspace_bytes, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

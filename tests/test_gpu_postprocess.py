@@ -173,3 +173,47 @@ def test_nms_and_voxel_switches_follow_the_oracle(b200, oracle_mod):
     default = out[: int(nvox.item())].cpu().numpy()
     assert (default == oracle_mod.post.voxel_down_sample(cloud.astype(np.float64), 0.01)).all()
     assert default.shape != shifted.shape or (default != shifted).any()
+
+
+@pytest.mark.parametrize("m,pad,flags", [(2048, 0, 0), (1500, 37, 0), (129, 0, 0), (1000, 24, "same_object"),
+                                         (640, 0, "fp32"), (1, 0, 0), (0, 16, 0)])
+def test_fused_chain_equals_separate_calls(b200, m, pad, flags):
+    """csrc/post_chain.cu (five graph nodes) against collision_mask_device -> compact_rows -> grasp_nms_device ->
+    gather_rows on the same rows: NaN scores, tied scores, padded garbage rows, the NMS switches; bit for bit"""
+    cloud = b200.synth.tabletop_cloud(20000, 77)
+    g = make_grasps(b200, cloud, max(m, 1), 900 + m)[:m]
+    if m >= 64:
+        g[5:25, 0] = np.float32(0.5)                                    # ties
+        g[40:44, 0] = np.nan                                            # NaN scores rank last, in row order
+        g[:, 16] = np.arange(m) % 3
+    rows = np.concatenate([g, np.full((pad, 17), np.nan, np.float32)]) if pad else g
+    rows_d = torch.from_numpy(np.ascontiguousarray(rows)).cuda()
+    nrows = torch.full((1,), m, dtype=torch.int32, device="cuda")
+    cloud_d = torch.from_numpy(cloud).cuda()
+    opt = {0: 0, "same_object": b200._abi.NMS_SAME_OBJECT, "fp32": b200._abi.NMS_FP32 | b200._abi.NMS_ROT_INCLUSIVE}[flags]
+    b200._abi.lib.b200_grasp_nms_set_options(opt)
+    try:
+        a = b200.grasp_postprocess_device(cloud_d, rows_d, nrows, 0.01, 0.05, 0.01)
+        c = b200.grasp_postprocess_device(cloud_d, rows_d, nrows, 0.01, 0.05, 0.01, separate_calls=True)
+    finally:
+        b200._abi.lib.b200_grasp_nms_set_options(0)
+    ka, kc = int(a[1].item()), int(c[1].item())
+    assert ka == kc
+    if m >= 64:
+        assert 0 < ka < m
+    assert torch.equal(a[2][:m], c[2][:m])
+    ra, rc = a[0][:ka].cpu().numpy(), c[0][:kc].cpu().numpy()
+    assert (ra.view(np.uint32) == rc.view(np.uint32)).all()             # bit patterns: the rows hold NaN scores
+
+
+def test_fused_chain_refuses_more_rows_than_its_limit(b200):
+    rows = torch.zeros((b200.ops.POST_CHAIN_MAX_M + 1, 17), device="cuda")
+    scene = torch.zeros((4, 3), dtype=torch.float64, device="cuda")
+    n = torch.full((1,), 4, dtype=torch.int32, device="cuda")
+    with pytest.raises(ValueError):
+        b200.ops.grasp_post_chain(scene, n, rows, n, 0.01, 0.05, 0.01, 0.03, 0.8)
+    ws = torch.empty((1 << 20,), dtype=torch.uint8, device="cuda")
+    rc = b200._abi.lib.b200_grasp_post_chain(scene.data_ptr(), n.data_ptr(), 4, rows.data_ptr(), n.data_ptr(),
+                                             rows.shape[0], 0.01, 0.05, 0.01, 0.03, 0.8, ws.data_ptr(), ws.data_ptr(),
+                                             n.data_ptr(), None, ws.data_ptr(), ws.numel(), None)
+    assert rc == -2                                                      # B200_ECAPACITY
