@@ -6,146 +6,170 @@
 // score = score * tolerance / 0.05, rotation from the (negated) approach view and the angle, and the rows of the
 // seeds whose objectness argmax is 1 compacted IN SEED ORDER into the (M,17) layout the collision detector and
 // NMS read: [score, width, 0.02, depth, R(9 row-major), centre(3), -1].  The reference does this with ~40 small
-// torch launches and a boolean-mask compaction per scene; here it is one launch for the whole batch, one CTA per
-// scene (1024 seeds = one pass), and the row count stays on the device.
+// torch launches and a boolean-mask compaction per scene; here it is one launch for the whole batch, 128 seeds per
+// CTA, and the row count stays on the device.
 //
 // Exactness: classes, depth, width, score and centre are selections of inputs or single-rounded fp32 expressions
 // in the reference's order (bit-exact against the reference, tests/golden/decode_*.npz); the rotation goes through
 // norms, sin/cos and a 3x3 product and is compared to 1e-6.  torch.argmax returns the FIRST maximum; the strict `>`
 // scans below do the same.  The reference calls torch.cross without `dim`: with exactly three surviving seeds the
-// cross product runs down the rows (first dimension of size 3) -- reproduced by the fix-up at the end.
+// cross product runs down the rows (first dimension of size 3) -- reproduced (the `total == 3` branch).
 #include "common.cuh"
 
 namespace {
 
-constexpr int DT = 1024;
+constexpr int DT = 128;       // seeds per CTA
 constexpr int MAXD = 8;
 
 struct Frame { float ax[3], ay[3], s, c; };
+struct Decoded { float score, width, depth, angle; };
 
+// one seed: best in-plane angle class per depth (first maximum over A), best depth (first maximum over the gathered
+// scores), then width / score / depth / angle of that (angle, depth) cell   [models/graspnet.py:92-118]
+__device__ __forceinline__ Decoded decode_seed(const float *__restrict__ sc, const float *__restrict__ cl,
+                                               const float *__restrict__ wd, const float *__restrict__ tl, int i, int ns,
+                                               int na, int nd, int vec4) {
+  int a_of[MAXD];
+  if (vec4) {
+    // D = 4: the four depths of (angle class a, seed i) are one aligned float4; the A loads are independent
+    const float4 *c4 = reinterpret_cast<const float4 *>(cl) + i;
+    float4 cb = __ldg(c4);
+    a_of[0] = a_of[1] = a_of[2] = a_of[3] = 0;
+#pragma unroll 4
+    for (int a = 1; a < na; ++a) {
+      const float4 c = __ldg(c4 + (size_t)a * ns);
+      if (c.x > cb.x) { cb.x = c.x; a_of[0] = a; }
+      if (c.y > cb.y) { cb.y = c.y; a_of[1] = a; }
+      if (c.z > cb.z) { cb.z = c.z; a_of[2] = a; }
+      if (c.w > cb.w) { cb.w = c.w; a_of[3] = a; }
+    }
+  } else {
+    for (int d = 0; d < nd; ++d) {
+      int a_best = 0;
+      float c_best = __ldg(cl + ((size_t)0 * ns + i) * nd + d);
+      for (int a = 1; a < na; ++a) {
+        const float c = __ldg(cl + ((size_t)a * ns + i) * nd + d);
+        if (c > c_best) { c_best = c; a_best = a; }
+      }
+      a_of[d] = a_best;
+    }
+  }
+  float s_of[MAXD];
+#pragma unroll
+  for (int d = 0; d < MAXD; ++d)
+    if (d < nd) s_of[d] = __ldg(sc + ((size_t)a_of[d] * ns + i) * nd + d);
+  int d_best = 0;
+#pragma unroll
+  for (int d = 1; d < MAXD; ++d)
+    if (d < nd && s_of[d] > s_of[d_best]) d_best = d;
+  // (static indexing keeps a_of / s_of in registers)
+  int a_best = a_of[0];
+  float best = s_of[0];
+#pragma unroll
+  for (int d = 1; d < MAXD; ++d)
+    if (d == d_best) { a_best = a_of[d]; best = s_of[d]; }
+  const size_t at = ((size_t)a_best * ns + i) * nd + d_best;
+  Decoded o;
+  o.width = fminf(fmaxf(__fmul_rn(1.2f, __ldg(wd + at)), 0.f), 0.1f);
+  o.score = __fdiv_rn(__fmul_rn(best, __ldg(tl + at)), 0.05f);
+  o.depth = __fmul_rn((float)(d_best + 1), 0.01f);
+  o.angle = __fmul_rn(__fdiv_rn((float)a_best, 12.f), 3.14159265358979323846f);
+  return o;
+}
+
+// approach axis, in-plane y axis and sin / cos of the angle   [utils/loss_utils.py:68-96]
+__device__ __forceinline__ Frame seed_frame(const float *__restrict__ vw, int i, float angle) {
+  const float tx = -__ldg(vw + 3 * (size_t)i), ty = -__ldg(vw + 3 * (size_t)i + 1), tz = -__ldg(vw + 3 * (size_t)i + 2);
+  float yx = -ty, yy = tx;                                      // axis_y = (-x1, x0, 0)
+  if (sqrtf(yx * yx + yy * yy) == 0.f) yy = 1.f;
+  const float nx = sqrtf(tx * tx + ty * ty + tz * tz), ny = sqrtf(yx * yx + yy * yy);
+  Frame f;
+  f.ax[0] = tx / nx; f.ax[1] = ty / nx; f.ax[2] = tz / nx;
+  f.ay[0] = yx / ny; f.ay[1] = yy / ny; f.ay[2] = 0.f / ny;
+  f.s = sinf(angle); f.c = cosf(angle);
+  return f;
+}
+
+// grid (ceil(ns / DT), scenes).  The rows are compacted in seed order across the CTAs of a scene without any
+// exchange: every CTA counts the kept seeds in front of its own range itself (2 floats per seed, L2-resident).
 __global__ void __launch_bounds__(DT)
 pred_decode_kernel(const float *__restrict__ objectness, const float *__restrict__ score,
                    const float *__restrict__ angle_cls, const float *__restrict__ width,
                    const float *__restrict__ tol, const float *__restrict__ xyz, const float *__restrict__ view,
                    int ns, int na, int nd, int vec4, float *__restrict__ rows, int32_t *__restrict__ nrows) {
-  __shared__ int warp_sum[DT / 32];
-  __shared__ int s_base;
+  __shared__ int warp_sum[DT / 32], warp_before[DT / 32], warp_total[DT / 32];
+  __shared__ int s_three[3], s_nthree;
   __shared__ Frame first3[3];
-  const int scene = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int scene = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int i_first = blockIdx.x * DT;
   const size_t head = (size_t)scene * na * ns * nd;
   const float *obj = objectness + (size_t)scene * 2 * ns;
   const float *sc = score + head, *cl = angle_cls + head, *wd = width + head, *tl = tol + head;
   const float *ctr = xyz + (size_t)scene * ns * 3, *vw = view + (size_t)scene * ns * 3;
   float *out = rows + (size_t)scene * ns * 17;
-  if (tid == 0) s_base = 0;
+  auto kept = [&](int i) { return __ldg(obj + ns + i) > __ldg(obj + i); };   // argmax over 2 == 1 (first maximum wins a tie)
+  // kept seeds in front of this CTA's range, and in the whole scene
+  int n_before = 0, n_total = 0;
+  for (int i = tid; i < ns; i += DT) {
+    const int k = kept(i) ? 1 : 0;
+    n_total += k;
+    n_before += i < i_first ? k : 0;
+  }
+  n_before = __reduce_add_sync(0xffffffffu, n_before);
+  n_total = __reduce_add_sync(0xffffffffu, n_total);
+  if (tid == 0) s_nthree = 0;
+  if (lane == 0) { warp_before[warp] = n_before; warp_total[warp] = n_total; }
   __syncthreads();
-  for (int i0 = 0; i0 < ns; i0 += DT) {
-    const int i = i0 + tid;
-    bool keep = false;
-    float g_score = 0.f, g_width = 0.f, g_depth = 0.f, g_angle = 0.f;
-    if (i < ns) {
-      keep = __ldg(obj + ns + i) > __ldg(obj + i);                 // argmax over 2 == 1 (first maximum wins a tie)
-      float best = 0.f;
-      int a_of[MAXD];
-      if (vec4) {
-        // D = 4: the four depths of (angle class a, seed i) are one aligned float4; the A loads are independent
-        const float4 *c4 = reinterpret_cast<const float4 *>(cl) + i;
-        float4 cb = __ldg(c4);
-        a_of[0] = a_of[1] = a_of[2] = a_of[3] = 0;
-#pragma unroll 4
-        for (int a = 1; a < na; ++a) {
-          const float4 c = __ldg(c4 + (size_t)a * ns);
-          if (c.x > cb.x) { cb.x = c.x; a_of[0] = a; }
-          if (c.y > cb.y) { cb.y = c.y; a_of[1] = a; }
-          if (c.z > cb.z) { cb.z = c.z; a_of[2] = a; }
-          if (c.w > cb.w) { cb.w = c.w; a_of[3] = a; }
-        }
-      } else {
-        for (int d = 0; d < nd; ++d) {
-          // angle class of this depth: first maximum over the A class scores
-          int a_best = 0;
-          float c_best = __ldg(cl + ((size_t)0 * ns + i) * nd + d);
-          for (int a = 1; a < na; ++a) {
-            const float c = __ldg(cl + ((size_t)a * ns + i) * nd + d);
-            if (c > c_best) { c_best = c; a_best = a; }
-          }
-          a_of[d] = a_best;
-        }
-      }
-      float s_of[MAXD];
+  int before = 0, total = 0;
 #pragma unroll
-      for (int d = 0; d < MAXD; ++d)
-        if (d < nd) s_of[d] = __ldg(sc + ((size_t)a_of[d] * ns + i) * nd + d);
-      int d_best = 0;
-#pragma unroll
-      for (int d = 1; d < MAXD; ++d)
-        if (d < nd && s_of[d] > s_of[d_best]) d_best = d;     // depth class: first maximum of the gathered scores
-      {
-        // (static indexing keeps a_of / s_of in registers)
-        int a_best = a_of[0];
-        best = s_of[0];
-#pragma unroll
-        for (int d = 1; d < MAXD; ++d)
-          if (d == d_best) { a_best = a_of[d]; best = s_of[d]; }
-        const size_t at = ((size_t)a_best * ns + i) * nd + d_best;
-        const float w = __fmul_rn(1.2f, __ldg(wd + at));
-        g_width = fminf(fmaxf(w, 0.f), 0.1f);
-        g_score = __fdiv_rn(__fmul_rn(best, __ldg(tl + at)), 0.05f);
-        g_depth = __fmul_rn((float)(d_best + 1), 0.01f);
-        g_angle = __fmul_rn(__fdiv_rn((float)a_best, 12.f), 3.14159265358979323846f);
-      }
-    }
-    // order-preserving compaction: block exclusive scan of the keep flags
-    const unsigned bal = __ballot_sync(0xffffffffu, keep);
-    if (lane == 0) warp_sum[warp] = __popc(bal);
+  for (int w = 0; w < DT / 32; ++w) { before += warp_before[w]; total += warp_total[w]; }
+  if (blockIdx.x == 0 && tid == 0) nrows[scene] = total;
+  if (total == 3) {
+    // torch.cross(axis_x, axis_y) without `dim` on (3,3) inputs is the cross product of the COLUMNS: each of the
+    // three rows needs the frames of the other two.  Every CTA decodes the three seeds again (rare, and cheap).
+    for (int i = tid; i < ns; i += DT)
+      if (kept(i)) s_three[atomicAdd(&s_nthree, 1)] = i;
     __syncthreads();
-    int before = s_base;
-    for (int w = 0; w < warp; ++w) before += warp_sum[w];
-    const int pos = before + __popc(bal & lanemask_lt());
-    if (keep) {
-      const float tx = -__ldg(vw + 3 * (size_t)i), ty = -__ldg(vw + 3 * (size_t)i + 1), tz = -__ldg(vw + 3 * (size_t)i + 2);
-      float yx = -ty, yy = tx;                                      // axis_y = (-x1, x0, 0)
-      if (sqrtf(yx * yx + yy * yy) == 0.f) yy = 1.f;
-      const float nx = sqrtf(tx * tx + ty * ty + tz * tz), ny = sqrtf(yx * yx + yy * yy);
-      const float ax0 = tx / nx, ax1 = ty / nx, ax2 = tz / nx;
-      const float ay0 = yx / ny, ay1 = yy / ny, ay2 = 0.f / ny;
-      const float az0 = ax1 * ay2 - ax2 * ay1, az1 = ax2 * ay0 - ax0 * ay2, az2 = ax0 * ay1 - ax1 * ay0;
-      const float s = sinf(g_angle), c = cosf(g_angle);
-      float *r = out + (size_t)pos * 17;
-      r[0] = g_score; r[1] = g_width; r[2] = 0.02f; r[3] = g_depth;
-      r[4] = ax0; r[5] = ay0 * c + az0 * s; r[6] = az0 * c - ay0 * s;
-      r[7] = ax1; r[8] = ay1 * c + az1 * s; r[9] = az1 * c - ay1 * s;
-      r[10] = ax2; r[11] = ay2 * c + az2 * s; r[12] = az2 * c - ay2 * s;
-      r[13] = __ldg(ctr + 3 * (size_t)i); r[14] = __ldg(ctr + 3 * (size_t)i + 1); r[15] = __ldg(ctr + 3 * (size_t)i + 2);
-      r[16] = -1.f;
-      if (pos < 3) {
-        Frame &f = first3[pos];
-        f.ax[0] = ax0; f.ax[1] = ax1; f.ax[2] = ax2;
-        f.ay[0] = ay0; f.ay[1] = ay1; f.ay[2] = ay2;
-        f.s = s; f.c = c;
-      }
+    if (tid == 0) {                                                     // seed order
+      if (s_three[0] > s_three[1]) { const int t = s_three[0]; s_three[0] = s_three[1]; s_three[1] = t; }
+      if (s_three[1] > s_three[2]) { const int t = s_three[1]; s_three[1] = s_three[2]; s_three[2] = t; }
+      if (s_three[0] > s_three[1]) { const int t = s_three[0]; s_three[0] = s_three[1]; s_three[1] = t; }
     }
     __syncthreads();
-    if (tid == DT - 1) s_base = pos + (keep ? 1 : 0);
+    if (tid < 3) first3[tid] = seed_frame(vw, s_three[tid], decode_seed(sc, cl, wd, tl, s_three[tid], ns, na, nd, vec4).angle);
     __syncthreads();
   }
-  if (tid == 0) {
-    const int total = s_base;
-    nrows[scene] = total;
-    if (total == 3) {
-      // torch.cross(axis_x, axis_y) without `dim` on (3,3) inputs: the cross product of the COLUMNS
-      for (int j = 0; j < 3; ++j) {
-        const float a0 = first3[0].ax[j], a1 = first3[1].ax[j], a2 = first3[2].ax[j];
-        const float b0 = first3[0].ay[j], b1 = first3[1].ay[j], b2 = first3[2].ay[j];
-        const float z[3] = {a1 * b2 - a2 * b1, a2 * b0 - a0 * b2, a0 * b1 - a1 * b0};
-        for (int i = 0; i < 3; ++i) {
-          float *r = out + (size_t)i * 17 + 4 + 3 * j;
-          r[1] = first3[i].ay[j] * first3[i].c + z[i] * first3[i].s;
-          r[2] = z[i] * first3[i].c - first3[i].ay[j] * first3[i].s;
-        }
-      }
+  const int i = i_first + tid;
+  const bool keep = i < ns && kept(i);
+  // order-preserving compaction inside the CTA
+  const unsigned bal = __ballot_sync(0xffffffffu, keep);
+  if (lane == 0) warp_sum[warp] = __popc(bal);
+  __syncthreads();
+  int pos = before + __popc(bal & lanemask_lt());
+  for (int w = 0; w < warp; ++w) pos += warp_sum[w];
+  if (!keep) return;
+  const Decoded g = decode_seed(sc, cl, wd, tl, i, ns, na, nd, vec4);
+  const Frame f = seed_frame(vw, i, g.angle);
+  const float ax0 = f.ax[0], ax1 = f.ax[1], ax2 = f.ax[2], ay0 = f.ay[0], ay1 = f.ay[1], ay2 = f.ay[2], s = f.s, c = f.c;
+  float az0 = ax1 * ay2 - ax2 * ay1, az1 = ax2 * ay0 - ax0 * ay2, az2 = ax0 * ay1 - ax1 * ay0;
+  if (total == 3) {                                                     // z[pos] of the column-wise cross products
+    float z[3];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const float a0 = first3[0].ax[j], a1 = first3[1].ax[j], a2 = first3[2].ax[j];
+      const float b0 = first3[0].ay[j], b1 = first3[1].ay[j], b2 = first3[2].ay[j];
+      const float zz[3] = {a1 * b2 - a2 * b1, a2 * b0 - a0 * b2, a0 * b1 - a1 * b0};
+      z[j] = pos == 0 ? zz[0] : (pos == 1 ? zz[1] : zz[2]);
     }
+    az0 = z[0]; az1 = z[1]; az2 = z[2];
   }
+  float *r = out + (size_t)pos * 17;
+  r[0] = g.score; r[1] = g.width; r[2] = 0.02f; r[3] = g.depth;
+  r[4] = ax0; r[5] = ay0 * c + az0 * s; r[6] = az0 * c - ay0 * s;
+  r[7] = ax1; r[8] = ay1 * c + az1 * s; r[9] = az1 * c - ay1 * s;
+  r[10] = ax2; r[11] = ay2 * c + az2 * s; r[12] = az2 * c - ay2 * s;
+  r[13] = __ldg(ctr + 3 * (size_t)i); r[14] = __ldg(ctr + 3 * (size_t)i + 1); r[15] = __ldg(ctr + 3 * (size_t)i + 2);
+  r[16] = -1.f;
 }
 
 // ApproachNet's tail (reference models/modules.py:60-73): per seed the best of the V template views (torch.max over
@@ -238,7 +262,12 @@ extern "C" int b200_pred_decode(const float *objectness, const float *score, con
   if (ns > 0 && (!objectness || !score || !angle_cls || !width || !tolerance || !xyz || !view_xyz || !rows))
     return B200_EINVAL;
   const int vec4 = num_depth == 4 && (reinterpret_cast<uintptr_t>(angle_cls) & 15u) == 0;
-  pred_decode_kernel<<<b, DT, 0, (cudaStream_t)stream>>>(objectness, score, angle_cls, width, tolerance, xyz, view_xyz,
+  if (b > 65535) return B200_ECAPACITY;
+  if (ns == 0) {
+    B200_CUDA(cudaMemsetAsync(nrows, 0, sizeof(int32_t) * (size_t)b, (cudaStream_t)stream));
+    return 0;
+  }
+  pred_decode_kernel<<<dim3((unsigned)ceil_div(ns, DT), (unsigned)b), DT, 0, (cudaStream_t)stream>>>(objectness, score, angle_cls, width, tolerance, xyz, view_xyz,
                                                         ns, num_angle, num_depth, vec4, rows, nrows);
   B200_LAUNCH_CHECK();
   return 0;

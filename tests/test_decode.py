@@ -63,3 +63,25 @@ def test_pred_decode_kernel_equals_oracle(b200, oracle_mod, b, ns, a, d, seed):
     out = b200.pred_decode(ep)
     for i in range(b):
         check_rows(out[i].cpu().numpy(), oracle_mod.post.pred_decode(*[h[i] for h in heads]))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ns,kept", [(1024, (5, 300, 900)), (1024, (0, 1, 2)), (200, (127, 128, 199)), (3, (0, 1, 2))])
+def test_pred_decode_three_surviving_seeds(b200, oracle_mod, ns, kept):
+    """exactly three kept seeds: the reference's torch.cross without `dim` runs down the rows (loss_utils.py:89);
+    the three seeds lie in different CTAs of the decode kernel"""
+    import torch
+    rng = np.random.default_rng(ns + kept[1])
+    f = np.float32
+    a, d = 12, 4
+    obj = np.zeros((1, 2, ns), f)
+    obj[0, 0] = 1
+    obj[0, 1, list(kept)] = 2
+    heads = [obj, (rng.random((1, a, ns, d)) * 1.2 - 0.1).astype(f), rng.standard_normal((1, a, ns, d)).astype(f),
+             (rng.random((1, a, ns, d)) * 0.12 - 0.01).astype(f), (rng.random((1, a, ns, d)) * 0.06).astype(f),
+             (rng.random((1, ns, 3)) * 0.6 - 0.3).astype(f), rng.standard_normal((1, ns, 3)).astype(f)]
+    ep = {k: torch.from_numpy(h).cuda() for k, h in zip(KEYS, heads)}
+    out = b200.pred_decode(ep)
+    want = oracle_mod.post.pred_decode(*[h[0] for h in heads])
+    assert want.shape == (3, 17)
+    check_rows(out[0].cpu().numpy(), want)
