@@ -36,11 +36,15 @@ collision_kernel(const double *__restrict__ scene, int n, const int32_t *__restr
   if (n_dev) n = min(n, __ldg(n_dev));               // scene length produced on the device
   if (m_dev) m = min(m, __ldg(m_dev));               // grasp count produced on the device (decode / compaction)
   const int g = blockIdx.x * CTH + threadIdx.x;
-  const int p0 = blockIdx.y * CPT;
+  // the scene is split EVENLY over the point tiles of the grid (sized for n_max / the SM count by the host): when the
+  // device-side n is a fraction of n_max every CTA still gets a slice, instead of a few CTAs of CPT points with one
+  // warp per scheduler waiting on fp64 latency while the rest of the grid exits
+  const int per = min(CPT, ((n + (int)gridDim.y - 1) / (int)gridDim.y + CU - 1) / CU * CU);
+  const int p0 = blockIdx.y * per;
   if (p0 >= n) return;
-  const int pn = min(CPT, n - p0);
+  const int pn = min(per, n - p0);
   // the tail of a short slice is NaN: every comparison below is false for it
-  for (int i = threadIdx.x; i < CPT * 3; i += CTH)
+  for (int i = threadIdx.x; i < per * 3; i += CTH)
     pts[i] = i < pn * 3 ? __ldg(scene + (size_t)p0 * 3 + i) : __longlong_as_double(0x7ff8000000000000LL);
   __syncthreads();
   if (g >= m) return;
@@ -106,6 +110,16 @@ static int collision_launch(const double *scene, int n, const int32_t *n_dev, co
                             const double *R, const double *thr, int st, int sr, int sh, int m,
                             const int32_t *m_dev, int32_t *counts, void *stream);
 
+// point tiles of the grid: slices of CPT points, or shorter ones (>= 32 points) while the grid is under four CTAs
+// per SM -- the kernel shares the scene evenly among whatever number of tiles it is given
+static int collision_point_tiles(int m, int n) {
+  const int gx = ceil_div(m, CTH);
+  int gy = ceil_div(n, CPT);
+  const int want = ceil_div(4 * b200_sm_count(), gx);
+  if (gy < want) gy = want < ceil_div(n, 32) ? want : ceil_div(n, 32);
+  return gy < 1 ? 1 : gy;
+}
+
 extern "C" int b200_collision_counts(const double *scene, int n, const double *T, const double *R,
                                      const double *thr, int m, int32_t *counts, void *stream) {
   return collision_launch(scene, n, nullptr, T, R, thr, 3, 9, 10, m, nullptr, counts, stream);
@@ -135,7 +149,7 @@ static int collision_launch(const double *scene, int n, const int32_t *n_dev, co
   if (n == 0) return 0;
   if (!scene || !T || !R || !thr) return B200_EINVAL;
   if (ceil_div(n, CPT) > 65535) return B200_ECAPACITY;
-  dim3 grid((unsigned)ceil_div(m, CTH), (unsigned)ceil_div(n, CPT));
+  dim3 grid((unsigned)ceil_div(m, CTH), (unsigned)collision_point_tiles(m, n));
   collision_kernel<<<grid, CTH, 0, cs>>>(scene, n, n_dev, T, R, thr, st, sr, sh, m, m_dev, counts);
   B200_LAUNCH_CHECK();
   return 0;
@@ -224,7 +238,7 @@ int b200i_collision_counts_rows(const double *scene, const int32_t *n_dev, int n
   if (n_max == 0) return 0;
   if (!scene) return B200_EINVAL;
   if (ceil_div(n_max, CPT) > 65535) return B200_ECAPACITY;
-  dim3 grid((unsigned)ceil_div(m_max, CTH), (unsigned)ceil_div(n_max, CPT));
+  dim3 grid((unsigned)ceil_div(m_max, CTH), (unsigned)collision_point_tiles(m_max, n_max));
   collision_kernel<<<grid, CTH, 0, st>>>(scene, n_max, n_dev, nullptr, nullptr, nullptr, 0, 0, 0, m_max, m_dev, counts, rows,
                                          fl, fw, ad);
   B200_LAUNCH_CHECK();

@@ -179,8 +179,9 @@ pred_decode_kernel(const float *__restrict__ objectness, const float *__restrict
 // this kernel looks them up -- the reference rebuilds the lattice in a Python loop and expands it to (B,S,V,3)
 // on every forward.  features is conv3's output [b, 2+V, s]; lanes = consecutive seeds, so every view row is read
 // coalesced.
-// A CTA is 32 seeds x 8 view slices: slice g scans the views g, g+8, ... (strict `>`, so the first maximum of its
-// own ascending sub-sequence), then the 8 candidates of a seed meet in shared memory (larger value, then lower index).
+// A CTA is 8 seeds x 32 view slices (128 CTAs per 1024 seeds, ~10 independent loads per thread): slice g scans the
+// views g, g+32, ... (strict `>`, so the first maximum of its own ascending sub-sequence), then the 32 candidates of a
+// seed meet in shared memory (larger value, then lower index).
 // NaN is treated as the largest value and the first NaN wins (torch.max propagates it).
 __device__ __forceinline__ bool view_better(float v, int k, float bv, int bk) {
   const bool vn = v != v, bn = bv != bv;
@@ -189,19 +190,22 @@ __device__ __forceinline__ bool view_better(float v, int k, float bv, int bk) {
   return k < bk;
 }
 
-__global__ void __launch_bounds__(256)
+constexpr int VSEEDS = 8;      // seeds per CTA (a 32-byte sector of every view row)
+constexpr int VSL = 32;        // view slices per CTA
+
+__global__ void __launch_bounds__(VSEEDS * VSL)
 view_select_kernel(const float *__restrict__ features, const float *__restrict__ views,
                    const float *__restrict__ frames, int s, int v, long long *__restrict__ top_inds,
                    float *__restrict__ top_score, float *__restrict__ vp_xyz, float *__restrict__ vp_rot) {
-  __shared__ float s_val[8][32];
-  __shared__ int s_idx[8][32];
-  const int scene = blockIdx.y, sx = threadIdx.x & 31, g = threadIdx.x >> 5;
-  const int i = blockIdx.x * 32 + sx;
+  __shared__ float s_val[VSL][VSEEDS];
+  __shared__ int s_idx[VSL][VSEEDS];
+  const int scene = blockIdx.y, sx = threadIdx.x % VSEEDS, g = threadIdx.x / VSEEDS;
+  const int i = blockIdx.x * VSEEDS + sx;
   const float *f = features + ((size_t)scene * (2 + v) + 2) * s + min(i, s - 1);
   int best = g < v ? g : 0;
   float bv = __ldg(f + (size_t)best * s);
-#pragma unroll 4
-  for (int k = g + 8; k < v; k += 8) {
+#pragma unroll 10
+  for (int k = g + VSL; k < v; k += VSL) {
     const float x = __ldg(f + (size_t)k * s);
     if (view_better(x, k, bv, best)) { bv = x; best = k; }
   }
@@ -210,7 +214,7 @@ view_select_kernel(const float *__restrict__ features, const float *__restrict__
   __syncthreads();
   if (g == 0 && i < s) {
 #pragma unroll
-    for (int q = 1; q < 8; ++q)
+    for (int q = 1; q < VSL; ++q)
       if (view_better(s_val[q][sx], s_idx[q][sx], bv, best)) { bv = s_val[q][sx]; best = s_idx[q][sx]; }
     s_idx[0][sx] = best;
     const size_t o = (size_t)scene * s + i;
@@ -218,9 +222,9 @@ view_select_kernel(const float *__restrict__ features, const float *__restrict__
     top_score[o] = bv;
   }
   __syncthreads();
-  // the 12 table floats of each seed, written by all 256 threads
-  for (int e = threadIdx.x; e < 32 * 12; e += 256) {
-    const int q = e / 12, c = e % 12, ii = blockIdx.x * 32 + q;
+  // the 12 table floats of each seed
+  for (int e = threadIdx.x; e < VSEEDS * 12; e += VSEEDS * VSL) {
+    const int q = e / 12, c = e % 12, ii = blockIdx.x * VSEEDS + q;
     if (ii >= s) break;
     const int k = s_idx[0][q];
     const size_t o = (size_t)scene * s + ii;
@@ -279,7 +283,7 @@ extern "C" int b200_view_select(const float *features, const float *views, const
   if (b == 0 || s == 0) return 0;
   if (!features || !views || !frames || !top_inds || !top_score || !vp_xyz || !vp_rot) return B200_EINVAL;
   if (b > 65535) return B200_ECAPACITY;
-  view_select_kernel<<<dim3((s + 31) / 32, b), 256, 0, (cudaStream_t)stream>>>(features, views, frames, s, v,
+  view_select_kernel<<<dim3((s + VSEEDS - 1) / VSEEDS, b), VSEEDS * VSL, 0, (cudaStream_t)stream>>>(features, views, frames, s, v,
                                                                                  top_inds, top_score, vp_xyz, vp_rot);
   B200_LAUNCH_CHECK();
   return 0;
