@@ -113,6 +113,7 @@ lib.b200_voxel_set_options.argtypes = [ctypes.c_uint]
 lib.b200_voxel_set_options.restype = None
 NMS_TRANS_INCLUSIVE, NMS_ROT_INCLUSIVE, NMS_SAME_OBJECT, NMS_FP32, NMS_ACOS = 1, 2, 4, 8, 16
 VOXEL_ORIGIN_AT_MIN = 1
+VOXEL_MULTI_CTA = 2
 lib.b200_fps_set_speculation.argtypes = [_i]
 lib.b200_fps_set_speculation.restype = None
 

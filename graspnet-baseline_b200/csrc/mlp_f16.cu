@@ -1576,7 +1576,14 @@ int launch(Params &p, cudaStream_t stream) {
     B200_CUDA(cudaFuncSetAttribute(mlp_f16_kernel<SRC_DENSE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
     attr_set.mark(dev);
   }
-  const int grid = p.tiles < b200_sm_count() ? p.tiles : b200_sm_count();
+  // as few CTAs as finish in the same number of tile rounds: 256 tiles on 148 SMs are two rounds either way, on 128
+  // CTAs the other 20 SMs stay free for the kernels of the other scenes in flight.
+  // (Negative result, round 2: a build of mlp_f16_kernel with 16 row warps -- half a K-slab per thread -- for the
+  // launches with ONE tile per CTA, SA3 / SA4 / heads, changed nothing: 32.4 -> 36.4, 30.1 -> 29.5, 28.7 -> 32.8 us.
+  // A lone tile's ~30 us is not its row threads' slab work.)
+  const int sms = b200_sm_count();
+  const int rounds = (p.tiles + sms - 1) / sms;
+  const int grid = rounds > 0 ? (p.tiles + rounds - 1) / rounds : 1;
   if (p.src == SRC_XYZ && p.pipelined) xyz_pipe_kernel<<<grid, XYZ_THREADS, smem, stream>>>(p);
   else if (p.src == SRC_XYZ) mlp_f16_kernel<SRC_XYZ, false><<<grid, NTHREADS, smem, stream>>>(p);
   else if (p.src == SRC_FEAT) mlp_f16_kernel<SRC_FEAT, false><<<grid, NTHREADS, smem, stream>>>(p);

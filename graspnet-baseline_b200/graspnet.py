@@ -505,15 +505,17 @@ class GraspNetEngine:
         ep = {'point_clouds': self.cloud, 'input_xyz': self.cloud, 'input_features': None}
         cloud = self.cloud
         P = self.post
+        npts = [sa.npoint for sa in sas]
         s_grid.wait_stream(main)
+        s_vox.wait_stream(main)
+        # SA1 sampling, the serial chain, is the FIRST node of the graph: a cluster launch takes ~25 us longer to get
+        # going than a plain one and holds up the submission of whatever follows it in capture order by as much
+        # (CUPTI timeline, profiles/r02_graph_timeline.txt) -- behind the grid / voxel nodes it started 30 us later
+        inds1 = ops.furthest_point_sampling(cloud, npts[0])
         with torch.cuda.stream(s_grid):
             grid = ops.query_grid_build(cloud, GRID_CELL) if cloud.shape[1] >= ops.GRID_QUERY_MIN_N else None
-        s_vox.wait_stream(main)
         with torch.cuda.stream(s_vox):
             voxels = [ops.voxel_down_sample(cloud[s].double(), P["voxel_size"]) for s in range(B)]
-        npts = [sa.npoint for sa in sas]
-        # SA1 sampling: the serial chain
-        inds1 = ops.furthest_point_sampling(cloud, npts[0])
         xyz1 = ops.gather_xyz(cloud, inds1, transposed=False)
         xyzs, inds = [xyz1], [inds1]
         nested = all(npts[l + 1] <= npts[l] for l in range(3))
@@ -527,12 +529,15 @@ class GraspNetEngine:
         with torch.cuda.stream(s_q):                   # coordinates-only work of the deeper levels
             for c in (s_chk if nested else []):
                 s_q.wait_stream(c)
-            for l in range(1, 4):
+            balls, ball_ready = [None], [None]
+            for l in range(1, 4):                      # each level's neighbour lists as soon as its samples exist:
                 ind = (ops.furthest_point_sampling_spec(xyzs[-1], npts[l], verdicts[:l]) if nested
                        else ops.furthest_point_sampling(xyzs[-1], npts[l]))
                 inds.append(ind)
                 xyzs.append(ops.gather_xyz(xyzs[-1], ind, transposed=False))
-            balls = [None] + [ops.ball_query(xyzs[l], xyzs[l - 1], sas[l].radius, sas[l].nsample) for l in range(1, 4)]
+                balls.append(ops.ball_query(xyzs[l], xyzs[l - 1], sas[l].radius, sas[l].nsample))
+                ball_ready.append(torch.cuda.Event())  # the level's grouped MLP waits for this, not for the whole
+                ball_ready[l].record(s_q)              # side stream (the three-nearest searches come after)
             nn = []
             for unknown, known in ((xyzs[2], xyzs[3]), (xyzs[1], xyzs[2])):
                 dist2, idx3 = ops.three_nn(unknown, known)
@@ -542,9 +547,10 @@ class GraspNetEngine:
         balls[0] = ops.ball_query(xyz1, cloud, sas[0].radius, sas[0].nsample, grid=grid)
         feats, feats_t = [None] * 4, [None] * 4
         feats[0], feats_t[0] = sas[0].pooled(cloud, xyz1, balls[0])
-        main.wait_stream(s_q)
         for l in range(1, 4):
+            main.wait_event(ball_ready[l])
             feats[l], feats_t[l] = sas[l].pooled(xyzs[l - 1], xyzs[l], balls[l], features_t=feats_t[l - 1])
+        main.wait_stream(s_q)
         for l in range(4):
             ep['sa%d_xyz' % (l + 1)], ep['sa%d_features' % (l + 1)] = xyzs[l], feats[l]
         ep['sa1_inds'], ep['sa2_inds'] = inds[0], inds[1]
@@ -597,7 +603,7 @@ class GraspNetEngine:
         for c in (s_chk if nested else []):
             main.wait_stream(c)
         ep['kept'] = kept
-        hold += [grid, voxels, verdicts, balls, nn, feats_t, inds, xyzs]
+        hold += [grid, voxels, verdicts, balls, ball_ready, nn, feats_t, inds, xyzs]
         ep['_hold'] = hold
         return ep
 

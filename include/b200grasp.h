@@ -361,6 +361,8 @@ size_t b200_grasp_nms_workspace(int m);
 #define B200_NMS_FP32 8u             /* pair arithmetic in fp32                           (default: fp64)           */
 #define B200_NMS_ACOS 16u            /* compare acos(clip((tr - 1) / 2)) with the angle   (default: cosines)        */
 #define B200_VOXEL_ORIGIN_AT_MIN 1u  /* voxel grid origin = min_bound                     (default: - voxel / 2)    */
+#define B200_VOXEL_MULTI_CTA 2u      /* not a choice of the restatement: always take the multi-launch path (library sort)
+                                      * instead of the single-CTA kernel for clouds of <= 32768 points; same output */
 void b200_grasp_nms_set_options(unsigned flags);
 void b200_voxel_set_options(unsigned flags);
 

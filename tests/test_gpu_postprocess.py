@@ -175,6 +175,48 @@ def test_nms_and_voxel_switches_follow_the_oracle(b200, oracle_mod):
     assert default.shape != shifted.shape or (default != shifted).any()
 
 
+@pytest.mark.parametrize("n,voxel,special", [(1, 0.01, ""), (5, 0.01, ""), (1023, 0.01, ""), (1024, 0.01, ""),
+                                             (1025, 0.01, "dup"), (20000, 0.01, ""), (20000, 0.0004, ""),
+                                             (20000, 0.01, "bad"), (32768, 0.003, "dup"), (4000, 0.01, "allbad"),
+                                             (20000, 5.0, ""), (20000, 0.01, "origin"), (20000, 0.0001, ""), (22528, 0.01, "bad")])
+def test_voxel_single_cta_path_equals_multi_launch_path_and_oracle(b200, oracle_mod, n, voxel, special):
+    """clouds of <= 32768 points are down-sampled by ONE single-CTA kernel (keys, radix sort over the bits in use,
+    run heads, means); B200_VOXEL_MULTI_CTA forces the multi-launch path with the library sort.  Same rows, same
+    counts, bit for bit, and equal to the oracle's restatement -- including duplicates (long runs), excluded points,
+    > 8 bits per axis, > 32 bits in all or > 22528 points (the sort leaves shared memory for the workspace) and a cloud
+    inside one voxel (no pass at all)"""
+    from b200grasp import _abi
+    lib = _abi.lib
+    rng = np.random.default_rng(n)
+    cloud = b200.synth.tabletop_cloud(n, 21).astype(np.float64)
+    if "dup" in special:
+        cloud[n // 2:] = cloud[rng.integers(0, n // 2, n - n // 2)]
+    if special == "bad":
+        cloud[3] = np.nan
+        cloud[n - 1, 2] = -np.inf
+        cloud[777] = [4e5, 0.1, 0.6]
+    if special == "allbad":
+        cloud[:] = np.nan
+    flags = _abi.VOXEL_ORIGIN_AT_MIN if special == "origin" else 0
+    pts = torch.from_numpy(cloud).cuda()
+    res = []
+    try:
+        for extra in (0, _abi.VOXEL_MULTI_CTA):
+            lib.b200_voxel_set_options(flags | extra)
+            out, nvox, nbad = b200.ops.voxel_down_sample(pts, voxel, return_bad=True)
+            res.append((out[: int(nvox.item())].cpu().numpy(), int(nbad.item())))
+    finally:
+        lib.b200_voxel_set_options(0)
+    (small, bad_s), (multi, bad_m) = res
+    assert bad_s == bad_m == {"bad": 3, "allbad": n}.get(special, 0)
+    assert small.shape == multi.shape and (small == multi).all()
+    if special != "allbad":
+        want = oracle_mod.post.voxel_down_sample(cloud, voxel, origin_at_min=special == "origin")
+        assert small.shape == want.shape and (small == want).all()
+    else:
+        assert len(small) == 0
+
+
 @pytest.mark.parametrize("m,pad,flags", [(2048, 0, 0), (1500, 37, 0), (129, 0, 0), (1000, 24, "same_object"),
                                          (640, 0, "fp32"), (1, 0, 0), (0, 16, 0)])
 def test_fused_chain_equals_separate_calls(b200, m, pad, flags):
