@@ -69,7 +69,7 @@ def build_mlp_profile():
     """Instrumented fused-MLP library (clock64 timeline of CTA 0) for tools/mlp_prof.py; not shipped."""
     out = os.path.join(HERE, "lib", "libb200mlp_prof.so")
     cmd = [NVCC, "-shared", "-o", out, os.path.join(CSRC, "mlp_fused.cu"), os.path.join(CSRC, "mlp_f16.cu"),
-           os.path.join(CSRC, "common.cu"), "-DMLP_PROFILE"] + FLAGS
+           os.path.join(CSRC, "common.cu"), "-DMLP_PROFILE"] + FLAGS + [a for a in sys.argv if a.startswith("-D")]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode:
         sys.stderr.write(r.stdout + r.stderr)

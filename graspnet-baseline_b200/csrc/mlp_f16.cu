@@ -135,7 +135,11 @@ __device__ unsigned long long g_mlp_prof[5][PROF_TILES][PROF_EV];    // xyz_pipe
   } while (0)
 // inside one slab (thread 0, slabs SLAB_SEQ and SLAB_SEQ + 2): entry, TMEM read, math, slot wait, stores, proxy fence, arrive
 __device__ unsigned long long g_slab_prof[2][8];
-constexpr uint32_t SLAB_SEQ = 24;
+__device__ unsigned long long g_kernel_prof[8];                        // CTA 0 thread 0: entry, set-up done, exit (clock64)
+#ifndef SLAB_SEQ_VALUE
+#define SLAB_SEQ_VALUE 24
+#endif
+constexpr uint32_t SLAB_SEQ = SLAB_SEQ_VALUE;
 #define SPROF(seq, ev)                                                                      \
   do {                                                                                      \
     if (blockIdx.x == 0 && threadIdx.x == 0 && ((seq) == SLAB_SEQ || (seq) == SLAB_SEQ + 2)) \
@@ -156,6 +160,13 @@ __device__ __forceinline__ float warp_max_nan(float v) {
   float r;
   asm volatile("redux.sync.max.NaN.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
   return r;
+}
+// (redux.sync over half-warp member masks is far slower than four shuffle steps: SA3's pooling went 5.4k -> 23k cycles)
+// 32 bytes per lane in one request (LDG.E.256): the feature rows are gathered, every lane of a load touches a line of
+// its own and the L1 takes them one line per cycle -- half as many instructions is half as many line look-ups
+__device__ __forceinline__ void ldg256(const float4 *p, float4 &a, float4 &b) {
+  asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
 }
 __device__ __forceinline__ float pow2f(int e) {                      // 2^e, -126 <= e <= 127
   return __int_as_float((e + 127) << 23);
@@ -252,6 +263,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_f16_kernel(const Params p) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   const uint32_t sm = tc::smem_u32(smem_raw);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+#ifdef MLP_PROFILE
+  if (blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) g_kernel_prof[0] = (unsigned long long)clock64();
+#endif
   float4 *w1s = reinterpret_cast<float4 *>(smem_raw + p.off_consts);
   float *biases = reinterpret_cast<float *>(w1s + p.C0);              // [layer][MAXC]
   float *pools = reinterpret_cast<float *>(smem_raw + p.off_pool);    // [tile parity][entries][MAXC] raw maxima, then
@@ -281,6 +295,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_f16_kernel(const Params p) {
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem = *holder;
+#ifdef MLP_PROFILE
+  if (blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) g_kernel_prof[1] = (unsigned long long)clock64();
+#endif
   const int last = p.NG - 1;
   const int ntile = ((int)blockIdx.x < p.tiles) ? (p.tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;   // this CTA's tiles
   const int PS = p.S[1] < 2 ? p.S[1] : 2;                             // pipelined schedule: layer-3 slabs staged ahead
@@ -424,15 +441,30 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_f16_kernel(const Params p) {
       const float gmax = max_nan(max_nan(fabsf(gt.g0), fabsf(gt.g1)), fabsf(gt.g2));
       if (SRC == SRC_FEAT) {
         // the row's largest |feature| (a first pass over the 16-byte loads the slabs repeat, from L1 / L2)
+        // (sixteen 16-byte loads in flight per step: with one block of four per iteration the pass cost one L2 round
+        // trip per block, 6k cycles for 256 channels -- profiles/r02_mlp_timeline.txt)
         const int nb = p.C >> 4;
         float amax = gmax;
-        for (int b16 = q; b16 < nb; b16 += NQ) {
-          float4 f[4];
+#pragma unroll 1
+        for (int b0 = q; b0 < nb; b0 += 4 * NQ) {
+          float4 f[4][4];
 #pragma unroll
-          for (int c = 0; c < 4; ++c) f[c] = __ldg(gt.frow + 4 * b16 + c);
+          for (int u = 0; u < 4; ++u) {
+            const int b16 = b0 + u * NQ;
+            if (b16 < nb) {
+              ldg256(gt.frow + 4 * b16, f[u][0], f[u][1]);
+              ldg256(gt.frow + 4 * b16 + 2, f[u][2], f[u][3]);
+            } else {
 #pragma unroll
-          for (int c = 0; c < 4; ++c)
-            amax = max_nan(max_nan(amax, max_nan(fabsf(f[c].x), fabsf(f[c].y))), max_nan(fabsf(f[c].z), fabsf(f[c].w)));
+              for (int c = 0; c < 4; ++c) f[u][c] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+              amax = max_nan(max_nan(amax, max_nan(fabsf(f[u][c].x), fabsf(f[u][c].y))),
+                             max_nan(fabsf(f[u][c].z), fabsf(f[u][c].w)));
         }
         amax = row_max_exchange(it_, amax);
         bound0 = gt.valid ? amax : 0.f;
@@ -473,6 +505,43 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_f16_kernel(const Params p) {
         }
         return;
       }
+      if (SRC == SRC_FEAT) {
+        // K order of layer 1: [features (C) | x y z | zero pad], C % 16 == 0.  As for the dense source, the pair's next
+        // slab is loaded while this one is split and stored (a slab cost one L2 round trip before its first store)
+        const int nb = p.C >> 4;
+        auto loadf = [&](int s, float4 (&f)[CH / 4]) {
+#pragma unroll
+          for (int h16 = 0; h16 < CH / 16; ++h16) {
+            const int b16 = (s * KS + half * CH + 16 * h16) >> 4;
+            if (b16 < nb) {
+              ldg256(gt.frow + 4 * b16, f[4 * h16], f[4 * h16 + 1]);
+              ldg256(gt.frow + 4 * b16 + 2, f[4 * h16 + 2], f[4 * h16 + 3]);
+            } else {
+#pragma unroll
+              for (int c = 0; c < 4; ++c) f[4 * h16 + c] = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (b16 == nb) f[4 * h16] = make_float4(gt.g0, gt.g1, gt.g2, 0.f);
+            }
+          }
+        };
+        int s = (int)((cur.seq ^ (uint32_t)pair) & 1u);               // first slab with (seq + s) % 2 == pair
+        float4 nxt[CH / 4];
+        if (s < S0) loadf(s, nxt);
+        if (s == 1) cur.next(NA);
+#pragma unroll 1
+        for (; s < S0; s += 2) {
+          float v[CH];
+#pragma unroll
+          for (int c = 0; c < CH / 4; ++c) {
+            v[4 * c] = __fmul_rn(nxt[c].x, sc); v[4 * c + 1] = __fmul_rn(nxt[c].y, sc);
+            v[4 * c + 2] = __fmul_rn(nxt[c].z, sc); v[4 * c + 3] = __fmul_rn(nxt[c].w, sc);
+          }
+          if (s + 2 < S0) loadf(s + 2, nxt);
+          put_part(p, sm, v, row, cur, half);
+          cur.next(NA);
+          if (s + 1 < S0) cur.next(NA);
+        }
+        return;
+      }
 #pragma unroll 1
       for (int s = 0; s < S0; ++s, cur.next(NA)) {
         if ((int)(cur.seq & 1u) != pair) continue;
@@ -480,24 +549,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_f16_kernel(const Params p) {
 #pragma unroll
         for (int h16 = 0; h16 < CH / 16; ++h16) {
           const int ch0 = s * KS + half * CH + 16 * h16;
-          if (SRC == SRC_FEAT) {
-            // K order of layer 1: [features (C) | x y z | zero pad], C % 16 == 0
-            const int b16 = ch0 >> 4, nb = p.C >> 4;
-            float4 f[4];
-            if (b16 < nb) {
-#pragma unroll
-              for (int c = 0; c < 4; ++c) f[c] = __ldg(gt.frow + 4 * b16 + c);
-            } else {
-#pragma unroll
-              for (int c = 0; c < 4; ++c) f[c] = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (b16 == nb) f[0] = make_float4(gt.g0, gt.g1, gt.g2, 0.f);
-            }
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-              v[16 * h16 + 4 * c] = __fmul_rn(f[c].x, sc); v[16 * h16 + 4 * c + 1] = __fmul_rn(f[c].y, sc);
-              v[16 * h16 + 4 * c + 2] = __fmul_rn(f[c].z, sc); v[16 * h16 + 4 * c + 3] = __fmul_rn(f[c].w, sc);
-            }
-          } else if (ch0 < p.C0) {                                    // C0 % 16 == 0
+          if (ch0 < p.C0) {                                           // xyz source; C0 % 16 == 0
 #pragma unroll
             for (int c = 0; c < 16; ++c) {
               const float4 w = w1s[ch0 + c];
@@ -739,6 +791,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_f16_kernel(const Params p) {
       float bn = 0.f;
       int en = 0;
       gather_a(0); gather_b();
+#ifdef MLP_PROFILE
+      if (blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) g_kernel_prof[3] = (unsigned long long)clock64() + (gt.valid ? __float_as_uint(gt.pt[0]) & 0u : 0u);
+#endif
       // t = -1 is the prologue (S(0) only)
 #pragma unroll 1
       for (int t = -1; t < ntile; ++t) {
@@ -766,7 +821,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_f16_kernel(const Params p) {
           // stack: then a source longer than the ring would wait for MMAs that wait for this read)
           if (h == ((p.alias || last == 0) ? 1 : 0) && t + 1 < ntile) {
             prepare(t + 1, bn); en = warp_scale_exp(bn);
+#ifdef MLP_PROFILE
+            if (t == -1 && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) g_kernel_prof[4] = (unsigned long long)clock64() + ((unsigned)en & 0u);
+#endif
             emit_source(en);
+#ifdef MLP_PROFILE
+            if (t == -1 && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) g_kernel_prof[5] = (unsigned long long)clock64();
+#endif
             gather_a(t + 2); gather_b();
           }
           if (h == 0 && t >= 0) {
@@ -889,6 +950,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_f16_kernel(const Params p) {
   }
   tc::fence_before_sync();
   __syncthreads();
+#ifdef MLP_PROFILE
+  if (blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) g_kernel_prof[2] = (unsigned long long)clock64();
+#endif
   if (warp == MMA_WARP) {
     __syncwarp();
     tc::tmem_dealloc_512(tmem);
@@ -1598,6 +1662,9 @@ int launch(Params &p, cudaStream_t stream) {
 extern "C" int b200_mlp_f16_read_profile(unsigned long long *host) {
   return (int)cudaMemcpyFromSymbol(host, g_mlp_prof, sizeof(g_mlp_prof));
 }
+extern "C" int b200_mlp_f16_read_kernel_profile(unsigned long long *host) {
+  return (int)cudaMemcpyFromSymbol(host, g_kernel_prof, sizeof(g_kernel_prof));
+}
 extern "C" int b200_mlp_f16_read_slab_profile(unsigned long long *host) {
   return (int)cudaMemcpyFromSymbol(host, g_slab_prof, sizeof(g_slab_prof));
 }
@@ -1650,7 +1717,7 @@ extern "C" int b200_group_feat_mlp_maxpool_f16(const float *xyz, const float *ne
   const long long lists = (long long)b * m;
   if (lists == 0) return 0;
   if (!xyz || !new_xyz || !feat_t || !idx || !out) return B200_EINVAL;
-  if ((reinterpret_cast<uintptr_t>(feat_t) & 15u) != 0) return B200_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(feat_t) & 31u) != 0) return B200_EINVAL;
   const long long tiles = ceil_div_ll(lists * ns, TM);
   if (lists > 0x7fffffffLL || tiles > 0x7fffffffLL) return B200_ECAPACITY;
   Params p = {};

@@ -138,7 +138,8 @@ int b200_group_mlp_maxpool_f16(const float *xyz, const float *new_xyz, const flo
                                int b, int n, int m, int ns, float radius, const float *w1, const float *b1, int c1,
                                float w1_norm1, float b1_max, const b200_mlp_layer *layers, float *out, float *out_t,
                                void *stream);
-/* b200_group_feat_mlp_maxpool in fp16x3: layers[0..2], layers[0] packed with feat_channels = c. */
+/* b200_group_feat_mlp_maxpool in fp16x3: layers[0..2], layers[0] packed with feat_channels = c; c % 16 == 0 and
+ * feat_t 32-byte aligned (the rows are gathered with 256-bit loads). */
 int b200_group_feat_mlp_maxpool_f16(const float *xyz, const float *new_xyz, const float *feat_t, const int32_t *idx,
                                     int b, int n, int m, int ns, int c, float radius, const b200_mlp_layer *layers,
                                     float *out, float *out_t, void *stream);

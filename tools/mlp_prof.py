@@ -49,19 +49,31 @@ with torch.no_grad():
             layers = mod._fused.get()
             run = lambda: ops.group_mlp_maxpool(xyz, new_xyz, idx, layers, radius=0.04, passes=3)
     else:
-        mod = fm.PointnetSAModuleVotes(npoint=1024, radius=0.1, nsample=32, mlp=[128, 128, 128, 256], normalize_xyz=True).cuda().eval()
-        xyz2 = new_xyz[:, :1024].contiguous()
-        idx = ops.ball_query(xyz2, new_xyz, 0.1, 32)
-        feat_t = torch.randn(1, 2048, 128, device="cuda")
+        npoint, radius, ns, cin, nin = {"sa2": (1024, 0.1, 32, 128, 2048), "sa3": (512, 0.2, 16, 256, 1024),
+                                        "sa4": (256, 0.3, 16, 256, 512)}[which]
+        mod = fm.PointnetSAModuleVotes(npoint=npoint, radius=radius, nsample=ns, mlp=[cin, 128, 128, 256], normalize_xyz=True).cuda().eval()
+        xyz2 = new_xyz[:, :npoint].contiguous()
+        new_xyz = new_xyz[:, :nin].contiguous()
+        idx = ops.ball_query(xyz2, new_xyz, radius, ns)
+        feat_t = torch.randn(1, nin, cin, device="cuda")
         if f16:
             l16 = mod._fused.get_f16()[1]
-            run = lambda: ops.group_feat_mlp_maxpool_f16(new_xyz, xyz2, feat_t, idx, l16, radius=0.1)
+            run = lambda: ops.group_feat_mlp_maxpool_f16(new_xyz, xyz2, feat_t, idx, l16, radius=radius)
         else:
             layers = mod._fused.get()
-            run = lambda: ops.group_feat_mlp_maxpool(new_xyz, xyz2, feat_t, idx, layers, radius=0.1, passes=3)
+            run = lambda: ops.group_feat_mlp_maxpool(new_xyz, xyz2, feat_t, idx, layers, radius=radius, passes=3)
     for _ in range(3):
         run()
 torch.cuda.synchronize()
+if f16 and which not in ("crop", "sa1"):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); run(); e1.record(); torch.cuda.synchronize()
+    kp = (ctypes.c_ulonglong * 8)()
+    prof.b200_mlp_f16_read_kernel_profile(kp)
+    print("kernel (CTA 0): entry -> set-up done %d cycles, -> exit %d cycles; CUDA events around the launch %.1f us"
+          % (kp[1] - kp[0], kp[2] - kp[0], e0.elapsed_time(e1) * 1e3))
+    print("prologue (thread 0): gathered %d, row bound known %d, source slabs out %d cycles after entry" % (kp[3] - kp[0], kp[4] - kp[0], kp[5] - kp[0]))
+    kernel_entry = kp[0]
 NG = 2
 xyzp = f16 and which in ("crop", "sa1")
 buf = (ctypes.c_ulonglong * ((5 if f16 else 3) * 16 * 8))()
@@ -83,6 +95,7 @@ elif f16:
     print(which, arith, "cycles relative to start; group rows = that group's k-th tile (tile 2k + g): start, gathered (before turn wait), "
           "source slabs out, acc(last-1) ready, mid epilogues out, acc(last) ready, last epilogue read, combine done; "
           "mma rows (per tile): first/last slab ready of the last two layers")
+    print("tile 0 start is %d cycles after kernel entry" % (t0 - kernel_entry))
     for k in range(8):
         for g in range(NG):
             print("tile %2d  g%d %s" % (k, g, " ".join("%7d" % (a[g, k, e] - t0) for e in range(8))))
