@@ -8,9 +8,7 @@ def us(r):
     return v / 1000 if u == 'ns' else v * 1000 if u == 'ms' else v
 names = [r['Kernel Name'] for r in rows]
 fps = [i for i, n in enumerate(names) if 'fps_multi' in n]
-start = fps[-1]
-while start > 0 and 'grid_bounds' not in names[start]:
-    start -= 1
+start = fps[-1]                       # the sampling chain is the first node of the graph
 tot = 0
 for r in rows[start:]:
     print("%8.2f  %s" % (us(r), r['Kernel Name'][:110])); tot += us(r)
