@@ -72,8 +72,8 @@ SIGNATURES = {
     "b200_query_grid_build": [_vp, _i, _i, _f, _vp, _sz, _vp],
     "b200_ball_query_prebuilt": [_vp, _vp, _i, _i, _i, _f, _i, _vp, _vp, _sz, _vp],
     "b200_mlp_f16_pack": [_vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp],
-    "b200_group_mlp_maxpool_f16": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp, _vp, _i, _f, _f, _lp, _vp, _vp, _vp],
-    "b200_group_feat_mlp_maxpool_f16": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _lp, _vp, _vp, _vp],
+    "b200_group_mlp_maxpool_f16": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp, _vp, _i, _f, _f, _lp, _vp, _vp, _vp, _vp],
+    "b200_group_feat_mlp_maxpool_f16": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _lp, _vp, _vp, _vp, _vp],
     "b200_pointwise_stack_f16": [_vp, _i, _vp, _i, _i, _i, _lp, _i, _i, _vp],
     "b200_cylinder_query_multi_prebuilt": [_vp, _vp, _vp, _i, _i, _i, _f, _f, ctypes.POINTER(_f), _i, _i, _vp, _vp, _sz, _vp],
 }

@@ -50,6 +50,7 @@ constexpr int CH = 32 / HALVES;                // channels of a slab per thread
 constexpr int ROWS = NQ * TM;                  // row threads
 constexpr int MMA_WARP = 4 * NQ;               // then the weight-loader warp
 constexpr int NTHREADS = ROWS + 64;
+static_assert(ROWS / 32 == 8, "the row-bound rider holds one partial maximum per row warp: 8");
 constexpr int SMEM_LIMIT = 227 * 1024;
 
 enum { SRC_XYZ = 0, SRC_FEAT = 1, SRC_DENSE = 2 };
@@ -96,6 +97,8 @@ struct Params {
   FastDiv fd_G, fd_m;                          // list number -> (batch, seed, depth slice) without divisions
   int tiles;
   float *out, *out_t;
+  float *out_rb;                               // [list][8]: per-warp partial maxima of |y| over the list's channels, or NULL
+  const float *feat_rb;                        // SRC_FEAT: the same rider of feat_t (row bound without scanning the row), or NULL
   // shared memory geometry
   int pool_entries;                            // pooling entries per tile (one per 32 rows, or per 16-row list)
   int NA;                                      // A ring slots
@@ -445,6 +448,18 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_f16_kernel(const Params p) {
         // trip per block, 6k cycles for 256 channels -- profiles/r02_mlp_timeline.txt)
         const int nb = p.C >> 4;
         float amax = gmax;
+        if (p.feat_rb) {
+          // the producer of feat_t left each row's bound beside it (eight per-warp partial maxima): 32 bytes instead
+          // of a pass over the row's C channels -- the pass was 6k (C = 128) to 8.5k cycles (C = 256) per tile
+          if (gt.valid) {
+            float4 r0, r1;
+            ldg256(reinterpret_cast<const float4 *>(p.feat_rb + ((long long)gt.bi * p.N + gt.i) * 8), r0, r1);
+            amax = max_nan(max_nan(max_nan(amax, max_nan(r0.x, r0.y)), max_nan(r0.z, r0.w)),
+                           max_nan(max_nan(r1.x, r1.y), max_nan(r1.z, r1.w)));
+          }
+          bound0 = gt.valid ? amax : 0.f;
+          return;
+        }
 #pragma unroll 1
         for (int b0 = q; b0 < nb; b0 += 4 * NQ) {
           float4 f[4][4];
@@ -720,6 +735,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_f16_kernel(const Params p) {
       for (int l = 0; l < lpt && (long long)q0 + l < p.Q; ++l) {
         const float *pl = pool + (l * epl) * MAXC;
         float *dst = p.out + (((long long)lbi * cout) * p.m + lseed) * p.G + lgi;
+        float ym = 0.f;
 #pragma unroll 1
         for (int c = q * TM + row; c < cout; c += ROWS) {
           float u = __fmul_rn(pl[c], pinv[l * epl]);
@@ -727,6 +743,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_f16_kernel(const Params p) {
           const float y = max_nan(__fadd_rn(u, bl[c]), floor_v);
           dst[(long long)c * p.m * p.G] = y;
           if (p.out_t) p.out_t[((long long)q0 + l) * cout + c] = y;
+          ym = max_nan(ym, fabsf(y));
+        }
+        if (p.out_rb) {                                // this warp's share of the list's row bound (see prepare())
+          ym = warp_max_nan(ym);
+          if (lane == 0) p.out_rb[((long long)q0 + l) * 8 + warp] = ym;
         }
         if (++lgi == p.G) {
           lgi = 0;
@@ -1391,6 +1412,7 @@ __global__ void __launch_bounds__(XYZ_THREADS, 1) xyz_pipe_kernel(const Params p
         for (int l = 0; l < lpt && (long long)q0 + l < p.Q; ++l) {
           const float *pl = pool + (l * epl) * MAXC;
           float *dst = p.out + (((long long)lbi * cout) * p.m + lseed) * p.G + lgi;
+          float ym = 0.f;
 #pragma unroll 1
           for (int c = (l & 1) == pg ? row : cout; c < cout; c += TM) {
             float u = __fmul_rn(pl[c], pinv[l * epl]);
@@ -1398,6 +1420,14 @@ __global__ void __launch_bounds__(XYZ_THREADS, 1) xyz_pipe_kernel(const Params p
             const float y = max_nan(__fadd_rn(u, bl[c]), floor_v);
             dst[(long long)c * p.m * p.G] = y;
             if (p.out_t) p.out_t[((long long)q0 + l) * cout + c] = y;
+            ym = max_nan(ym, fabsf(y));
+          }
+          if (p.out_rb && (l & 1) == pg) {             // the group's four warps: partial row bounds 0..3, 4..7 unused
+            ym = warp_max_nan(ym);
+            if (lane == 0) {
+              p.out_rb[((long long)q0 + l) * 8 + (warp & 3)] = ym;
+              p.out_rb[((long long)q0 + l) * 8 + 4 + (warp & 3)] = 0.f;
+            }
           }
           if (++lgi == p.G) {
             lgi = 0;
@@ -1687,7 +1717,8 @@ extern "C" int b200_mlp_f16_pack(const float *w, int cout, int cin, int ldw, int
 extern "C" int b200_group_mlp_maxpool_f16(const float *xyz, const float *new_xyz, const float *rot, const int32_t *idx,
                                           int g, int b, int n, int m, int ns, float radius, const float *w1,
                                           const float *b1, int c1, float w1_norm1, float b1_max,
-                                          const b200_mlp_layer *layers, float *out, float *out_t, void *stream) {
+                                          const b200_mlp_layer *layers, float *out, float *out_t, float *out_row_bound,
+                                          void *stream) {
   if (g < 1 || b < 0 || n < 1 || m < 0 || ns < 1) return B200_EINVAL;
   if (ns != 16 && ns != 32 && ns != 64 && ns != 128) return B200_ECAPACITY;
   if (c1 < 1 || c1 > MAXC) return B200_ECAPACITY;
@@ -1704,13 +1735,14 @@ extern "C" int b200_group_mlp_maxpool_f16(const float *xyz, const float *new_xyz
   const int rc = fill_layers(p, layers, 2);
   if (rc) return rc;
   if (p.L[0].K != (c1 + KS - 1) / KS * KS || p.L[1].cout != p.L[1].N) return B200_EINVAL;
-  p.Q = lists; p.tiles = (int)tiles; p.out = out; p.out_t = out_t;
+  p.Q = lists; p.tiles = (int)tiles; p.out = out; p.out_t = out_t; p.out_rb = out_row_bound;
   return launch(p, (cudaStream_t)stream);
 }
 
 extern "C" int b200_group_feat_mlp_maxpool_f16(const float *xyz, const float *new_xyz, const float *feat_t,
-                                               const int32_t *idx, int b, int n, int m, int ns, int c, float radius,
-                                               const b200_mlp_layer *layers, float *out, float *out_t, void *stream) {
+                                               const float *feat_row_bound, const int32_t *idx, int b, int n, int m,
+                                               int ns, int c, float radius, const b200_mlp_layer *layers, float *out,
+                                               float *out_t, float *out_row_bound, void *stream) {
   if (b < 0 || n < 1 || m < 0 || ns < 1 || c < 4) return B200_EINVAL;
   if (ns != 16 && ns != 32 && ns != 64 && ns != 128) return B200_ECAPACITY;
   if (c % 4) return B200_ECAPACITY;
@@ -1728,7 +1760,8 @@ extern "C" int b200_group_feat_mlp_maxpool_f16(const float *xyz, const float *ne
   const int rc = fill_layers(p, layers, 3);
   if (rc) return rc;
   if (p.L[0].K != (c + 3 + KS - 1) / KS * KS || p.L[2].cout != p.L[2].N) return B200_EINVAL;
-  p.Q = lists; p.tiles = (int)tiles; p.out = out; p.out_t = out_t;
+  if ((reinterpret_cast<uintptr_t>(feat_row_bound) & 31u) != 0) return B200_EINVAL;
+  p.Q = lists; p.tiles = (int)tiles; p.out = out; p.out_t = out_t; p.out_rb = out_row_bound; p.feat_rb = feat_row_bound;
   return launch(p, (cudaStream_t)stream);
 }
 

@@ -250,21 +250,29 @@ def group_mlp_maxpool_f16(xyz, new_xyz, idx, first, layers, radius=0.0, rot=None
     c3 = layers[-1].cout
     out = torch.empty((b, c3, m, g), dtype=torch.float32, device=xyz.device)
     out_t = torch.empty((b, m, g, c3), dtype=torch.float32, device=xyz.device) if channels_last else None
+    rb = torch.empty((b * m * g, 8), dtype=torch.float32, device=xyz.device) if channels_last else None
     arr = _layer_array(layers)
     with torch.cuda.device(xyz.device):
         _abi.check(_lib.b200_group_mlp_maxpool_f16(_ptr(xyz), _ptr(new_xyz), _ptr(rot) if rot is not None else None,
                                                    _ptr(idx), g, b, n, m, ns, float(radius), _ptr(w1), _ptr(b1),
                                                    w1.shape[0], float(w1n), float(b1m), arr, _ptr(out),
-                                                   _ptr(out_t) if channels_last else None, _stream()),
+                                                   _ptr(out_t) if channels_last else None,
+                                                   _ptr(rb) if rb is not None else None, _stream()),
                    "group_mlp_maxpool_f16")
     if squeeze:
         out = out.view(b, c3, m)
         out_t = out_t.view(b, m, c3) if channels_last else None
+    if channels_last and rb is not None:
+        out_t.b200_row_bound = rb                      # the rider travels with THIS tensor object only (see below)
     return (out, out_t) if channels_last else out
 
 
 def group_feat_mlp_maxpool_f16(xyz, new_xyz, feat_t, idx, layers, radius=0.0, channels_last=False):
-    """group_feat_mlp_maxpool in fp16x3 arithmetic: layers = three F16Layer, the first packed with feat_channels = C"""
+    """group_feat_mlp_maxpool in fp16x3 arithmetic: layers = three F16Layer, the first packed with feat_channels = C.
+    Row-bound rider: the fp16x3 grouped kernels leave, beside a channels-last output, each row's largest magnitude
+    (attribute `b200_row_bound` of the returned out_t: (rows, 8) per-warp partial maxima).  When feat_t is such a tensor
+    OBJECT (not a view / slice / copy of it: those do not carry the attribute) the kernel reads the 32-byte rider
+    instead of scanning every gathered row for its magnitude; the result is bit-identical either way."""
     _chk(xyz, "xyz", torch.float32)
     _chk(new_xyz, "new_xyz", torch.float32)
     _chk(feat_t, "feat_t", torch.float32)
@@ -277,12 +285,20 @@ def group_feat_mlp_maxpool_f16(xyz, new_xyz, feat_t, idx, layers, radius=0.0, ch
     c3 = layers[-1].cout
     out = torch.empty((b, c3, m), dtype=torch.float32, device=xyz.device)
     out_t = torch.empty((b, m, c3), dtype=torch.float32, device=xyz.device) if channels_last else None
+    rb = torch.empty((b * m, 8), dtype=torch.float32, device=xyz.device) if channels_last else None
+    rb_in = getattr(feat_t, "b200_row_bound", None)
+    if rb_in is not None and (rb_in.shape != (b * n, 8) or rb_in.device != feat_t.device):
+        rb_in = None
     arr = _layer_array(layers)
     with torch.cuda.device(xyz.device):
-        _abi.check(_lib.b200_group_feat_mlp_maxpool_f16(_ptr(xyz), _ptr(new_xyz), _ptr(feat_t), _ptr(idx), b, n, m, ns,
-                                                        c, float(radius), arr, _ptr(out),
-                                                        _ptr(out_t) if channels_last else None, _stream()),
+        _abi.check(_lib.b200_group_feat_mlp_maxpool_f16(_ptr(xyz), _ptr(new_xyz), _ptr(feat_t),
+                                                        _ptr(rb_in) if rb_in is not None else None, _ptr(idx), b, n, m,
+                                                        ns, c, float(radius), arr, _ptr(out),
+                                                        _ptr(out_t) if channels_last else None,
+                                                        _ptr(rb) if channels_last else None, _stream()),
                    "group_feat_mlp_maxpool_f16")
+    if channels_last:
+        out_t.b200_row_bound = rb
     return (out, out_t) if channels_last else out
 
 

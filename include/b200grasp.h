@@ -133,16 +133,22 @@ size_t b200_mlp_f16_packed_bytes(int n_pad, int k_pad);
 int b200_mlp_f16_pack(const float *w, int cout, int cin, int ldw, int n_pad, int k_pad, int w_exp, int feat_channels,
                       void *packed, void *stream);
 /* b200_group_mlp_maxpool in fp16x3: layer 1 (w1[c1,3], b1[c1], on the CUDA cores; w1_norm1 = max_c (|w|_1 of row c),
- * b1_max = max |b1|), then layers[0..1] on the tensor cores (layers[0].k_pad = c1 rounded up to 32). */
+ * b1_max = max |b1|), then layers[0..1] on the tensor cores (layers[0].k_pad = c1 rounded up to 32).
+ * out_row_bound (may be NULL): [B * m * g][8] f32, 32-byte aligned -- the ROW-BOUND RIDER of out_t: for every output
+ * row eight partial maxima of |y| over its channels (one per writing warp, unused ones 0; the row's bound is their
+ * maximum).  Handed to the next module as feat_row_bound it replaces that module's pass over each gathered row for
+ * the row's magnitude (the fp16 scale is derived from it): same value, so the same bits come out. */
 int b200_group_mlp_maxpool_f16(const float *xyz, const float *new_xyz, const float *rot, const int32_t *idx, int g,
                                int b, int n, int m, int ns, float radius, const float *w1, const float *b1, int c1,
                                float w1_norm1, float b1_max, const b200_mlp_layer *layers, float *out, float *out_t,
-                               void *stream);
+                               float *out_row_bound, void *stream);
 /* b200_group_feat_mlp_maxpool in fp16x3: layers[0..2], layers[0] packed with feat_channels = c; c % 16 == 0 and
- * feat_t 32-byte aligned (the rows are gathered with 256-bit loads). */
-int b200_group_feat_mlp_maxpool_f16(const float *xyz, const float *new_xyz, const float *feat_t, const int32_t *idx,
-                                    int b, int n, int m, int ns, int c, float radius, const b200_mlp_layer *layers,
-                                    float *out, float *out_t, void *stream);
+ * feat_t 32-byte aligned (the rows are gathered with 256-bit loads).  feat_row_bound (may be NULL): the rider written
+ * beside feat_t by the call that produced it ([B * n][8]); out_row_bound as above. */
+int b200_group_feat_mlp_maxpool_f16(const float *xyz, const float *new_xyz, const float *feat_t,
+                                    const float *feat_row_bound, const int32_t *idx, int b, int n, int m, int ns, int c,
+                                    float radius, const b200_mlp_layer *layers, float *out, float *out_t,
+                                    float *out_row_bound, void *stream);
 /* Replaces the Conv1d / Conv2d(1x1) [+ BatchNorm + ReLU] stacks over point columns between the geometry ops
  * (pointnet2/pointnet2_modules.py:409-414, models/modules.py:52-57, 170-177, 215-222): x = [x1[B,c1,n] | x2[B,c2,n]]
  * through 1..3 layers in one launch, activations resident on the SM; each layer with y != NULL is written

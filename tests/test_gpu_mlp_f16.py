@@ -111,3 +111,36 @@ def test_grouped_f16_agrees_with_tf32x3_kernel(b200, batch):
         a = ops.group_feat_mlp_maxpool_f16(new_xyz, seeds, feat_t, idx2, sa2._fused.get_f16()[1], radius=0.1)
         b = ops.group_feat_mlp_maxpool(new_xyz, seeds, feat_t, idx2, sa2._fused.get(), radius=0.1, passes=3)
         assert rel(a, b.double()) <= REL
+
+
+@pytest.mark.parametrize("batch", [1, 3])
+def test_row_bound_rider_gives_the_same_bits_as_the_row_scan(b200, batch):
+    """the grouped fp16x3 kernels leave each output row's largest magnitude beside the channels-last output
+    (out_t.b200_row_bound); the next module reads that instead of scanning every gathered row.  SA1 -> SA2 -> SA3 with
+    the rider against the same chain on detached copies of the features (no rider): equal bits; the rider itself
+    equals the row maxima"""
+    from b200grasp import ops, synth, fused_modules as fm
+    xyz = torch.from_numpy(np.stack([synth.tabletop_cloud(20000, 50 + i) for i in range(batch)])).cuda()
+    inds = ops.furthest_point_sampling(xyz, 2048)
+    p1 = ops.gather_xyz(xyz, inds, transposed=False)
+    with torch.no_grad():
+        sa1 = fm.PointnetSAModuleVotes(npoint=2048, radius=0.04, nsample=64, mlp=[0, 64, 64, 128], normalize_xyz=True).cuda().eval()
+        sa2 = fm.PointnetSAModuleVotes(npoint=1024, radius=0.1, nsample=32, mlp=[128, 128, 128, 256], normalize_xyz=True).cuda().eval()
+        sa3 = fm.PointnetSAModuleVotes(npoint=512, radius=0.2, nsample=16, mlp=[256, 128, 128, 256], normalize_xyz=True).cuda().eval()
+        for i, sa in enumerate((sa1, sa2, sa3)):
+            synth.fill_state_dict(sa, 70 + i)
+        p2, p3 = p1[:, :1024].contiguous(), p1[:, :512].contiguous()
+        i1 = ops.ball_query(p1, xyz, 0.04, 64)
+        i2 = ops.ball_query(p2, p1, 0.1, 32)
+        i3 = ops.ball_query(p3, p2, 0.2, 16)
+        f1, t1 = sa1.pooled(xyz, p1, i1)
+        rb1 = t1.b200_row_bound
+        assert rb1.shape == (batch * 2048, 8)
+        assert torch.equal(rb1.max(dim=1).values.view(batch, 2048), t1.abs().amax(dim=2))
+        f2, t2 = sa2.pooled(p1, p2, i2, features_t=t1)
+        assert torch.equal(t2.b200_row_bound.max(dim=1).values.view(batch, 1024), t2.abs().amax(dim=2))
+        f3, t3 = sa3.pooled(p2, p3, i3, features_t=t2)
+        g2, u2 = sa2.pooled(p1, p2, i2, features_t=t1.clone())          # a copy carries no rider: the row scan runs
+        g3, u3 = sa3.pooled(p2, p3, i3, features_t=t2.clone())
+        assert not hasattr(t1.clone(), "b200_row_bound")
+        assert torch.equal(f2, g2) and torch.equal(t2, u2) and torch.equal(f3, g3) and torch.equal(t3, u3)
