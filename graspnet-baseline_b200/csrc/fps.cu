@@ -420,6 +420,8 @@ int launch_et(const float *xyz, int b, int n, int m, int C, int bits, FpsVerdict
 constexpr int SPEC_NT = 128;
 constexpr int SPEC_SUB = 8;            // lanes cooperating on one point
 constexpr int SPEC_PTS = SPEC_NT / SPEC_SUB;
+constexpr int CHK_SUB = 32;            // ... in the check kernel (a whole warp per point: 4x shorter serial walks)
+constexpr int CHK_PTS = SPEC_NT / CHK_SUB;
 constexpr int SPEC_MAX_M = 2048;       // prefix length the check supports (32 KB of shared memory)
 constexpr int SPEC_MAX_N = 4096;
 
@@ -451,7 +453,7 @@ fps_prefix_dist_kernel(const float *__restrict__ xyz, long long cstride, int n, 
   if (j < m && sub == 0) out[j] = j ? __float_as_int(md) : 0;   // idx[0] = verdict, starts as "identity holds"
 }
 
-// Eight lanes per point k, each owning a contiguous range of steps j.  Pass 1: minimum of the
+// CHK_SUB lanes per point k, each owning a contiguous range of steps j.  Pass 1: minimum of the
 // distances in the lane's range; an exclusive prefix-min over the eight lanes gives the running
 // min-distance at the start of each range; pass 2 walks the range again comparing with D_j.
 // A violation (k would have been picked instead of j) or a skipped j clears the verdict.
@@ -468,11 +470,11 @@ fps_prefix_check_kernel(const float *__restrict__ xyz, long long cstride, int n,
     if (j && (double)sq3_p2(a, b, c) <= 1e-3) bad = true;       // a skipped point is never picked
   }
   __syncthreads();
-  const int sub = threadIdx.x & (SPEC_SUB - 1);
-  const int k = blockIdx.x * SPEC_PTS + (threadIdx.x >> 3);
+  const int sub = threadIdx.x & (CHK_SUB - 1);
+  const int k = blockIdx.x * CHK_PTS + threadIdx.x / CHK_SUB;
   // steps per lane, rounded to an odd count: the 8 lanes of a group then read 8 different 16-byte
   // bank groups (an even stride puts all of them on the same banks: 8-way conflict, measured 12x slower)
-  const int len = ((m - 1 + SPEC_SUB - 1) / SPEC_SUB) | 1;
+  const int len = ((m - 1 + CHK_SUB - 1) / CHK_SUB) | 1;
   const int j0 = 1 + sub * len, j1 = min(m, j0 + len);
   float x = 0.f, y = 0.f, z = 0.f;
   bool live = false;
@@ -489,20 +491,23 @@ fps_prefix_check_kernel(const float *__restrict__ xyz, long long cstride, int n,
   // exclusive prefix-min over the 8 lanes of the group
   float run = mn;
 #pragma unroll
-  for (int o = 1; o < SPEC_SUB; o <<= 1) {
-    const float t = __shfl_up_sync(0xffffffffu, run, o, SPEC_SUB);
+  for (int o = 1; o < CHK_SUB; o <<= 1) {
+    const float t = __shfl_up_sync(0xffffffffu, run, o, CHK_SUB);
     if (sub >= o) run = fminf(run, t);
   }
-  float md = __shfl_up_sync(0xffffffffu, run, 1, SPEC_SUB);
+  float md = __shfl_up_sync(0xffffffffu, run, 1, CHK_SUB);
   if (sub == 0) md = 1e10f;
   if (live && !bad) {
     const unsigned pk = prio_of(k, bits);
+    // (no early exit: a violation is rare, and without the break the loop unrolls -- four independent distances in
+    // flight under the dependent running minimum)
+#pragma unroll 4
     for (int j = j0; j < j1; ++j) {
       const float4 c = sel[j - 1];
       md = fminf(sq3_p2(__fsub_rn(x, c.x), __fsub_rn(y, c.y), __fsub_rn(z, c.z)), md);
       const float dj = sel[j].w;
       if (md >= dj && k != j) {                                 // rare: decide with the tie priority
-        if (md > dj || pk < prio_of(j, bits)) { bad = true; break; }
+        if (md > dj || pk < prio_of(j, bits)) bad = true;
       }
     }
   }
@@ -623,7 +628,7 @@ static int fps_impl(const float *xyz, int b, int n, int m, const FpsVerdicts *ex
   } else if (g_spec_enabled && spec_eligible(b, n, m)) {
     fps_prefix_dist_kernel<<<dim3((unsigned)ceil_div(m, SPEC_PTS), (unsigned)b), SPEC_NT, 0, st>>>(xyz, n, n, m, idx);
     B200_LAUNCH_CHECK();
-    fps_prefix_check_kernel<<<dim3((unsigned)ceil_div(n, SPEC_PTS), (unsigned)b), SPEC_NT, 0, st>>>(xyz, n, n, m, bits, idx);
+    fps_prefix_check_kernel<<<dim3((unsigned)ceil_div(n, CHK_PTS), (unsigned)b), SPEC_NT, 0, st>>>(xyz, n, n, m, bits, idx);
     B200_LAUNCH_CHECK();
     spec.p[0] = idx;                                            // verdict of cloud c in idx[c * m]
     spec.stride[0] = m;
@@ -664,7 +669,7 @@ extern "C" int b200_fps_prefix_check(const float *xyz, int b, int n, int m, long
   fps_prefix_dist_kernel<<<dim3((unsigned)ceil_div(m, SPEC_PTS), (unsigned)b), SPEC_NT, 0, st>>>(xyz, cloud_stride, n, m,
                                                                                                verdict);
   B200_LAUNCH_CHECK();
-  fps_prefix_check_kernel<<<dim3((unsigned)ceil_div(n, SPEC_PTS), (unsigned)b), SPEC_NT, 0, st>>>(xyz, cloud_stride, n,
+  fps_prefix_check_kernel<<<dim3((unsigned)ceil_div(n, CHK_PTS), (unsigned)b), SPEC_NT, 0, st>>>(xyz, cloud_stride, n,
                                                                                                 m, bits, verdict);
   B200_LAUNCH_CHECK();
   return 0;
