@@ -507,15 +507,18 @@ class GraspNetEngine:
         P = self.post
         npts = [sa.npoint for sa in sas]
         s_grid.wait_stream(main)
-        s_vox.wait_stream(main)
+        for sp in s_post[:B]:                          # each scene's voxel down-sample runs on the stream that later
+            sp.wait_stream(main)                       # runs its post-processing chain (stream order = dependency)
         # SA1 sampling, the serial chain, is the FIRST node of the graph: a cluster launch takes ~25 us longer to get
         # going than a plain one and holds up the submission of whatever follows it in capture order by as much
         # (CUPTI timeline, profiles/r02_graph_timeline.txt) -- behind the grid / voxel nodes it started 30 us later
         inds1 = ops.furthest_point_sampling(cloud, npts[0])
         with torch.cuda.stream(s_grid):
             grid = ops.query_grid_build(cloud, GRID_CELL) if cloud.shape[1] >= ops.GRID_QUERY_MIN_N else None
-        with torch.cuda.stream(s_vox):
-            voxels = [ops.voxel_down_sample(cloud[s].double(), P["voxel_size"]) for s in range(B)]
+        voxels = []
+        for s in range(B):
+            with torch.cuda.stream(s_post[s % len(s_post)]):
+                voxels.append(ops.voxel_down_sample(cloud[s].double(), P["voxel_size"]))
         xyz1 = ops.gather_xyz(cloud, inds1, transposed=False)
         xyzs, inds = [xyz1], [inds1]
         nested = all(npts[l + 1] <= npts[l] for l in range(3))
@@ -573,7 +576,6 @@ class GraspNetEngine:
                                         ("objectness_score", "grasp_score_pred", "grasp_angle_cls_pred",
                                          "grasp_width_pred", "grasp_tolerance_pred", "fp2_xyz", "grasp_top_view_xyz")])
         ep['grasp_rows'], ep['grasp_nrows'] = rows, nrows
-        main.wait_stream(s_vox)
         kept = []
         for sp in s_post[:B]:
             sp.wait_stream(main)
