@@ -47,8 +47,9 @@ UNIT = "scenes/s"
 WORKLOAD = ("cfg2: GraspNet inference (seeded random weights, eval), batch 1, 20000 pts -> SA 2048/1024/512/256 -> "
             "1024 seeds, 300 views / 12 angles / 4 depths, pred_decode, collision (voxel 0.01, approach 0.05, "
             "thresh 0.01) of the decoded grasps + NMS")
-PIPE_DEPTH = 16           # scenes in flight (tools/pipe_window.py, round 2: 20-scene windows / steady state at depth
-                          # 4: 2730 / 2862, 8: 3054 / 3460, 12: 3335 / 3488, 16: 3344 / 3684 scenes/s)
+PIPE_DEPTH = 24           # scenes in flight (tools/pipe_window.py, round 2 final code, 20-scene windows / steady state at
+                          # depth 16: 3466 / 3890, 20: 3712 / 3976, 24: 3711 / 3949, 32: 3709 / 3959 scenes/s; the slots'
+                          # few-tile fused-MLP launches run 4 tiles per CTA: GraspNetPipeline(tiles_per_cta))
 POOL = 640                # different clouds the timed stream rotates through (640 x 240 kB = 154 MB > L2)
 WEIGHT_SEED = 12          # synth.fill_state_dict seed: every seed passes the objectness test -> 1024 grasps per scene
 SA_CFG = [(2048, 0.04, 64, 0), (1024, 0.1, 32, 128), (512, 0.2, 16, 256), (256, 0.3, 16, 256)]

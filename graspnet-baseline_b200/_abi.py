@@ -114,10 +114,12 @@ lib.b200_voxel_set_options.restype = None
 NMS_TRANS_INCLUSIVE, NMS_ROT_INCLUSIVE, NMS_SAME_OBJECT, NMS_FP32, NMS_ACOS = 1, 2, 4, 8, 16
 VOXEL_ORIGIN_AT_MIN = 1
 VOXEL_MULTI_CTA = 2
+lib.b200_mlp_f16_set_tiles_per_cta.argtypes = [_i]
+lib.b200_mlp_f16_set_tiles_per_cta.restype = None
 lib.b200_fps_set_speculation.argtypes = [_i]
 lib.b200_fps_set_speculation.restype = None
 
-EXPORTS = sorted(list(SIGNATURES) + ["b200_grasp_nms_workspace", "b200_voxel_down_sample_workspace", "b200_query_grid_workspace", "b200_collision_mask_workspace", "b200_grasp_post_chain_workspace", "b200_mlp_f16_packed_bytes", "b200_label_object_table_bytes", "b200_grasp_nms_set_options", "b200_voxel_set_options", "b200_error_string", "b200_version", "b200_launch_count"])
+EXPORTS = sorted(list(SIGNATURES) + ["b200_grasp_nms_workspace", "b200_voxel_down_sample_workspace", "b200_query_grid_workspace", "b200_collision_mask_workspace", "b200_grasp_post_chain_workspace", "b200_mlp_f16_packed_bytes", "b200_label_object_table_bytes", "b200_grasp_nms_set_options", "b200_voxel_set_options", "b200_mlp_f16_set_tiles_per_cta", "b200_error_string", "b200_version", "b200_launch_count"])
 
 
 def check(code, what):

@@ -1642,6 +1642,8 @@ int plan_smem(Params &p) {
   return (int)(p.off_holder + 16);
 }
 
+int g_tiles_per_cta = 1;
+
 int launch(Params &p, cudaStream_t stream) {
   p.fd_G = make_fastdiv((uint32_t)(p.G > 0 ? p.G : 1));
   p.fd_m = make_fastdiv((uint32_t)(p.m > 0 ? p.m : 1));
@@ -1675,8 +1677,12 @@ int launch(Params &p, cudaStream_t stream) {
   // (Negative result, round 2: a build of mlp_f16_kernel with 16 row warps -- half a K-slab per thread -- for the
   // launches with ONE tile per CTA, SA3 / SA4 / heads, changed nothing: 32.4 -> 36.4, 30.1 -> 29.5, 28.7 -> 32.8 us.
   // A lone tile's ~30 us is not its row threads' slab work.)
+  // b200_mlp_f16_set_tiles_per_cta(k): at least k tile rounds per CTA for the lock-step kernels (SA2-SA4, stacks) -- a
+  // lone tile costs its whole dependent chain (SA3: 44k cycles), a second one on the same CTA 16k more because the two
+  // row groups overlap tiles: fewer, longer CTAs do the same work in less SM-time (throughput) at a longer launch (latency)
   const int sms = b200_sm_count();
-  const int rounds = (p.tiles + sms - 1) / sms;
+  int rounds = (p.tiles + sms - 1) / sms;
+  if (p.src != SRC_XYZ && rounds < g_tiles_per_cta) rounds = g_tiles_per_cta < p.tiles ? g_tiles_per_cta : p.tiles;
   const int grid = rounds > 0 ? (p.tiles + rounds - 1) / rounds : 1;
   if (p.src == SRC_XYZ && p.pipelined) xyz_pipe_kernel<<<grid, XYZ_THREADS, smem, stream>>>(p);
   else if (p.src == SRC_XYZ) mlp_f16_kernel<SRC_XYZ, false><<<grid, NTHREADS, smem, stream>>>(p);
@@ -1699,6 +1705,8 @@ extern "C" int b200_mlp_f16_read_slab_profile(unsigned long long *host) {
   return (int)cudaMemcpyFromSymbol(host, g_slab_prof, sizeof(g_slab_prof));
 }
 #endif
+
+extern "C" void b200_mlp_f16_set_tiles_per_cta(int k) { g_tiles_per_cta = k < 1 ? 1 : (k > 64 ? 64 : k); }
 
 extern "C" size_t b200_mlp_f16_packed_bytes(int n_pad, int k_pad) { return (size_t)n_pad * k_pad * 4; }
 

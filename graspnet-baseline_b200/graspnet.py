@@ -661,12 +661,21 @@ class GraspNetPipeline:
         res = pipe.collect(slot)       # dict(nrows, mask, kept) of that scene (waits for it)
     """
 
-    def __init__(self, net, depth=2, num_point=20000, device="cuda", post=None):
+    def __init__(self, net, depth=2, num_point=20000, device="cuda", post=None, tiles_per_cta=None):
+        """tiles_per_cta: tiles per CTA of the few-tile fused-MLP launches in the slots' graphs (SA3 / SA4 / heads);
+        default: 4 from depth 4 on (a stream is SM-time-bound: fewer, longer CTAs; 1 / 2 / 4 / 8 / 16 tiles per CTA ran
+        3805 / 3845 / 3910 / 3905 / 3872 scenes/s at depth 16), 1 below (latency)"""
+        from . import _abi
         self.dev = torch.device(device)
         self.engines = [GraspNetEngine(net, batch=1, num_point=num_point, device=device, post=post)
                         for _ in range(depth)]
-        for eng in self.engines:
-            eng.run_graph()                             # capture now (capturing synchronises)
+        self.tiles_per_cta = int(tiles_per_cta) if tiles_per_cta else (4 if depth >= 4 else 1)
+        _abi.lib.b200_mlp_f16_set_tiles_per_cta(self.tiles_per_cta)
+        try:
+            for eng in self.engines:
+                eng.run_graph()                         # capture now (capturing synchronises)
+        finally:
+            _abi.lib.b200_mlp_f16_set_tiles_per_cta(1)
         torch.cuda.synchronize(self.dev)
         self.streams = [torch.cuda.Stream(device=self.dev) for _ in range(depth)]
         self.done = [None] * depth

@@ -144,3 +144,34 @@ def test_row_bound_rider_gives_the_same_bits_as_the_row_scan(b200, batch):
         g3, u3 = sa3.pooled(p2, p3, i3, features_t=t2.clone())
         assert not hasattr(t1.clone(), "b200_row_bound")
         assert torch.equal(f2, g2) and torch.equal(t2, u2) and torch.equal(f3, g3) and torch.equal(t3, u3)
+
+
+def test_tiles_per_cta_knob_does_not_change_results(b200):
+    """b200_mlp_f16_set_tiles_per_cta (GraspNetPipeline runs its slots' few-tile launches with 4 tiles per CTA): SA3-like
+    grouped module (64 tiles) and two heads (32 tiles each) with 1, 2, 4 and 64 tiles per CTA give the same bits"""
+    from b200grasp import ops, synth, _abi, fused_modules as fm
+    lib = _abi.lib
+    xyz = torch.from_numpy(synth.tabletop_cloud(20000, 3)[None]).cuda()
+    pts = ops.gather_xyz(xyz, ops.furthest_point_sampling(xyz, 1024), transposed=False)
+    wa, wt = make_layers([256, 128, 128, 36], 21), make_layers([256, 128, 128, 12], 22)
+    x = torch.relu(torch.randn(1, 256, 4096, device="cuda"))
+    la, lt = ops.f16_stack(wa, relu_last=False, n_pads=[128, 128, 48]), ops.f16_stack(wt, relu_last=False, n_pads=[128, 128, 48])
+    with torch.no_grad():
+        sa = fm.PointnetSAModuleVotes(npoint=512, radius=0.2, nsample=16, mlp=[256, 128, 128, 256], normalize_xyz=True).cuda().eval()
+        synth.fill_state_dict(sa, 9)
+        seeds = pts[:, :512].contiguous()
+        idx = ops.ball_query(seeds, pts, 0.2, 16)
+        feat_t = torch.relu(torch.randn(1, 1024, 256, device="cuda")) * 3
+        l16 = sa._fused.get_f16()[1]
+        res = []
+        try:
+            for k in (1, 2, 4, 64):
+                lib.b200_mlp_f16_set_tiles_per_cta(k)
+                a = ops.group_feat_mlp_maxpool_f16(pts, seeds, feat_t, idx, l16, radius=0.2)
+                ya, yt = ops.pointwise_stack_f16(x, la, layers2=lt)
+                torch.cuda.synchronize()
+                res.append((a.clone(), ya.clone(), yt.clone()))
+        finally:
+            lib.b200_mlp_f16_set_tiles_per_cta(1)
+    for r in res[1:]:
+        assert all(torch.equal(u, v) for u, v in zip(res[0], r))

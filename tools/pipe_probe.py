@@ -19,7 +19,7 @@ host = [bench.scene_cloud(5000 + i) for i in range(P)]
 pool = torch.from_numpy(np.stack(host)).cuda()
 K = 200
 for depth in [int(a) for a in sys.argv[1:]] or (1, 2, 3, 4):
-    pipe = b200grasp.graspnet.GraspNetPipeline(net, depth=depth)
+    pipe = b200grasp.graspnet.GraspNetPipeline(net, depth=depth, tiles_per_cta=int(os.environ.get('B200_TPC', '0')) or None)
     for mode in ("device", "host"):
         for rep in range(2):
             torch.cuda.synchronize()

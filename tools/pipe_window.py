@@ -9,7 +9,7 @@ net = bench.make_net("cuda")
 P = 640
 pool = torch.from_numpy(np.stack([bench.scene_cloud(5000 + i) for i in range(P)])).cuda()
 for depth in [int(a) for a in sys.argv[1:]] or (6, 8, 12, 16):
-    pipe = b200grasp.graspnet.GraspNetPipeline(net, depth=depth)
+    pipe = b200grasp.graspnet.GraspNetPipeline(net, depth=depth, tiles_per_cta=int(os.environ.get('B200_TPC', '0')) or None)
     for K in (20, 200):
         ms = []
         first = 0
