@@ -101,6 +101,8 @@ lib.b200_version.restype = _i
 lib.b200_launch_count.restype = ctypes.c_ulonglong
 lib.b200_fps_set_cluster.argtypes = [_i]
 lib.b200_fps_set_cluster.restype = None
+lib.b200_fps_set_max_cluster.argtypes = [_i]
+lib.b200_fps_set_max_cluster.restype = None
 lib.b200_fps_set_threads.argtypes = [_i]
 lib.b200_fps_set_threads.restype = None
 lib.b200_query_grid_set_threads.argtypes = [_i]

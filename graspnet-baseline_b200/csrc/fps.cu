@@ -533,7 +533,7 @@ bool spec_eligible(int b, int n, int m) {
   return m >= 2 && m <= n && m <= SPEC_MAX_M && n <= SPEC_MAX_N && b <= 65535;
 }
 
-int g_force_cluster = 0, g_force_threads = 0, g_spec_enabled = 1, g_multi_enabled = 1;
+int g_force_cluster = 0, g_force_threads = 0, g_spec_enabled = 1, g_multi_enabled = 1, g_max_cluster = 0;
 
 // Largest cluster size the device will co-schedule for this kernel family (16 needs the
 // non-portable opt-in and a GPC with 16 free SMs; fall back to the portable 8).
@@ -568,6 +568,10 @@ int max_cluster() {
 // Test / tuning hooks: force the cluster size and the CTA size (0 = automatic).
 extern "C" void b200_fps_set_cluster(int c) { g_force_cluster = c; }
 extern "C" void b200_fps_set_threads(int t) { g_force_threads = t; }
+// Cap on the AUTOMATIC cluster size (0 = none).  A stream of scenes is SM-time-bound and a 16-CTA cluster holds 16 SMs'
+// registers for the whole sampling chain: 8 CTAs take 395 us instead of 365 us per cloud but half the SMs (GraspNetPipeline
+// captures its slots with 8: +3 % scenes/s); small clouds (one CTA) are not affected.
+extern "C" void b200_fps_set_max_cluster(int c) { g_max_cluster = c; }
 extern "C" void b200_fps_set_speculation(int on) { g_spec_enabled = on; }
 extern "C" void b200_fps_set_multi(int on) { g_multi_enabled = on; }
 #ifdef FPS_PROFILE
@@ -598,6 +602,7 @@ static int fps_impl(const float *xyz, int b, int n, int m, const FpsVerdicts *ex
     // (tools/fps_multi_sweep.py: 8 CTAs from ~3k points, 16 beyond ~16k)
     if (g_multi_enabled) want = n <= 3072 ? 1 : (n <= 16384 || (long long)b * 16 > sms / 2) ? 8 : 16;
     while (want > 1 && (long long)b * want > sms) want /= 2;
+    if (g_max_cluster > 0 && want > g_max_cluster) want = g_max_cluster;   // throughput setting: see b200_fps_set_max_cluster
     if (g_force_cluster > 0) want = g_force_cluster;
     NT = 128;
     if (g_force_threads == 128 || g_force_threads == 256 || g_force_threads == 512) NT = g_force_threads;

@@ -661,7 +661,7 @@ class GraspNetPipeline:
         res = pipe.collect(slot)       # dict(nrows, mask, kept) of that scene (waits for it)
     """
 
-    def __init__(self, net, depth=2, num_point=20000, device="cuda", post=None, tiles_per_cta=None):
+    def __init__(self, net, depth=2, num_point=20000, device="cuda", post=None, tiles_per_cta=None, fps_cluster=None):
         """tiles_per_cta: tiles per CTA of the few-tile fused-MLP launches in the slots' graphs (SA3 / SA4 / heads);
         default: 4 from depth 4 on (a stream is SM-time-bound: fewer, longer CTAs; 1 / 2 / 4 / 8 / 16 tiles per CTA ran
         3805 / 3845 / 3910 / 3905 / 3872 scenes/s at depth 16), 1 below (latency)"""
@@ -670,12 +670,17 @@ class GraspNetPipeline:
         self.engines = [GraspNetEngine(net, batch=1, num_point=num_point, device=device, post=post)
                         for _ in range(depth)]
         self.tiles_per_cta = int(tiles_per_cta) if tiles_per_cta else (4 if depth >= 4 else 1)
+        # fps_cluster: cap on the sampling chain's cluster size in the slots' graphs (default 8 from depth 4 on: half
+        # the SMs of the 16-CTA cluster for 8 % more time per cloud; 0 / 16 = the latency setting)
+        self.fps_cluster = int(fps_cluster) if fps_cluster is not None else (8 if depth >= 4 else 0)
         _abi.lib.b200_mlp_f16_set_tiles_per_cta(self.tiles_per_cta)
+        _abi.lib.b200_fps_set_max_cluster(self.fps_cluster)
         try:
             for eng in self.engines:
                 eng.run_graph()                         # capture now (capturing synchronises)
         finally:
             _abi.lib.b200_mlp_f16_set_tiles_per_cta(1)
+            _abi.lib.b200_fps_set_max_cluster(0)
         torch.cuda.synchronize(self.dev)
         self.streams = [torch.cuda.Stream(device=self.dev) for _ in range(depth)]
         self.done = [None] * depth
