@@ -48,8 +48,9 @@ WORKLOAD = ("cfg2: GraspNet inference (seeded random weights, eval), batch 1, 20
             "1024 seeds, 300 views / 12 angles / 4 depths, pred_decode, collision (voxel 0.01, approach 0.05, "
             "thresh 0.01) of the decoded grasps + NMS")
 PIPE_DEPTH = 24           # scenes in flight (tools/pipe_window.py, round 2 final code, 20-scene windows / steady state at
-                          # depth 16: 3466 / 3890, 20: 3712 / 3976, 24: 3711 / 3949, 32: 3709 / 3959 scenes/s; the slots'
-                          # few-tile fused-MLP launches run 4 tiles per CTA: GraspNetPipeline(tiles_per_cta))
+                          # depth 16: 3466 / 3890, 20: 3712 / 3976, 24: 3711 / 3949, 32: 3709 / 3959 scenes/s; GraspNetPipeline's
+                          # throughput settings on top of that -- 4 tiles per CTA in the few-tile fused-MLP launches, the
+                          # sampling chain on 8-CTA clusters: 3818 / 4136)
 POOL = 640                # different clouds the timed stream rotates through (640 x 240 kB = 154 MB > L2)
 WEIGHT_SEED = 12          # synth.fill_state_dict seed: every seed passes the objectness test -> 1024 grasps per scene
 SA_CFG = [(2048, 0.04, 64, 0), (1024, 0.1, 32, 128), (512, 0.2, 16, 256), (256, 0.3, 16, 256)]
@@ -1053,7 +1054,9 @@ def run_ours(args, rank, world, local_rank):
                                                  "fp32 accumulate: fp32-grade) for the grouped MLPs and the 1x1-conv stacks "
                                                  "(csrc/mlp_f16.cu)",
                        "execution": "GraspNetPipeline: %d scenes in flight, each a batch-1 CUDA graph (GraspNetEngine, "
-                                    "forked over streams by data dependence) on its own stream" % PIPE_DEPTH,
+                                    "forked over streams by data dependence) on its own stream; throughput settings of the "
+                                    "slots: 4 tiles per CTA in the few-tile fused-MLP launches, FPS on 8-CTA clusters (the "
+                                    "latency leg uses one engine with the latency settings)" % PIPE_DEPTH,
                        "l2": "inputs rotate through a pool of %d different clouds (%d MB > 126 MB L2) resident in HBM; "
                              "the latency / per-kernel legs flush L2 (512 MiB write) between iterations" %
                              (POOL, POOL * 240000 // 1000000),
