@@ -1683,6 +1683,10 @@ int launch(Params &p, cudaStream_t stream) {
   const int sms = b200_sm_count();
   int rounds = (p.tiles + sms - 1) / sms;
   if (p.src != SRC_XYZ && rounds < g_tiles_per_cta) rounds = g_tiles_per_cta < p.tiles ? g_tiles_per_cta : p.tiles;
+  // ... and 4 k for the pipelined xyz kernels (their fill / drain is a few tiles long: SA1's 4 tiles per CTA take 37 us,
+  // 16 on a quarter of the CTAs ~3x that; measured with k = 4: steady stream 4151 -> 4201 scenes/s, 28 rounds: 4220)
+  if (p.src == SRC_XYZ && g_tiles_per_cta > 1 && rounds < 4 * g_tiles_per_cta)
+    rounds = 4 * g_tiles_per_cta < p.tiles ? 4 * g_tiles_per_cta : p.tiles;
   const int grid = rounds > 0 ? (p.tiles + rounds - 1) / rounds : 1;
   if (p.src == SRC_XYZ && p.pipelined) xyz_pipe_kernel<<<grid, XYZ_THREADS, smem, stream>>>(p);
   else if (p.src == SRC_XYZ) mlp_f16_kernel<SRC_XYZ, false><<<grid, NTHREADS, smem, stream>>>(p);

@@ -158,9 +158,10 @@ int b200_group_feat_mlp_maxpool_f16(const float *xyz, const float *new_xyz, cons
  * crop features; the two halves of a layer wider than 256 channels). */
 int b200_pointwise_stack_f16(const float *x1, int c1, const float *x2, int c2, int b, int n,
                              const b200_mlp_layer *layers, int nlayers, int nheads, void *stream);
-/* Scheduling knob of the fp16x3 entry points with features / dense inputs (not part of the reference's interface): at least
- * k tiles per CTA (default 1).  A launch of few tiles (SA3 / SA4 / the heads of ONE scene) then uses fewer CTAs for longer:
- * less SM-time per scene for a stream of scenes, a longer launch for a scene alone.  Results do not depend on it.
+/* Scheduling knob of the fp16x3 entry points (not part of the reference's interface): at least k tiles per CTA for the
+ * launches with features / dense inputs, 4 k for the xyz-only modules when k > 1 (default k = 1).  A launch of few tiles
+ * (SA3 / SA4 / the heads of ONE scene) then uses fewer CTAs for longer: less SM-time per scene for a stream of scenes, a
+ * longer launch for a scene alone.  Results do not depend on it.
  * Process-wide, applies to the launches (or graph captures) that follow. */
 void b200_mlp_f16_set_tiles_per_cta(int k);
 

@@ -163,12 +163,17 @@ def test_tiles_per_cta_knob_does_not_change_results(b200):
         idx = ops.ball_query(seeds, pts, 0.2, 16)
         feat_t = torch.relu(torch.randn(1, 1024, 256, device="cuda")) * 3
         l16 = sa._fused.get_f16()[1]
+        sa1 = fm.PointnetSAModuleVotes(npoint=1024, radius=0.04, nsample=64, mlp=[0, 64, 64, 128], normalize_xyz=True).cuda().eval()
+        synth.fill_state_dict(sa1, 10)
+        idx1 = ops.ball_query(pts, xyz, 0.04, 64)
+        first1, l1 = sa1._fused.get_f16()
         res = []
         try:
             for k in (1, 2, 4, 64):
                 lib.b200_mlp_f16_set_tiles_per_cta(k)
                 a = ops.group_feat_mlp_maxpool_f16(pts, seeds, feat_t, idx, l16, radius=0.2)
                 ya, yt = ops.pointwise_stack_f16(x, la, layers2=lt)
+                ya = torch.cat([ya.flatten(), ops.group_mlp_maxpool_f16(xyz, pts, idx1, first1, l1, radius=0.04).flatten()])
                 torch.cuda.synchronize()
                 res.append((a.clone(), ya.clone(), yt.clone()))
         finally:
