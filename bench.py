@@ -50,7 +50,7 @@ WORKLOAD = ("cfg2: GraspNet inference (seeded random weights, eval), batch 1, 20
 PIPE_DEPTH = 24           # scenes in flight (tools/pipe_window.py, round 2 final code, 20-scene windows / steady state at
                           # depth 16: 3466 / 3890, 20: 3712 / 3976, 24: 3711 / 3949, 32: 3709 / 3959 scenes/s; GraspNetPipeline's
                           # throughput settings on top of that -- 4 tiles per CTA in the few-tile fused-MLP launches, the
-                          # sampling chain on 8-CTA clusters: 3818 / 4136)
+                          # sampling chain on 8-CTA clusters, >= 16 tile rounds in the xyz kernels: 3867 / 4201)
 POOL = 640                # different clouds the timed stream rotates through (640 x 240 kB = 154 MB > L2)
 WEIGHT_SEED = 12          # synth.fill_state_dict seed: every seed passes the objectness test -> 1024 grasps per scene
 SA_CFG = [(2048, 0.04, 64, 0), (1024, 0.1, 32, 128), (512, 0.2, 16, 256), (256, 0.3, 16, 256)]
